@@ -1,0 +1,193 @@
+/*
+ * pillowfight_b200.h -- C-ABI of the B200 (sm_100a) build of libpillowfight's
+ * data-parallel hot path: ACE and the Gaussian / Sobel / Canny stencil chain.
+ *
+ * Everything here is plain C: pointers, ints, doubles.  No CUDA or torch types
+ * appear in a signature (a CUDA stream is passed as `void *`).
+ *
+ * REFERENCE CITATIONS.  The snapshot mounted at /root/reference holds only a
+ * "moved to GNOME GitLab" README (README.md:1-3) -- no C sources.  Where this
+ * header says "replaces <upstream file>", it names the upstream file of the
+ * published libpillowfight source tree (src/pillowfight/...) that the entry
+ * point stands in for; line numbers cannot be given because the file is not in
+ * the mount.  See DESIGN.md section 0 ("parity unpinned").
+ */
+#ifndef PILLOWFIGHT_B200_H
+#define PILLOWFIGHT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------ */
+/* Reference data types (upstream src/pillowfight/util.h)                    */
+/* ------------------------------------------------------------------------ */
+
+#define PF_NB_COLORS 4      /* RGBA, 32 bits per pixel */
+#define PF_NB_RGB_COLORS 3
+
+enum pf_color { COLOR_R = 0, COLOR_G = 1, COLOR_B = 2, COLOR_A = 3 };
+
+union pf_pixel {
+	uint32_t whole;
+	struct {
+		uint8_t r;
+		uint8_t g;
+		uint8_t b;
+		uint8_t a;
+	} color;
+	uint8_t channels[PF_NB_COLORS];
+};
+
+/* Row-major RGBA8 image, no row padding: pixel (x, y) is pixels[y*size.x+x]. */
+struct pf_bitmap {
+	struct {
+		int x;
+		int y;
+	} size;
+	union pf_pixel *pixels;
+};
+
+/* Row-major matrix of doubles: value (x, y) is values[y*size.x+x]. */
+struct pf_dbl_matrix {
+	struct {
+		int x;
+		int y;
+	} size;
+	double *values;
+};
+
+/* ------------------------------------------------------------------------ */
+/* Drop-in entry points: host bitmaps in, host bitmaps out.                  */
+/* `out->pixels` is caller-allocated, same size as `in`; in/out may alias.   */
+/* These are void like the reference's.  On a CUDA failure (no device, out   */
+/* of memory, launch error) they print one line to stderr, record the error  */
+/* (pf_b200_last_error) and leave `out` untouched; with the environment      */
+/* variable PF_B200_ABORT_ON_ERROR=1 they abort().  There is no CPU fallback. */
+/* ------------------------------------------------------------------------ */
+
+/* replaces upstream src/pillowfight/_ace.c: pf_ace().  Draws nb_samples
+ * (x, y) sample coordinates from libc rand() (caller seeds with srand()),
+ * then runs the ACE adjustment and scaling passes on the GPU.  nb_threads is
+ * accepted for signature compatibility and ignored. */
+void pf_apply_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
+		int nb_samples, double slope, double limit, int nb_threads);
+
+/* replaces upstream src/pillowfight/_gaussian.c: pf_gaussian(). */
+void pf_apply_gaussian(const struct pf_bitmap *in, struct pf_bitmap *out,
+		double sigma, int nb_stddev);
+
+/* replaces upstream src/pillowfight/_sobel.c: pf_sobel(). */
+void pf_apply_sobel(const struct pf_bitmap *in, struct pf_bitmap *out);
+
+/* replaces upstream src/pillowfight/_canny.c: pf_canny(). */
+void pf_apply_canny(const struct pf_bitmap *in, struct pf_bitmap *out);
+
+/* Upstream spellings of the same four functions (pillowfight.h). */
+void pf_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
+		int nb_samples, double slope, double limit, int nb_threads);
+void pf_gaussian(const struct pf_bitmap *in, struct pf_bitmap *out,
+		double sigma, int nb_stddev);
+void pf_sobel(const struct pf_bitmap *in, struct pf_bitmap *out);
+void pf_canny(const struct pf_bitmap *in, struct pf_bitmap *out);
+
+/* ------------------------------------------------------------------------ */
+/* Status-returning variants of the same calls (0 = success, else PF_B200_E*) */
+/* ------------------------------------------------------------------------ */
+
+#define PF_B200_OK            0
+#define PF_B200_EINVAL        1   /* bad argument (NULL, size <= 0, ...)     */
+#define PF_B200_ENODEV        2   /* no usable CUDA device                   */
+#define PF_B200_ECUDA         3   /* a CUDA runtime call or launch failed    */
+#define PF_B200_ETOOBIG       4   /* size beyond a stated maximum            */
+
+int pf_b200_last_error(void);                 /* of the calling thread */
+const char *pf_b200_last_error_string(void);  /* of the calling thread */
+int pf_b200_device_count(void);               /* 0 when CUDA is unusable */
+
+/* ACE with the sample table given explicitly: sample_xy holds nb_samples
+ * pairs (x0, y0, x1, y1, ...).  This is what pf_apply_ace calls after it has
+ * drawn the pairs (upstream _ace.c: create_random_pairs + pf_ace body). */
+int pf_b200_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
+		int nb_samples, const int *sample_xy, double slope, double limit);
+int pf_b200_gaussian(const struct pf_bitmap *in, struct pf_bitmap *out,
+		double sigma, int nb_stddev);
+int pf_b200_sobel(const struct pf_bitmap *in, struct pf_bitmap *out);
+int pf_b200_canny(const struct pf_bitmap *in, struct pf_bitmap *out);
+
+/* Draw nb_samples pairs the way pf_apply_ace does (x = rand() % width, then
+ * y = rand() % height, per sample; upstream _ace.c: create_random_pairs). */
+void pf_b200_ace_draw_samples(int nb_samples, int width, int height,
+		int *sample_xy);
+
+/* Pinned host memory for callers that want DMA-speed transfers through the
+ * entry points above (pageable pointers work too, through a staging copy). */
+void *pf_b200_host_alloc(size_t bytes);
+void pf_b200_host_free(void *ptr);
+
+/* ------------------------------------------------------------------------ */
+/* Device-resident entry points: RGBA8 pages already in HBM.                 */
+/* d_in / d_out are device pointers to width*height uint32 RGBA pixels on    */
+/* the current device; `stream` is a cudaStream_t (NULL = default stream).   */
+/* All work is enqueued on `stream`; nothing synchronises the host.          */
+/* They are the bodies the host-pointer entry points run between their       */
+/* copies (upstream: the same pf_gaussian/pf_sobel/pf_canny/pf_ace bodies).  */
+/* ------------------------------------------------------------------------ */
+
+int pf_b200_dev_gaussian(const uint32_t *d_in, uint32_t *d_out,
+		int width, int height, double sigma, int nb_stddev, void *stream);
+
+int pf_b200_dev_sobel(const uint32_t *d_in, uint32_t *d_out,
+		int width, int height, void *stream);
+
+/* Canny needs scratch for the hysteresis work lists:
+ * pf_b200_canny_scratch_bytes(width, height) bytes, 256-byte aligned.
+ * nb_pages pages of the same size, stored back to back, are processed by one
+ * call (page batches, BASELINE.json config 5); scratch is per call, not per
+ * page. */
+size_t pf_b200_canny_scratch_bytes(int width, int height);
+int pf_b200_dev_canny(const uint32_t *d_in, uint32_t *d_out,
+		int width, int height, int nb_pages,
+		void *d_scratch, size_t scratch_bytes, void *stream);
+
+/* Batched Gaussian / Sobel over nb_pages same-size pages stored back to back. */
+int pf_b200_dev_gaussian_batch(const uint32_t *d_in, uint32_t *d_out,
+		int width, int height, int nb_pages,
+		double sigma, int nb_stddev, void *stream);
+int pf_b200_dev_sobel_batch(const uint32_t *d_in, uint32_t *d_out,
+		int width, int height, int nb_pages, void *stream);
+
+/* ACE in two device passes so that row bands can be split across GPUs
+ * (BASELINE.json config 4):
+ *   1. pf_b200_dev_ace_scores: for rows [row_begin, row_end) of the page,
+ *      accumulate the per-pixel, per-channel scores into d_scores
+ *      (3 doubles per pixel of the band: plane-major R, G, B, each
+ *      (row_end-row_begin)*width doubles) and fold the band's per-channel
+ *      minimum / maximum into d_minmax (6 doubles: min R,G,B then max R,G,B;
+ *      initialise with pf_b200_dev_ace_minmax_init first).
+ *   2. (multi-GPU only) all-reduce d_minmax: min over the first 3, max over
+ *      the last 3.
+ *   3. pf_b200_dev_ace_scale: rescale the band's scores to RGBA8 rows of
+ *      d_out_band ((row_end-row_begin)*width pixels).
+ * d_samples: nb_samples * 2 ints (x, y) on the device.
+ * upstream _ace.c: ace_thread_adjustment (pass 1), ace_thread_scaling (pass 3). */
+int pf_b200_dev_ace_minmax_init(double *d_minmax, void *stream);
+int pf_b200_dev_ace_scores(const uint32_t *d_in, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, int nb_samples, double slope, double limit,
+		double *d_scores, double *d_minmax, void *stream);
+int pf_b200_dev_ace_scale(const double *d_scores, const double *d_minmax,
+		int width, int nb_rows, uint32_t *d_out_band, void *stream);
+
+/* Measures the FP64 FMA rate of the current device (the ACE roofline
+ * denominator): returns TFLOP/s (FMA = 2 flops), or a negative PF_B200_E*. */
+double pf_b200_fp64_peak_tflops(void);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* PILLOWFIGHT_B200_H */

@@ -1,0 +1,108 @@
+"""B200 (sm_100a) build of libpillowfight's hot path, with the call surface of
+the reference's `pillowfight` Python module for that path:
+
+    ace(img_in, slope=10, limit=1000, samples=100, seed=None)
+    gaussian(img_in, sigma=2.0, nb_stddev=5)
+    sobel(img_in)
+    canny(img_in)
+
+(upstream src/pillowfight/__init__.py -- not in the mount).
+`img_in` is a PIL image (converted to RGBA, a PIL RGBA image is returned, as
+upstream does) or an (H, W, 4) uint8 numpy array (an array is returned).
+
+All work is done by libpillowfight_b200.so through its C-ABI
+(include/pillowfight_b200.h); there is no CPU fallback and importing this
+package fails if the library has not been built.
+"""
+import ctypes
+import time
+
+import numpy as np
+
+from . import _capi
+from ._capi import PillowfightB200Error, PfBitmap, lib  # noqa: F401
+
+__all__ = ["ace", "gaussian", "sobel", "canny", "PillowfightB200Error",
+           "device_count"]
+
+_libc = ctypes.CDLL(None)
+
+
+def device_count():
+    return lib.pf_b200_device_count()
+
+
+def _to_array(img_in):
+    """-> (array (H, W, 4) uint8 C-contiguous, was_pil)"""
+    if isinstance(img_in, np.ndarray):
+        arr = np.ascontiguousarray(img_in, dtype=np.uint8)
+        if arr.ndim != 3 or arr.shape[2] != 4:
+            raise ValueError("expected an (H, W, 4) uint8 RGBA array")
+        return arr, False
+    # PIL image: same conversion as upstream (img_in.convert("RGBA"))
+    rgba = img_in.convert("RGBA")
+    arr = np.frombuffer(rgba.tobytes(), dtype=np.uint8).reshape(
+        rgba.size[1], rgba.size[0], 4)
+    return arr, True
+
+
+def _from_array(arr, was_pil):
+    if not was_pil:
+        return arr
+    from PIL import Image
+    return Image.frombytes("RGBA", (arr.shape[1], arr.shape[0]), arr.tobytes())
+
+
+def _bitmap(arr):
+    bm = PfBitmap()
+    bm.size.x = arr.shape[1]
+    bm.size.y = arr.shape[0]
+    bm.pixels = arr.ctypes.data
+    return bm
+
+
+def _run(fn, img_in, *args):
+    arr, was_pil = _to_array(img_in)
+    out = np.empty_like(arr)
+    bi, bo = _bitmap(arr), _bitmap(out)
+    _capi.check(fn(ctypes.byref(bi), ctypes.byref(bo), *args))
+    return _from_array(out, was_pil)
+
+
+def gaussian(img_in, sigma=2.0, nb_stddev=5):
+    """Gaussian blur of R, G and B (upstream pillowfight.gaussian)."""
+    return _run(lib.pf_b200_gaussian, img_in, float(sigma), int(nb_stddev))
+
+
+def sobel(img_in):
+    """Sobel gradient intensity (upstream pillowfight.sobel)."""
+    return _run(lib.pf_b200_sobel, img_in)
+
+
+def canny(img_in):
+    """Canny edge map, 0 / 255 (upstream pillowfight.canny)."""
+    return _run(lib.pf_b200_canny, img_in)
+
+
+def ace_samples(samples, width, height, seed):
+    """The sample table pf_apply_ace would draw after srand(seed)."""
+    _libc.srand(ctypes.c_uint(int(seed) & 0xFFFFFFFF))
+    xy = np.zeros(2 * int(samples), dtype=np.int32)
+    lib.pf_b200_ace_draw_samples(int(samples), int(width), int(height),
+                                 xy.ctypes.data_as(ctypes.POINTER(ctypes.c_int)))
+    return xy
+
+
+def ace(img_in, slope=10, limit=1000, samples=100, seed=None):
+    """Automatic Color Equalization (upstream pillowfight.ace).  The sample
+    coordinates come from libc rand() seeded with `seed`, on the host."""
+    if seed is None:
+        seed = int(time.time())
+    arr, was_pil = _to_array(img_in)
+    xy = ace_samples(samples, arr.shape[1], arr.shape[0], seed)
+    out = np.empty_like(arr)
+    bi, bo = _bitmap(arr), _bitmap(out)
+    _capi.check(lib.pf_b200_ace(ctypes.byref(bi), ctypes.byref(bo), int(samples),
+                                xy.ctypes.data_as(ctypes.POINTER(ctypes.c_int)),
+                                float(slope), float(limit)))
+    return _from_array(out, was_pil)

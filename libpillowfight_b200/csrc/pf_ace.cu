@@ -1,0 +1,531 @@
+// Automatic Color Equalization for sm_100a.
+//
+// Reference loop (upstream src/pillowfight/_ace.c, ace_thread_adjustment; the
+// file is not in the mount): for every pixel p and
+// every sample k farther than height/5,
+//     score[c] += saturate(slope * (p[c] - sample_k[c]), +-limit) / dist(p, k)
+//     denom    += limit / dist(p, k)
+// then score[c] /= denom, a page-wide min/max per channel, and a linear
+// rescale to 0..255.
+//
+// B200 formulation.  With w_k = 1/dist and L = limit/slope,
+//     score[c] = (slope/limit) * sum_k w_k * clamp(p[c]-s_k[c], -L, L) / sum_k w_k
+// so a common factor on w cancels.  The N samples are one table for the whole
+// page: a block gathers the sample pixels once into shared memory, and the
+// inner loop has no global loads at all.  Per pixel-sample pair the FP64 pipe
+// does: d^2 (1 add), one Newton step on MUFU.RSQ64H (3), three accumulating
+// FMAs and the weight sum (4).  The clamp runs on the integer pipe, two
+// pixels per instruction in 16-bit halves, and its result is spliced straight
+// into the high word of a double (4224 + c, exact), so no conversion
+// instruction is issued in the loop.  Samples whose skip circle contains the
+// whole tile are dropped per tile, those that cannot reach it skip the test.
+#include <cfloat>
+#include <cmath>
+
+#include "pf_common.cuh"
+
+namespace pfb {
+
+namespace {
+
+constexpr int kAceBlock = 128;      // threads = columns per block
+constexpr int kRowsPerThread = 4;   // P: pixels a thread carries (same column)
+constexpr int kTileRows = 32;       // rows a block walks (8 row groups)
+constexpr int kChunk = 512;         // samples staged in shared memory at a time
+constexpr double kBias = 4224.0;    // 4096 + 128: value spliced around c
+
+struct SampleEntry {
+	int sx;
+	uint32_t bias[3];   // (1152 - s_c) in both 16-bit halves
+};
+
+struct AceShared {
+	SampleEntry tbl[kChunk];                    // reordered: far samples, then straddling
+	double dy2[kChunk][kRowsPerThread];
+	int sy[kChunk];
+	double lut[511];                            // general path only
+	int n_far, n_str;
+};
+
+__device__ __forceinline__ double rsqrt_approx(double x)
+{
+	double y;
+	asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+	return y;
+}
+
+// 2/sqrt(d2) to ~2^-43 (NEWTON) or ~2^-22 relative; the factor 2 cancels.
+template <bool NEWTON>
+__device__ __forceinline__ double weight_of(double d2)
+{
+	const double y0 = rsqrt_approx(d2);
+	if (!NEWTON)
+		return y0;
+	const double t = d2 * y0;
+	const double q = fma(-t, y0, 3.0);
+	return y0 * q;
+}
+
+__device__ __forceinline__ uint32_t umin16x2(uint32_t a, uint32_t b)
+{
+	uint32_t d;
+	asm("min.u16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+	return d;
+}
+
+__device__ __forceinline__ uint32_t umax16x2(uint32_t a, uint32_t b)
+{
+	uint32_t d;
+	asm("max.u16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+	return d;
+}
+
+__device__ __forceinline__ void atomic_min_double(double *addr, double v)
+{
+	unsigned long long *a = reinterpret_cast<unsigned long long *>(addr);
+	unsigned long long old = *a;
+	while (v < __longlong_as_double((long long)old)) {
+		const unsigned long long seen = atomicCAS(a, old,
+				(unsigned long long)__double_as_longlong(v));
+		if (seen == old)
+			break;
+		old = seen;
+	}
+}
+
+__device__ __forceinline__ void atomic_max_double(double *addr, double v)
+{
+	unsigned long long *a = reinterpret_cast<unsigned long long *>(addr);
+	unsigned long long old = *a;
+	while (v > __longlong_as_double((long long)old)) {
+		const unsigned long long seen = atomicCAS(a, old,
+				(unsigned long long)__double_as_longlong(v));
+		if (seen == old)
+			break;
+		old = seen;
+	}
+}
+
+struct AceConst {
+	int w, h;
+	int row_begin, row_end;
+	int nb_samples;
+	int too_close2;        // (h/5)^2: pairs with d^2 below this are skipped
+	int clamp_l;           // L = limit/slope when it is an integer <= 127 (fast path)
+	double ratio;          // slope / limit
+	double slope, limit;
+};
+
+// Stages one chunk of the sample table for this block's tile.  Samples are
+// classified against the tile rectangle: "far" ones can never be skipped,
+// "inside" ones always are (dropped here), the rest straddle the skip circle.
+// Order inside each class is the sample order, so sums are reproducible.
+template <bool FAST>
+__device__ void stage_samples(AceShared &sh, const AceConst &cs,
+		const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
+		int k0, int kn, int x_lo, int x_hi, int y_lo, int y_hi)
+{
+	const int lane = threadIdx.x & 31;
+	if (threadIdx.x < 32) {
+		int n_far = 0, n_str = 0;
+		// pass 1: count far samples so that straddling ones go after them
+		for (int b = 0; b < kn; b += 32) {
+			const int k = b + lane;
+			bool far_ = false;
+			if (k < kn) {
+				const int sx = samples_xy[2 * (k0 + k)], sy = samples_xy[2 * (k0 + k) + 1];
+				const int dxm = max(max(x_lo - sx, sx - x_hi), 0);
+				const int dym = max(max(y_lo - sy, sy - y_hi), 0);
+				far_ = dxm * dxm + dym * dym >= cs.too_close2;
+			}
+			n_far += __popc(__ballot_sync(0xFFFFFFFFu, far_));
+		}
+		int pos_far = 0, pos_str = n_far;
+		for (int b = 0; b < kn; b += 32) {
+			const int k = b + lane;
+			bool far_ = false, str_ = false;
+			int sx = 0, sy = 0;
+			if (k < kn) {
+				sx = samples_xy[2 * (k0 + k)];
+				sy = samples_xy[2 * (k0 + k) + 1];
+				const int dxm = max(max(x_lo - sx, sx - x_hi), 0);
+				const int dym = max(max(y_lo - sy, sy - y_hi), 0);
+				const int dxM = max(abs(sx - x_lo), abs(sx - x_hi));
+				const int dyM = max(abs(sy - y_lo), abs(sy - y_hi));
+				far_ = dxm * dxm + dym * dym >= cs.too_close2;
+				str_ = !far_ && (dxM * dxM + dyM * dyM >= cs.too_close2);
+			}
+			const unsigned mf = __ballot_sync(0xFFFFFFFFu, far_);
+			const unsigned ms = __ballot_sync(0xFFFFFFFFu, str_);
+			const unsigned below = (1u << lane) - 1;
+			int dst = -1;
+			if (far_)
+				dst = pos_far + __popc(mf & below);
+			else if (str_)
+				dst = pos_str + __popc(ms & below);
+			if (dst >= 0) {
+				const uint32_t p = __ldg(in + (size_t)sy * cs.w + sx);
+				sh.tbl[dst].sx = sx;
+				sh.sy[dst] = sy;
+#pragma unroll
+				for (int c = 0; c < 3; c++) {
+					const uint32_t s = (p >> (8 * c)) & 0xFF;
+					sh.tbl[dst].bias[c] = FAST ? (1152u - s) * 0x00010001u : s;
+				}
+			}
+			pos_far += __popc(mf);
+			pos_str += __popc(ms);
+			n_str += __popc(ms);
+		}
+		if (lane == 0) {
+			sh.n_far = n_far;
+			sh.n_str = n_str;
+		}
+	}
+	__syncthreads();
+}
+
+// One sample against the P pixels of a thread.  TEST: the sample straddles the
+// skip circle on this tile, so each pair is tested (weight forced to 0).
+template <bool FAST, bool NEWTON, bool TEST>
+__device__ __forceinline__ void accumulate_sample(const AceShared &sh, int j, int x,
+		const uint32_t (&pix)[kRowsPerThread], const uint32_t (&pk)[kRowsPerThread / 2][3],
+		uint32_t lo2, uint32_t hi2, double too_close2,
+		double (&acc)[kRowsPerThread][3], double (&wsum)[kRowsPerThread])
+{
+	constexpr int P = kRowsPerThread;
+	const SampleEntry se = sh.tbl[j];
+	const int dx = x - se.sx;
+	const double dx2 = (double)(dx * dx);
+	double wgt[P];
+#pragma unroll
+	for (int r = 0; r < P; r++) {
+		const double d2 = dx2 + sh.dy2[j][r];
+		double wv = weight_of<NEWTON>(d2);
+		if (TEST && d2 < too_close2)
+			wv = 0.0;
+		wgt[r] = wv;
+		wsum[r] += wv;
+	}
+	if (FAST) {
+#pragma unroll
+		for (int g = 0; g < P / 2; g++) {
+#pragma unroll
+			for (int c = 0; c < 3; c++) {
+				uint32_t t = pk[g][c] + se.bias[c];
+				t = umin16x2(umax16x2(t, lo2), hi2);
+				const double va = __hiloint2double(
+						(int)__byte_perm(t, 0x40B00000u, 0x7604), 0);
+				const double vb = __hiloint2double(
+						(int)__byte_perm(t, 0x40B00000u, 0x7624), 0);
+				acc[2 * g][c] = fma(wgt[2 * g], va, acc[2 * g][c]);
+				acc[2 * g + 1][c] = fma(wgt[2 * g + 1], vb, acc[2 * g + 1][c]);
+			}
+		}
+	} else {
+#pragma unroll
+		for (int r = 0; r < P; r++) {
+#pragma unroll
+			for (int c = 0; c < 3; c++) {
+				const int v = (pix[r] >> (8 * c)) & 0xFF;
+				acc[r][c] = fma(wgt[r], sh.lut[v - (int)se.bias[c] + 255], acc[r][c]);
+			}
+		}
+	}
+}
+
+// The accumulation pass.  Thread = one column, kRowsPerThread rows at a time.
+// FAST: L = limit/slope is an integer <= 127, clamp on the integer pipe.
+// !FAST: any slope/limit, saturation values read from a 511-entry table.
+template <bool FAST, bool NEWTON>
+__global__ void __launch_bounds__(kAceBlock)
+ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
+		const AceConst cs, double *__restrict__ scores, double *__restrict__ minmax)
+{
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	AceShared &sh = *reinterpret_cast<AceShared *>(smem_raw);
+	constexpr int P = kRowsPerThread;
+
+	const int x = blockIdx.x * kAceBlock + threadIdx.x;
+	const int xc = min(x, cs.w - 1);
+	// Tiles sit on a page-wide grid of kTileRows rows whatever the band is, so
+	// a band split (multi-GPU) classifies and sums exactly like the whole page.
+	const int tile_y0 = (cs.row_begin / kTileRows + blockIdx.y) * kTileRows;
+	const int tile_y1 = min(cs.h, tile_y0 + kTileRows);         // exclusive
+	const int x_lo = blockIdx.x * kAceBlock;
+	const int x_hi = min(cs.w - 1, x_lo + kAceBlock - 1);
+	const int band_rows = cs.row_end - cs.row_begin;
+	const size_t plane = (size_t)band_rows * cs.w;
+
+	if (!FAST) {
+		for (int i = threadIdx.x; i < 511; i += kAceBlock) {
+			// the reference's calc_saturation on the integer difference i-255
+			double v = (double)(i - 255) * cs.slope;
+			if (v > cs.limit)
+				v = cs.limit;
+			else if (v < -cs.limit)
+				v = -cs.limit;
+			sh.lut[i] = v;
+		}
+	}
+
+	const uint32_t lo2 = (uint32_t)(1152 - cs.clamp_l) * 0x00010001u;
+	const uint32_t hi2 = (uint32_t)(1152 + cs.clamp_l) * 0x00010001u;
+	const double too_close2 = (double)cs.too_close2;
+
+	double mn[3] = { DBL_MAX, DBL_MAX, DBL_MAX };
+	double mx[3] = { -DBL_MAX, -DBL_MAX, -DBL_MAX };
+
+	bool staged = false;
+	for (int y0 = tile_y0; y0 < tile_y1; y0 += P) {
+		if (y0 + P <= cs.row_begin || y0 >= cs.row_end)
+			continue;       // row group outside this band (block-uniform)
+		// pixel values of this thread's P rows (rows past the page repeat the last)
+		uint32_t pix[P];
+#pragma unroll
+		for (int r = 0; r < P; r++)
+			pix[r] = __ldg(in + (size_t)min(y0 + r, cs.h - 1) * cs.w + xc);
+		// packed channel values: rows (0,1) and (2,3) share a register
+		uint32_t pk[P / 2][3];
+#pragma unroll
+		for (int g = 0; g < P / 2; g++)
+#pragma unroll
+			for (int c = 0; c < 3; c++)
+				pk[g][c] = ((pix[2 * g] >> (8 * c)) & 0xFF)
+					| (((pix[2 * g + 1] >> (8 * c)) & 0xFF) << 16);
+
+		double acc[P][3], wsum[P];
+#pragma unroll
+		for (int r = 0; r < P; r++) {
+			wsum[r] = 0.0;
+#pragma unroll
+			for (int c = 0; c < 3; c++)
+				acc[r][c] = 0.0;
+		}
+
+		for (int k0 = 0; k0 < cs.nb_samples; k0 += kChunk) {
+			const int kn = min(kChunk, cs.nb_samples - k0);
+			// (re)stage when the chunk or the tile changes; with one chunk the
+			// table is staged once per tile
+			if (!staged || cs.nb_samples > kChunk) {
+				staged = true;
+				__syncthreads();
+				stage_samples<FAST>(sh, cs, in, samples_xy, k0, kn,
+						x_lo, x_hi, tile_y0, tile_y1 - 1);
+			}
+			const int n_act = sh.n_far + sh.n_str;
+			__syncthreads();
+			for (int j = threadIdx.x; j < n_act; j += kAceBlock) {
+#pragma unroll
+				for (int r = 0; r < P; r++) {
+					const int dy = y0 + r - sh.sy[j];
+					sh.dy2[j][r] = (double)(dy * dy);
+				}
+			}
+			__syncthreads();
+
+			const int n_far = sh.n_far;
+			for (int j = 0; j < n_far; j++)
+				accumulate_sample<FAST, NEWTON, false>(sh, j, x, pix, pk, lo2, hi2,
+						too_close2, acc, wsum);
+			for (int j = n_far; j < n_act; j++)
+				accumulate_sample<FAST, NEWTON, true>(sh, j, x, pix, pk, lo2, hi2,
+						too_close2, acc, wsum);
+		}
+
+		// score = sum(sat/dist) / sum(limit/dist)
+#pragma unroll
+		for (int r = 0; r < P; r++) {
+			const int y = y0 + r;
+			if (y >= cs.row_begin && y < cs.row_end && y < tile_y1 && x < cs.w) {
+				const size_t o = (size_t)(y - cs.row_begin) * cs.w + x;
+				const double inv = 1.0 / wsum[r];
+#pragma unroll
+				for (int c = 0; c < 3; c++) {
+					double s;
+					if (FAST)
+						s = fma(-kBias, wsum[r], acc[r][c]) * inv * cs.ratio;
+					else
+						s = acc[r][c] * inv / cs.limit;
+					scores[c * plane + o] = s;
+					if (s < mn[c]) mn[c] = s;     // NaN never enters
+					if (s > mx[c]) mx[c] = s;
+				}
+			}
+		}
+	}
+
+	// block-wide min / max, then 6 atomics per block
+	__shared__ double red[2][3][kAceBlock / 32];
+#pragma unroll
+	for (int c = 0; c < 3; c++) {
+#pragma unroll
+		for (int d = 16; d > 0; d >>= 1) {
+			mn[c] = fmin(mn[c], __shfl_xor_sync(0xFFFFFFFFu, mn[c], d));
+			mx[c] = fmax(mx[c], __shfl_xor_sync(0xFFFFFFFFu, mx[c], d));
+		}
+		if ((threadIdx.x & 31) == 0) {
+			red[0][c][threadIdx.x >> 5] = mn[c];
+			red[1][c][threadIdx.x >> 5] = mx[c];
+		}
+	}
+	__syncthreads();
+	if (threadIdx.x < 3) {
+		const int c = threadIdx.x;
+		double a = red[0][c][0], b = red[1][c][0];
+		for (int i = 1; i < kAceBlock / 32; i++) {
+			a = fmin(a, red[0][c][i]);
+			b = fmax(b, red[1][c][i]);
+		}
+		atomic_min_double(minmax + c, a);
+		atomic_max_double(minmax + 3 + c, b);
+	}
+}
+
+__global__ void ace_minmax_init_kernel(double *minmax)
+{
+	if (threadIdx.x < 3)
+		minmax[threadIdx.x] = DBL_MAX;
+	else if (threadIdx.x < 6)
+		minmax[threadIdx.x] = -DBL_MAX;
+}
+
+// out[c] = trunc(clamp(255 * (score - min) / (max - min), 0, 255)); alpha 255.
+// Same operation order as the reference's linear scaling, true FP64 divide.
+__global__ void __launch_bounds__(256)
+ace_scale_kernel(const double *__restrict__ scores, const double *__restrict__ minmax,
+		size_t npix, uint32_t *__restrict__ out)
+{
+	double mn[3], span[3];
+#pragma unroll
+	for (int c = 0; c < 3; c++) {
+		mn[c] = minmax[c];
+		span[c] = minmax[3 + c] - mn[c];
+	}
+	for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < npix;
+			i += (size_t)gridDim.x * blockDim.x) {
+		uint32_t rgba = 0xFF000000u;
+#pragma unroll
+		for (int c = 0; c < 3; c++) {
+			const double s = __ldcs(scores + c * npix + i);
+			const double v = __ddiv_rn(__dmul_rn(255.0, __dadd_rn(s, -mn[c])), span[c]);
+			uint32_t q = 0;
+			if (v > 0.0)        // false for NaN
+				q = (uint32_t)__double2int_rz(fmin(v, 255.0));
+			rgba |= q << (8 * c);
+		}
+		out[i] = rgba;
+	}
+}
+
+// FP64 FMA rate probe: 8 independent chains per thread.
+__global__ void fp64_peak_kernel(double *sink, int iters, double a, double b)
+{
+	double v0 = threadIdx.x, v1 = v0 + 1, v2 = v0 + 2, v3 = v0 + 3;
+	double v4 = v0 + 4, v5 = v0 + 5, v6 = v0 + 6, v7 = v0 + 7;
+	for (int i = 0; i < iters; i++) {
+		v0 = fma(v0, a, b); v1 = fma(v1, a, b); v2 = fma(v2, a, b); v3 = fma(v3, a, b);
+		v4 = fma(v4, a, b); v5 = fma(v5, a, b); v6 = fma(v6, a, b); v7 = fma(v7, a, b);
+	}
+	const double s = v0 + v1 + v2 + v3 + v4 + v5 + v6 + v7;
+	if (s == 12345.678)
+		sink[0] = s;
+}
+
+}  // namespace
+
+int launch_ace_minmax_init(double *minmax, cudaStream_t st)
+{
+	ace_minmax_init_kernel<<<1, 32, 0, st>>>(minmax);
+	PFB_CUDA(cudaGetLastError());
+	return PF_B200_OK;
+}
+
+int launch_ace_scores(const uint32_t *in, const int *samples_xy,
+		const AceParams &p, double *scores, double *minmax, cudaStream_t st)
+{
+	if (p.nb_samples < 1)
+		return fail(PF_B200_EINVAL, "ace: nb_samples must be >= 1");
+	if (p.row_begin < 0 || p.row_end > p.h || p.row_begin >= p.row_end)
+		return fail(PF_B200_EINVAL, "ace: bad row band [%d, %d) of %d rows",
+				p.row_begin, p.row_end, p.h);
+	if (!(p.slope > 0.0) || !(p.limit > 0.0))
+		return fail(PF_B200_EINVAL, "ace: slope and limit must be positive");
+	if (p.w > 46340 || p.h > 32767)
+		return fail(PF_B200_ETOOBIG, "ace: page of %d x %d too large", p.w, p.h);
+
+	AceConst cs;
+	cs.w = p.w;
+	cs.h = p.h;
+	cs.row_begin = p.row_begin;
+	cs.row_end = p.row_end;
+	cs.nb_samples = p.nb_samples;
+	const int tc = p.h / 5;
+	cs.too_close2 = tc * tc;
+	cs.slope = p.slope;
+	cs.limit = p.limit;
+	cs.ratio = p.slope / p.limit;
+	// fast path: saturate(slope*d) == slope*clamp(d, -L, L) with integer L <= 127
+	const double l = p.limit / p.slope;
+	const bool fast = l >= 1.0 && l <= 127.0 && l == floor(l) && p.slope * l == p.limit;
+	cs.clamp_l = fast ? (int)l : 0;
+
+	dim3 grid((p.w + kAceBlock - 1) / kAceBlock,
+			(p.row_end - 1) / kTileRows - p.row_begin / kTileRows + 1);
+	const size_t smem = sizeof(AceShared);
+	if (fast) {
+		auto kern = ace_scores_kernel<true, true>;
+		PFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		kern<<<grid, kAceBlock, smem, st>>>(in, samples_xy, cs, scores, minmax);
+	} else {
+		auto kern = ace_scores_kernel<false, true>;
+		PFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		kern<<<grid, kAceBlock, smem, st>>>(in, samples_xy, cs, scores, minmax);
+	}
+	PFB_CUDA(cudaGetLastError());
+	return PF_B200_OK;
+}
+
+int launch_ace_scale(const double *scores, const double *minmax, int w,
+		int rows, uint32_t *out, cudaStream_t st)
+{
+	const size_t npix = (size_t)w * rows;
+	const int blocks = (int)((npix + 255) / 256 < (size_t)sm_count() * 16
+			? (npix + 255) / 256 : (size_t)sm_count() * 16);
+	ace_scale_kernel<<<blocks, 256, 0, st>>>(scores, minmax, npix, out);
+	PFB_CUDA(cudaGetLastError());
+	return PF_B200_OK;
+}
+
+double measure_fp64_peak_tflops()
+{
+	double *sink = nullptr;
+	if (cudaMalloc(&sink, 64) != cudaSuccess)
+		return -(double)fail(PF_B200_ECUDA, "fp64 probe: cudaMalloc failed");
+	const int blocks = sm_count() * 8, threads = 256, iters = 1 << 15;
+	cudaEvent_t e0, e1;
+	cudaEventCreate(&e0);
+	cudaEventCreate(&e1);
+	fp64_peak_kernel<<<blocks, threads>>>(sink, 1024, 1.0000001, 1e-9);   // warm-up
+	double best_ms = 1e30;
+	for (int rep = 0; rep < 5; rep++) {
+		cudaEventRecord(e0);
+		fp64_peak_kernel<<<blocks, threads>>>(sink, iters, 1.0000001, 1e-9);
+		cudaEventRecord(e1);
+		cudaEventSynchronize(e1);
+		float ms = 0.f;
+		cudaEventElapsedTime(&ms, e0, e1);
+		if (ms < best_ms)
+			best_ms = ms;
+	}
+	cudaEventDestroy(e0);
+	cudaEventDestroy(e1);
+	const cudaError_t err = cudaGetLastError();
+	cudaFree(sink);
+	if (err != cudaSuccess)
+		return -(double)fail(PF_B200_ECUDA, "fp64 probe: %s", cudaGetErrorString(err));
+	const double flops = 2.0 * 8.0 * (double)iters * blocks * threads;
+	return flops / (best_ms * 1e-3) / 1e12;
+}
+
+}  // namespace pfb

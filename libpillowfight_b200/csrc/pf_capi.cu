@@ -1,0 +1,623 @@
+// C-ABI of libpillowfight_b200.so (see include/pillowfight_b200.h).
+//
+// Host-pointer entry points (pf_apply_*) keep one context per host thread: a
+// stream, grow-only device buffers and a pinned staging buffer.  A call is
+//   host bitmap -> (staging) -> HBM -> kernels -> HBM -> (staging) -> host bitmap
+// and returns after the result is in the caller's memory.  There is no CPU
+// implementation behind any of them: without a CUDA device they fail.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "pf_common.cuh"
+
+namespace pfb {
+
+// ---------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------
+
+static thread_local int t_err = PF_B200_OK;
+static thread_local char t_msg[512] = "";
+
+int fail(int code, const char *fmt, ...)
+{
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(t_msg, sizeof(t_msg), fmt, ap);
+	va_end(ap);
+	t_err = code;
+	return code;
+}
+
+static void clear_error()
+{
+	t_err = PF_B200_OK;
+	t_msg[0] = '\0';
+}
+
+int sm_count()
+{
+	static thread_local int cached_dev = -1, cached = 148;
+	int dev = 0;
+	if (cudaGetDevice(&dev) != cudaSuccess)
+		return cached;
+	if (dev != cached_dev) {
+		int n = 0;
+		if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
+			cached = n;
+		cached_dev = dev;
+	}
+	return cached;
+}
+
+// ---------------------------------------------------------------------------
+// per-thread context for the host-pointer entry points
+// ---------------------------------------------------------------------------
+
+struct Buffer {
+	void *p = nullptr;
+	size_t cap = 0;
+};
+
+struct Context {
+	int dev = -1;
+	cudaStream_t st = nullptr;
+	Buffer d_in, d_out, d_scratch, d_scores, d_small;
+	Buffer h_stage;   // pinned
+
+	~Context()
+	{
+		// Thread exit: release what this thread holds.  Errors are ignored
+		// (the CUDA runtime may already be shutting down).
+		if (dev < 0)
+			return;
+		cudaSetDevice(dev);
+		Buffer *bufs[] = { &d_in, &d_out, &d_scratch, &d_scores, &d_small };
+		for (Buffer *b : bufs)
+			if (b->p)
+				cudaFree(b->p);
+		if (h_stage.p)
+			cudaFreeHost(h_stage.p);
+		if (st)
+			cudaStreamDestroy(st);
+	}
+};
+
+static thread_local Context t_ctx;
+
+static int ctx_init(Context &c)
+{
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0)
+		return fail(PF_B200_ENODEV, "no CUDA device is usable (%s); this build has no CPU path",
+				cudaGetErrorString(cudaGetLastError()));
+	int dev = 0;
+	PFB_CUDA(cudaGetDevice(&dev));
+	if (c.dev == dev && c.st)
+		return PF_B200_OK;
+	if (c.dev >= 0 && c.dev != dev)
+		return fail(PF_B200_EINVAL, "thread first used device %d, now on %d: "
+				"one device per host thread", c.dev, dev);
+	c.dev = dev;
+	PFB_CUDA(cudaStreamCreateWithFlags(&c.st, cudaStreamNonBlocking));
+	return PF_B200_OK;
+}
+
+static int grow(Buffer &b, size_t bytes, bool pinned)
+{
+	if (b.cap >= bytes)
+		return PF_B200_OK;
+	if (b.p) {
+		if (pinned)
+			cudaFreeHost(b.p);
+		else
+			cudaFree(b.p);
+		b.p = nullptr;
+		b.cap = 0;
+	}
+	if (pinned)
+		PFB_CUDA(cudaMallocHost(&b.p, bytes));
+	else
+		PFB_CUDA(cudaMalloc(&b.p, bytes));
+	b.cap = bytes;
+	return PF_B200_OK;
+}
+
+static bool is_pinned(const void *p)
+{
+	cudaPointerAttributes a;
+	if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+		cudaGetLastError();
+		return false;
+	}
+	return a.type == cudaMemoryTypeHost;
+}
+
+// host -> device.  Pinned caller memory goes by DMA directly; pageable memory
+// is copied through the pinned staging buffer in chunks so that the memcpy of
+// chunk i+1 overlaps the DMA of chunk i.
+static int upload(Context &c, void *dst, const void *src, size_t bytes)
+{
+	if (is_pinned(src)) {
+		PFB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c.st));
+		return PF_B200_OK;
+	}
+	const size_t chunk = 4u << 20;
+	int rc = grow(c.h_stage, 2 * chunk, true);
+	if (rc)
+		return rc;
+	cudaEvent_t ev[2];
+	PFB_CUDA(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming));
+	PFB_CUDA(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
+	int slot = 0;
+	bool used[2] = { false, false };
+	for (size_t off = 0; off < bytes; off += chunk, slot ^= 1) {
+		const size_t n = bytes - off < chunk ? bytes - off : chunk;
+		char *stage = static_cast<char *>(c.h_stage.p) + slot * chunk;
+		if (used[slot])
+			cudaEventSynchronize(ev[slot]);
+		memcpy(stage, static_cast<const char *>(src) + off, n);
+		cudaMemcpyAsync(static_cast<char *>(dst) + off, stage, n,
+				cudaMemcpyHostToDevice, c.st);
+		cudaEventRecord(ev[slot], c.st);
+		used[slot] = true;
+	}
+	cudaStreamSynchronize(c.st);
+	cudaEventDestroy(ev[0]);
+	cudaEventDestroy(ev[1]);
+	PFB_CUDA(cudaGetLastError());
+	return PF_B200_OK;
+}
+
+// device -> host, then wait: the result is in the caller's memory on return.
+static int download(Context &c, void *dst, const void *src, size_t bytes)
+{
+	if (is_pinned(dst)) {
+		PFB_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c.st));
+		PFB_CUDA(cudaStreamSynchronize(c.st));
+		return PF_B200_OK;
+	}
+	const size_t chunk = 4u << 20;
+	int rc = grow(c.h_stage, 2 * chunk, true);
+	if (rc)
+		return rc;
+	cudaEvent_t ev[2];
+	PFB_CUDA(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming));
+	PFB_CUDA(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
+	// DMA of chunk i+1 runs while chunk i is copied out of the staging buffer
+	size_t issued = 0, done = 0;
+	int slot = 0;
+	size_t len[2] = { 0, 0 }, at[2] = { 0, 0 };
+	while (done < bytes) {
+		while (issued < bytes && issued - done < 2 * chunk) {
+			const size_t n = bytes - issued < chunk ? bytes - issued : chunk;
+			const int s = (int)((issued / chunk) & 1);
+			cudaMemcpyAsync(static_cast<char *>(c.h_stage.p) + s * chunk,
+					static_cast<const char *>(src) + issued, n,
+					cudaMemcpyDeviceToHost, c.st);
+			cudaEventRecord(ev[s], c.st);
+			len[s] = n;
+			at[s] = issued;
+			issued += n;
+		}
+		cudaEventSynchronize(ev[slot]);
+		memcpy(static_cast<char *>(dst) + at[slot],
+				static_cast<char *>(c.h_stage.p) + slot * chunk, len[slot]);
+		done += len[slot];
+		slot ^= 1;
+	}
+	cudaEventDestroy(ev[0]);
+	cudaEventDestroy(ev[1]);
+	PFB_CUDA(cudaGetLastError());
+	return PF_B200_OK;
+}
+
+static int check_bitmaps(const struct pf_bitmap *in, const struct pf_bitmap *out)
+{
+	if (!in || !out || !in->pixels || !out->pixels)
+		return fail(PF_B200_EINVAL, "NULL bitmap or pixel buffer");
+	if (in->size.x <= 0 || in->size.y <= 0)
+		return fail(PF_B200_EINVAL, "bitmap size %d x %d", in->size.x, in->size.y);
+	if (out->size.x != in->size.x || out->size.y != in->size.y)
+		return fail(PF_B200_EINVAL, "output bitmap is %d x %d, input %d x %d",
+				out->size.x, out->size.y, in->size.x, in->size.y);
+	return PF_B200_OK;
+}
+
+// upstream _gaussian.c: generate_gaussian_1d_kernel -- the taps are made on
+// the host with glibc's exp/sqrt, in the reference's operation order, so the
+// device only ever multiplies and adds.
+static int make_taps(double sigma, int nb_stddev, Taps &t)
+{
+	if (nb_stddev < 1 || nb_stddev > kMaxTaps)
+		return fail(PF_B200_EINVAL, "gaussian: nb_stddev %d outside 1..%d", nb_stddev, kMaxTaps);
+	if (sigma == 0.0)
+		sigma = 0.3 * (((double)(nb_stddev - 1)) * 0.5 - 1.0) + 0.8;
+	t.n = nb_stddev;
+	double sum = 0.0;     // host code is built with -ffp-contract=off
+	for (int i = 0; i < nb_stddev; i++) {
+		const double d = (double)(i - nb_stddev / 2);
+		t.t[i] = exp(-(d * d) / (2.0 * sigma * sigma))
+			/ sqrt(2.0 * M_PI * sigma * sigma);
+		sum += t.t[i];
+	}
+	for (int i = 0; i < nb_stddev; i++)
+		t.t[i] = t.t[i] / sum;
+	return PF_B200_OK;
+}
+
+// upstream _canny.c thresholds, turned into exact integer tests on
+// g_x^2 + g_y^2 (hypot of two integers is compared against the double).
+static int threshold_to_sq(double thr)
+{
+	long m = (long)floor(thr * thr);
+	if (m < 0)
+		m = 0;
+	while (m > 0 && sqrt((double)(m - 1)) > thr)
+		m--;
+	while (!(sqrt((double)m) > thr))
+		m++;
+	return (int)m;
+}
+
+static CannyThresholds canny_thresholds()
+{
+	CannyThresholds t;
+	t.weak_min = threshold_to_sq(0.686 * 255.0);
+	t.strong_min = threshold_to_sq(1.372 * 255.0);
+	return t;
+}
+
+enum Op { OP_GAUSSIAN, OP_SOBEL, OP_CANNY };
+
+static int run_stencil(Op op, const struct pf_bitmap *in, struct pf_bitmap *out,
+		double sigma, int nb_stddev)
+{
+	clear_error();
+	int rc = check_bitmaps(in, out);
+	if (rc)
+		return rc;
+	Taps taps;
+	if (op == OP_GAUSSIAN && (rc = make_taps(sigma, nb_stddev, taps)))
+		return rc;
+	Context &c = t_ctx;
+	if ((rc = ctx_init(c)))
+		return rc;
+	const int w = in->size.x, h = in->size.y;
+	const size_t bytes = (size_t)w * h * sizeof(uint32_t);
+	if ((rc = grow(c.d_in, bytes, false)) || (rc = grow(c.d_out, bytes, false)))
+		return rc;
+	if ((rc = upload(c, c.d_in.p, in->pixels, bytes)))
+		return rc;
+	const uint32_t *din = static_cast<const uint32_t *>(c.d_in.p);
+	uint32_t *dout = static_cast<uint32_t *>(c.d_out.p);
+	switch (op) {
+	case OP_GAUSSIAN:
+		rc = launch_gaussian(din, dout, w, h, 1, taps, c.st);
+		break;
+	case OP_SOBEL:
+		rc = launch_sobel(din, dout, w, h, 1, c.st);
+		break;
+	case OP_CANNY: {
+		const size_t sb = canny_scratch_bytes(w, h);
+		if ((rc = grow(c.d_scratch, sb, false)))
+			return rc;
+		rc = launch_canny(din, dout, w, h, 1, canny_thresholds(),
+				c.d_scratch.p, c.d_scratch.cap, c.st);
+		break;
+	}
+	}
+	if (rc)
+		return rc;
+	return download(c, out->pixels, dout, bytes);
+}
+
+static int run_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
+		int nb_samples, const int *sample_xy, double slope, double limit)
+{
+	clear_error();
+	int rc = check_bitmaps(in, out);
+	if (rc)
+		return rc;
+	if (nb_samples < 1 || !sample_xy)
+		return fail(PF_B200_EINVAL, "ace: nb_samples %d", nb_samples);
+	const int w = in->size.x, h = in->size.y;
+	for (int i = 0; i < nb_samples; i++)
+		if (sample_xy[2 * i] < 0 || sample_xy[2 * i] >= w
+				|| sample_xy[2 * i + 1] < 0 || sample_xy[2 * i + 1] >= h)
+			return fail(PF_B200_EINVAL, "ace: sample %d (%d, %d) outside the page",
+					i, sample_xy[2 * i], sample_xy[2 * i + 1]);
+	Context &c = t_ctx;
+	if ((rc = ctx_init(c)))
+		return rc;
+	const size_t npix = (size_t)w * h;
+	const size_t bytes = npix * sizeof(uint32_t);
+	const size_t small = 64 + sizeof(int) * 2 * (size_t)nb_samples;
+	if ((rc = grow(c.d_in, bytes, false)) || (rc = grow(c.d_out, bytes, false))
+			|| (rc = grow(c.d_scores, 3 * npix * sizeof(double), false))
+			|| (rc = grow(c.d_small, small, false)))
+		return rc;
+	double *minmax = static_cast<double *>(c.d_small.p);
+	int *d_xy = reinterpret_cast<int *>(static_cast<char *>(c.d_small.p) + 64);
+	// the table is tiny; a synchronous copy keeps the caller's array free to reuse
+	PFB_CUDA(cudaMemcpyAsync(d_xy, sample_xy, sizeof(int) * 2 * (size_t)nb_samples,
+			cudaMemcpyHostToDevice, c.st));
+	if ((rc = upload(c, c.d_in.p, in->pixels, bytes)))
+		return rc;
+	AceParams p = { w, h, 0, h, nb_samples, slope, limit };
+	if ((rc = launch_ace_minmax_init(minmax, c.st)))
+		return rc;
+	if ((rc = launch_ace_scores(static_cast<const uint32_t *>(c.d_in.p), d_xy, p,
+			static_cast<double *>(c.d_scores.p), minmax, c.st)))
+		return rc;
+	if ((rc = launch_ace_scale(static_cast<const double *>(c.d_scores.p), minmax, w, h,
+			static_cast<uint32_t *>(c.d_out.p), c.st)))
+		return rc;
+	return download(c, out->pixels, c.d_out.p, bytes);
+}
+
+static void report(const char *who, int rc)
+{
+	if (rc == PF_B200_OK)
+		return;
+	fprintf(stderr, "libpillowfight_b200: %s failed (%d): %s\n", who, rc, t_msg);
+	const char *e = getenv("PF_B200_ABORT_ON_ERROR");
+	if (e && e[0] == '1')
+		abort();
+}
+
+}  // namespace pfb
+
+// ---------------------------------------------------------------------------
+// extern "C"
+// ---------------------------------------------------------------------------
+
+using namespace pfb;
+
+extern "C" {
+
+int pf_b200_last_error(void) { return t_err; }
+const char *pf_b200_last_error_string(void) { return t_msg; }
+
+int pf_b200_device_count(void)
+{
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess) {
+		cudaGetLastError();
+		return 0;
+	}
+	return n;
+}
+
+void pf_b200_ace_draw_samples(int nb_samples, int width, int height, int *sample_xy)
+{
+	for (int i = 0; i < nb_samples; i++) {
+		sample_xy[2 * i] = rand() % width;
+		sample_xy[2 * i + 1] = rand() % height;
+	}
+}
+
+int pf_b200_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
+		int nb_samples, const int *sample_xy, double slope, double limit)
+{
+	return run_ace(in, out, nb_samples, sample_xy, slope, limit);
+}
+
+int pf_b200_gaussian(const struct pf_bitmap *in, struct pf_bitmap *out,
+		double sigma, int nb_stddev)
+{
+	return run_stencil(OP_GAUSSIAN, in, out, sigma, nb_stddev);
+}
+
+int pf_b200_sobel(const struct pf_bitmap *in, struct pf_bitmap *out)
+{
+	return run_stencil(OP_SOBEL, in, out, 0.0, 0);
+}
+
+int pf_b200_canny(const struct pf_bitmap *in, struct pf_bitmap *out)
+{
+	return run_stencil(OP_CANNY, in, out, 0.0, 0);
+}
+
+void pf_apply_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
+		int nb_samples, double slope, double limit, int nb_threads)
+{
+	(void)nb_threads;
+	clear_error();
+	if (nb_samples < 1 || !in || in->size.x <= 0 || in->size.y <= 0) {
+		report("pf_apply_ace", fail(PF_B200_EINVAL, "ace: bad arguments"));
+		return;
+	}
+	int *xy = static_cast<int *>(malloc(sizeof(int) * 2 * (size_t)nb_samples));
+	if (!xy) {
+		report("pf_apply_ace", fail(PF_B200_EINVAL, "ace: out of host memory"));
+		return;
+	}
+	pf_b200_ace_draw_samples(nb_samples, in->size.x, in->size.y, xy);
+	report("pf_apply_ace", run_ace(in, out, nb_samples, xy, slope, limit));
+	free(xy);
+}
+
+void pf_apply_gaussian(const struct pf_bitmap *in, struct pf_bitmap *out,
+		double sigma, int nb_stddev)
+{
+	report("pf_apply_gaussian", run_stencil(OP_GAUSSIAN, in, out, sigma, nb_stddev));
+}
+
+void pf_apply_sobel(const struct pf_bitmap *in, struct pf_bitmap *out)
+{
+	report("pf_apply_sobel", run_stencil(OP_SOBEL, in, out, 0.0, 0));
+}
+
+void pf_apply_canny(const struct pf_bitmap *in, struct pf_bitmap *out)
+{
+	report("pf_apply_canny", run_stencil(OP_CANNY, in, out, 0.0, 0));
+}
+
+void pf_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
+		int nb_samples, double slope, double limit, int nb_threads)
+{
+	pf_apply_ace(in, out, nb_samples, slope, limit, nb_threads);
+}
+
+void pf_gaussian(const struct pf_bitmap *in, struct pf_bitmap *out,
+		double sigma, int nb_stddev)
+{
+	pf_apply_gaussian(in, out, sigma, nb_stddev);
+}
+
+void pf_sobel(const struct pf_bitmap *in, struct pf_bitmap *out)
+{
+	pf_apply_sobel(in, out);
+}
+
+void pf_canny(const struct pf_bitmap *in, struct pf_bitmap *out)
+{
+	pf_apply_canny(in, out);
+}
+
+void *pf_b200_host_alloc(size_t bytes)
+{
+	void *p = nullptr;
+	if (cudaMallocHost(&p, bytes) != cudaSuccess) {
+		fail(PF_B200_ECUDA, "cudaMallocHost(%zu): %s", bytes,
+				cudaGetErrorString(cudaGetLastError()));
+		return nullptr;
+	}
+	return p;
+}
+
+void pf_b200_host_free(void *ptr)
+{
+	if (ptr)
+		cudaFreeHost(ptr);
+}
+
+// ---- device-resident entry points ----------------------------------------
+
+static int check_dev(const void *a, const void *b, int w, int h, int pages)
+{
+	if (!a || !b)
+		return fail(PF_B200_EINVAL, "NULL device pointer");
+	if (w <= 0 || h <= 0 || pages <= 0)
+		return fail(PF_B200_EINVAL, "size %d x %d x %d pages", w, h, pages);
+	if (a == b)
+		return fail(PF_B200_EINVAL, "device entry points do not run in place");
+	return PF_B200_OK;
+}
+
+int pf_b200_dev_gaussian_batch(const uint32_t *d_in, uint32_t *d_out,
+		int width, int height, int nb_pages, double sigma, int nb_stddev, void *stream)
+{
+	clear_error();
+	int rc = check_dev(d_in, d_out, width, height, nb_pages);
+	if (rc)
+		return rc;
+	Taps taps;
+	if ((rc = make_taps(sigma, nb_stddev, taps)))
+		return rc;
+	for (int p0 = 0; p0 < nb_pages; p0 += 65535) {
+		const int np = nb_pages - p0 < 65535 ? nb_pages - p0 : 65535;
+		const size_t off = (size_t)p0 * width * height;
+		if ((rc = launch_gaussian(d_in + off, d_out + off, width, height, np, taps,
+				static_cast<cudaStream_t>(stream))))
+			return rc;
+	}
+	return PF_B200_OK;
+}
+
+int pf_b200_dev_gaussian(const uint32_t *d_in, uint32_t *d_out,
+		int width, int height, double sigma, int nb_stddev, void *stream)
+{
+	return pf_b200_dev_gaussian_batch(d_in, d_out, width, height, 1, sigma, nb_stddev, stream);
+}
+
+int pf_b200_dev_sobel_batch(const uint32_t *d_in, uint32_t *d_out,
+		int width, int height, int nb_pages, void *stream)
+{
+	clear_error();
+	int rc = check_dev(d_in, d_out, width, height, nb_pages);
+	if (rc)
+		return rc;
+	for (int p0 = 0; p0 < nb_pages; p0 += 65535) {
+		const int np = nb_pages - p0 < 65535 ? nb_pages - p0 : 65535;
+		const size_t off = (size_t)p0 * width * height;
+		if ((rc = launch_sobel(d_in + off, d_out + off, width, height, np,
+				static_cast<cudaStream_t>(stream))))
+			return rc;
+	}
+	return PF_B200_OK;
+}
+
+int pf_b200_dev_sobel(const uint32_t *d_in, uint32_t *d_out,
+		int width, int height, void *stream)
+{
+	return pf_b200_dev_sobel_batch(d_in, d_out, width, height, 1, stream);
+}
+
+size_t pf_b200_canny_scratch_bytes(int width, int height)
+{
+	if (width <= 0 || height <= 0)
+		return 0;
+	return canny_scratch_bytes(width, height);
+}
+
+int pf_b200_dev_canny(const uint32_t *d_in, uint32_t *d_out,
+		int width, int height, int nb_pages,
+		void *d_scratch, size_t scratch_bytes, void *stream)
+{
+	clear_error();
+	int rc = check_dev(d_in, d_out, width, height, nb_pages);
+	if (rc)
+		return rc;
+	return launch_canny(d_in, d_out, width, height, nb_pages, canny_thresholds(),
+			d_scratch, scratch_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int pf_b200_dev_ace_minmax_init(double *d_minmax, void *stream)
+{
+	clear_error();
+	if (!d_minmax)
+		return fail(PF_B200_EINVAL, "NULL device pointer");
+	return launch_ace_minmax_init(d_minmax, static_cast<cudaStream_t>(stream));
+}
+
+int pf_b200_dev_ace_scores(const uint32_t *d_in, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, int nb_samples, double slope, double limit,
+		double *d_scores, double *d_minmax, void *stream)
+{
+	clear_error();
+	if (!d_in || !d_samples || !d_scores || !d_minmax)
+		return fail(PF_B200_EINVAL, "NULL device pointer");
+	if (width <= 0 || height <= 0)
+		return fail(PF_B200_EINVAL, "size %d x %d", width, height);
+	AceParams p = { width, height, row_begin, row_end, nb_samples, slope, limit };
+	return launch_ace_scores(d_in, d_samples, p, d_scores, d_minmax,
+			static_cast<cudaStream_t>(stream));
+}
+
+int pf_b200_dev_ace_scale(const double *d_scores, const double *d_minmax,
+		int width, int nb_rows, uint32_t *d_out_band, void *stream)
+{
+	clear_error();
+	if (!d_scores || !d_minmax || !d_out_band)
+		return fail(PF_B200_EINVAL, "NULL device pointer");
+	if (width <= 0 || nb_rows <= 0)
+		return fail(PF_B200_EINVAL, "size %d x %d", width, nb_rows);
+	return launch_ace_scale(d_scores, d_minmax, width, nb_rows, d_out_band,
+			static_cast<cudaStream_t>(stream));
+}
+
+double pf_b200_fp64_peak_tflops(void)
+{
+	clear_error();
+	if (pf_b200_device_count() <= 0)
+		return -(double)fail(PF_B200_ENODEV, "no CUDA device");
+	return measure_fp64_peak_tflops();
+}
+
+}  // extern "C"

@@ -1,0 +1,140 @@
+"""Multi-GPU sharding of the hot path: one process per GPU, torch.distributed
+for the plumbing (NCCL on GPUs, gloo in the CPU tests).
+
+Only the two splits BASELINE.json names:
+  * ACE: the page is broadcast, each rank accumulates the scores of one band
+    of rows, the per-channel min/max are all-reduced (6 doubles -- the one
+    real exchange the algorithm has), each rank rescales its band, and the
+    bands are all-gathered.
+  * Gaussian/Sobel/Canny: pages are independent; page i goes to rank
+    i mod world and nothing is exchanged.
+
+The arithmetic is behind a small `compute` object so that the same sharding
+code runs in the CPU gloo tests (tests/ plug the oracle in there); the product
+object, CudaAceCompute, calls the C-ABI device entry points on torch CUDA
+tensors' data pointers.
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def row_bands(height, world):
+    """[begin, end) rows of each rank; sizes differ by at most one row."""
+    return [(height * r // world, height * (r + 1) // world) for r in range(world)]
+
+
+def page_shard(n_pages, world, rank):
+    """Indices of the pages rank `rank` processes (round robin)."""
+    return list(range(rank, n_pages, world))
+
+
+class CudaAceCompute:
+    """ACE band arithmetic on the current CUDA device through the C-ABI."""
+
+    def __init__(self):
+        from . import _capi
+        self._capi = _capi
+        self._lib = _capi.lib
+
+    def new_minmax(self, device):
+        mm = torch.empty(6, dtype=torch.float64, device=device)
+        st = torch.cuda.current_stream().cuda_stream
+        self._capi.check(self._lib.pf_b200_dev_ace_minmax_init(mm.data_ptr(), st))
+        return mm
+
+    def scores(self, page, xy, slope, limit, band, minmax):
+        """page: (H, W, 4) uint8 CUDA tensor; xy: int32 CUDA tensor (2N);
+        returns (3, rows, W) float64 scores, folds min/max into `minmax`."""
+        h, w = page.shape[0], page.shape[1]
+        b0, b1 = band
+        out = torch.empty((3, b1 - b0, w), dtype=torch.float64, device=page.device)
+        st = torch.cuda.current_stream().cuda_stream
+        self._capi.check(self._lib.pf_b200_dev_ace_scores(
+            page.data_ptr(), w, h, b0, b1, xy.data_ptr(), xy.numel() // 2,
+            float(slope), float(limit), out.data_ptr(), minmax.data_ptr(), st))
+        return out
+
+    def scale(self, scores, minmax):
+        rows, w = scores.shape[1], scores.shape[2]
+        out = torch.empty((rows, w, 4), dtype=torch.uint8, device=scores.device)
+        st = torch.cuda.current_stream().cuda_stream
+        self._capi.check(self._lib.pf_b200_dev_ace_scale(
+            scores.data_ptr(), minmax.data_ptr(), w, rows, out.data_ptr(), st))
+        return out
+
+
+def ace_sharded(page, xy, slope, limit, compute, group=None, src=0):
+    """Row-band sharded ACE.  `page` must hold the input on rank `src` and be
+    an equally shaped buffer elsewhere; every rank returns the whole result."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    h, w = page.shape[0], page.shape[1]
+    if world > 1:
+        dist.broadcast(page, src=src, group=group)
+        dist.broadcast(xy, src=src, group=group)
+    bands = row_bands(h, world)
+    minmax = compute.new_minmax(page.device)
+    scores = compute.scores(page, xy, slope, limit, bands[rank], minmax)
+    if world > 1:
+        dist.all_reduce(minmax[:3], op=dist.ReduceOp.MIN, group=group)
+        dist.all_reduce(minmax[3:], op=dist.ReduceOp.MAX, group=group)
+    band = compute.scale(scores, minmax)
+    if world == 1:
+        return band
+    # all-gather needs equal shapes: pad every band to the tallest
+    max_rows = max(b1 - b0 for b0, b1 in bands)
+    padded = torch.zeros((max_rows, w, 4), dtype=torch.uint8, device=page.device)
+    padded[: band.shape[0]] = band
+    gathered = torch.empty((world, max_rows, w, 4), dtype=torch.uint8, device=page.device)
+    dist.all_gather_into_tensor(gathered.view(-1), padded.view(-1), group=group)
+    out = torch.empty((h, w, 4), dtype=torch.uint8, device=page.device)
+    for r, (b0, b1) in enumerate(bands):
+        out[b0:b1] = gathered[r, : b1 - b0]
+    return out
+
+
+class CudaChain:
+    """Gaussian -> Sobel -> Canny on batches of same-size pages resident in
+    HBM, through the C-ABI device entry points."""
+
+    def __init__(self):
+        from . import _capi
+        self._capi = _capi
+        self._lib = _capi.lib
+        self._scratch = None
+
+    def _stream(self):
+        return torch.cuda.current_stream().cuda_stream
+
+    def gaussian(self, pages, out, sigma=2.0, nb_stddev=5):
+        n, h, w = pages.shape[0], pages.shape[1], pages.shape[2]
+        self._capi.check(self._lib.pf_b200_dev_gaussian_batch(
+            pages.data_ptr(), out.data_ptr(), w, h, n, float(sigma), int(nb_stddev),
+            self._stream()))
+        return out
+
+    def sobel(self, pages, out):
+        n, h, w = pages.shape[0], pages.shape[1], pages.shape[2]
+        self._capi.check(self._lib.pf_b200_dev_sobel_batch(
+            pages.data_ptr(), out.data_ptr(), w, h, n, self._stream()))
+        return out
+
+    def canny(self, pages, out, pages_per_launch=1):
+        n, h, w = pages.shape[0], pages.shape[1], pages.shape[2]
+        need = 256 + 4 * w * h * max(1, min(n, pages_per_launch))
+        if self._scratch is None or self._scratch.numel() < need \
+                or self._scratch.device != pages.device:
+            self._scratch = torch.empty(need, dtype=torch.uint8, device=pages.device)
+        self._capi.check(self._lib.pf_b200_dev_canny(
+            pages.data_ptr(), out.data_ptr(), w, h, n,
+            self._scratch.data_ptr(), self._scratch.numel(), self._stream()))
+        return out
+
+
+def to_numpy_u8(t):
+    return t.detach().cpu().numpy().astype(np.uint8, copy=False)
+
+
+def xy_tensor(xy, device):
+    return torch.from_numpy(np.ascontiguousarray(xy, dtype=np.int32)).to(device)

@@ -1,0 +1,320 @@
+"""Parity of the CUDA path with the CPU oracle, through the C-ABI.
+
+Bar (BASELINE.json north_star): bit-exact for the integer stages (Sobel
+intensity, Canny edge maps); for the floating-point stages at most 0.1 % of
+channel values may differ, and then by no more than 1 LSB.  Gaussian follows
+the reference's operation order in FP64 and is held to bit-exactness too.
+"""
+import ctypes
+
+import numpy as np
+import pytest
+
+from libpillowfight_b200.pages import A4_300DPI, synthetic_page, uniform_random_page
+
+pytestmark = pytest.mark.gpu
+
+FP_MAX_FRACTION = 1e-3     # <= 0.1 % of channel values ...
+FP_MAX_LSB = 1             # ... off by at most 1
+
+
+def assert_fp_parity(got, ref, what):
+    assert got.shape == ref.shape
+    d = np.abs(got.astype(np.int16) - ref.astype(np.int16))
+    assert d.max() <= FP_MAX_LSB, "%s: max diff %d" % (what, d.max())
+    frac = (d[..., :3] != 0).mean()
+    assert frac <= FP_MAX_FRACTION, "%s: %.5f %% of values differ" % (what, 100 * frac)
+    return frac
+
+
+SIZES = [(1, 1), (2, 3), (5, 4), (7, 9), (33, 17), (64, 48), (130, 67), (257, 129),
+         (256, 200), (620, 877)]
+
+
+@pytest.fixture(scope="module")
+def gpu(pf):
+    if pf.device_count() <= 0:
+        pytest.fail("no CUDA device: the gpu-marked tests must run on the B200 box")
+    return pf
+
+
+@pytest.mark.parametrize("w,h", SIZES)
+def test_gaussian_bit_exact(gpu, oracle, w, h):
+    page = uniform_random_page(w, h, seed=w * 1000 + h)
+    assert np.array_equal(gpu.gaussian(page, 2.0, 5), oracle.gaussian(page, 2.0, 5))
+
+
+@pytest.mark.parametrize("sigma,n", [(2.0, 5), (0.0, 5), (1.0, 3), (3.0, 7), (2.5, 9),
+                                     (2.0, 4), (1.0, 1), (4.0, 11), (2.0, 6)])
+def test_gaussian_tap_counts(gpu, oracle, sigma, n):
+    page = synthetic_page(150, 90, 2)
+    assert np.array_equal(gpu.gaussian(page, sigma, n), oracle.gaussian(page, sigma, n))
+
+
+def test_gaussian_flat_regions(gpu, oracle):
+    # saturated / flat areas are where a different rounding order would show
+    # up as whole regions off by one
+    for v in (255, 235, 200, 1, 0):
+        page = np.full((40, 52, 4), v, dtype=np.uint8)
+        page[..., 3] = 255
+        assert np.array_equal(gpu.gaussian(page, 2.0, 5), oracle.gaussian(page, 2.0, 5))
+
+
+@pytest.mark.parametrize("w,h", SIZES)
+def test_sobel_bit_exact(gpu, oracle, w, h):
+    page = uniform_random_page(w, h, seed=7 + w * 1000 + h)
+    assert np.array_equal(gpu.sobel(page), oracle.sobel(page))
+
+
+@pytest.mark.parametrize("w,h", SIZES)
+def test_canny_bit_exact_random(gpu, oracle, w, h):
+    page = uniform_random_page(w, h, seed=11 + w * 1000 + h)
+    assert np.array_equal(gpu.canny(page), oracle.canny(page))
+
+
+@pytest.mark.parametrize("idx", [0, 1, 2])
+def test_canny_bit_exact_document(gpu, oracle, idx):
+    page = synthetic_page(620, 877, idx)
+    got, ref = gpu.canny(page), oracle.canny(page)
+    assert np.array_equal(got, ref)
+    assert (ref[..., 0] == 255).any()
+
+
+def test_canny_adversarial_pages(gpu, oracle):
+    flat = np.full((100, 120, 4), 128, dtype=np.uint8)
+    flat[..., 3] = 255
+    assert np.array_equal(gpu.canny(flat), oracle.canny(flat))
+    yy, xx = np.mgrid[0:100, 0:120]
+    cb = np.where((xx + yy) % 2 == 0, 255, 0).astype(np.uint8)
+    page = np.stack([cb, cb, cb, np.full_like(cb, 255)], axis=-1)
+    assert np.array_equal(gpu.canny(page), oracle.canny(page))
+
+
+def test_canny_long_weak_chains(gpu, oracle):
+    # A weak edge hundreds of pixels long, kept only because one end touches a
+    # strong segment: the hysteresis has to follow the whole chain, across
+    # thread, warp and strip boundaries.  A second, unconnected weak edge of
+    # the same contrast must vanish.
+    h, w = 700, 300
+    g = np.zeros((h, w), dtype=np.uint8)
+    g[:, 100:] = 50            # |g_x| = 200: weak (174.9 < 200 <= 349.9)
+    g[:30, 100:] = 120         # |g_x| = 480: strong near the top
+    g[60:, 200:] = np.minimum(g[60:, 200:] + 50, 255)   # second weak edge, isolated
+    page = np.stack([g, g, g, np.full_like(g, 255)], axis=-1)
+    got, ref = gpu.canny(page), oracle.canny(page)
+    assert np.array_equal(got, ref)
+    assert ref[600, 99:101, 0].any()        # the chain reached the bottom
+    assert not ref[100:600, 198:202, 0].any()
+
+
+def test_canny_snake_fills_queues(gpu, oracle):
+    # dense weak texture seeded by a few strong pixels: stresses the per-warp
+    # queues (overflow -> repeat sweep path)
+    rng = np.random.default_rng(5)
+    h, w = 256, 256
+    g = (rng.integers(0, 2, size=(h, w)) * 45).astype(np.uint8)
+    g[::64, ::64] = 255
+    page = np.stack([g, g, g, np.full_like(g, 255)], axis=-1)
+    assert np.array_equal(gpu.canny(page), oracle.canny(page))
+
+
+@pytest.mark.parametrize("w,h,n", [(64, 48, 8), (200, 150, 30), (130, 257, 100), (620, 877, 100)])
+def test_ace_parity(gpu, oracle, w, h, n):
+    page = synthetic_page(w, h, 4)
+    xy = oracle.ace_draw_samples(n, w, h, 12345)
+    ref = oracle.ace_with_samples(page, xy, 10.0, 1000.0, nb_threads=8)
+    got = gpu.ace(page, 10, 1000, n, seed=12345)     # draws the same table itself
+    assert_fp_parity(got, ref, "ace %dx%d" % (w, h))
+    assert (got[..., 3] == 255).all()
+
+
+@pytest.mark.parametrize("slope,limit", [(10.0, 1000.0), (5.0, 500.0), (7.5, 1000.0),
+                                         (1.0, 300.0), (20.0, 100.0), (3.0, 1000.0)])
+def test_ace_slope_limit_variants(gpu, oracle, slope, limit):
+    # integer limit/slope <= 127 takes the integer-clamp kernel, the rest the
+    # table kernel; both must agree with the oracle
+    page = uniform_random_page(160, 120, seed=9)
+    xy = oracle.ace_draw_samples(40, 160, 120, 3)
+    ref = oracle.ace_with_samples(page, xy, slope, limit, nb_threads=4)
+    got = gpu.ace(page, slope, limit, 40, seed=3)
+    assert_fp_parity(got, ref, "ace slope=%g limit=%g" % (slope, limit))
+
+
+def test_ace_many_samples_chunked(gpu, oracle):
+    # more samples than one shared-memory chunk holds (512)
+    page = synthetic_page(96, 128, 6)
+    xy = oracle.ace_draw_samples(700, 96, 128, 21)
+    ref = oracle.ace_with_samples(page, xy, 10.0, 1000.0, nb_threads=8)
+    got = gpu.ace(page, 10, 1000, 700, seed=21)
+    assert_fp_parity(got, ref, "ace 700 samples")
+
+
+def test_ace_scores_relative_error(gpu, oracle):
+    """The score planes themselves, before quantisation: FP64 accumulation
+    with a Newton-refined rsqrt should agree to ~1e-12."""
+    import torch
+    from libpillowfight_b200.distributed import CudaAceCompute, xy_tensor
+    w, h, n = 300, 200, 64
+    page = synthetic_page(w, h, 8)
+    xy = oracle.ace_draw_samples(n, w, h, 5)
+    ref = oracle.ace_scores(page, xy, 10.0, 1000.0, nb_threads=4)
+    dev = torch.device("cuda:0")
+    comp = CudaAceCompute()
+    mm = comp.new_minmax(dev)
+    s = comp.scores(torch.from_numpy(page).to(dev), xy_tensor(xy, dev), 10.0, 1000.0, (0, h), mm)
+    torch.cuda.synchronize()
+    got = s.cpu().numpy()
+    err = np.nanmax(np.abs(got - ref))
+    assert err < 1e-11, err
+    mmh = mm.cpu().numpy()
+    assert np.allclose(mmh[:3], np.nanmin(ref, axis=(1, 2)), rtol=0, atol=1e-11)
+    assert np.allclose(mmh[3:], np.nanmax(ref, axis=(1, 2)), rtol=0, atol=1e-11)
+
+
+def test_ace_band_split_equals_whole(gpu, oracle):
+    """Row bands computed separately (the multi-GPU split) give the same page."""
+    import torch
+    from libpillowfight_b200.distributed import CudaAceCompute, row_bands, xy_tensor
+    w, h, n = 200, 151, 32
+    page = synthetic_page(w, h, 9)
+    xy = oracle.ace_draw_samples(n, w, h, 77)
+    dev = torch.device("cuda:0")
+    comp = CudaAceCompute()
+    tp, txy = torch.from_numpy(page).to(dev), xy_tensor(xy, dev)
+    mm = comp.new_minmax(dev)
+    whole = comp.scale(comp.scores(tp, txy, 10.0, 1000.0, (0, h), mm), mm)
+    mm2 = comp.new_minmax(dev)
+    parts = [comp.scores(tp, txy, 10.0, 1000.0, b, mm2) for b in row_bands(h, 3)]
+    split = torch.cat([comp.scale(p, mm2) for p in parts], dim=0)
+    torch.cuda.synchronize()
+    assert torch.equal(mm, mm2)
+    assert torch.equal(whole, split)
+
+
+def test_c_entry_points_and_aliases(gpu, oracle):
+    """pf_apply_* (void, rand()-driven ACE) and the upstream spellings."""
+    from libpillowfight_b200 import _capi
+    page = synthetic_page(128, 96, 10)
+    out = np.empty_like(page)
+    bi = _capi.PfBitmap()
+    bi.size.x, bi.size.y, bi.pixels = 128, 96, page.ctypes.data
+    bo = _capi.PfBitmap()
+    bo.size.x, bo.size.y, bo.pixels = 128, 96, out.ctypes.data
+    lib = _capi.lib
+    for name, ref in (("pf_apply_sobel", oracle.sobel(page)), ("pf_sobel", oracle.sobel(page)),
+                      ("pf_apply_canny", oracle.canny(page)), ("pf_canny", oracle.canny(page))):
+        out[:] = 0
+        getattr(lib, name)(ctypes.byref(bi), ctypes.byref(bo))
+        assert np.array_equal(out, ref), name
+    for name in ("pf_apply_gaussian", "pf_gaussian"):
+        out[:] = 0
+        getattr(lib, name)(ctypes.byref(bi), ctypes.byref(bo), 2.0, 5)
+        assert np.array_equal(out, oracle.gaussian(page, 2.0, 5)), name
+    for name in ("pf_apply_ace", "pf_ace"):
+        out[:] = 0
+        oracle.srand(4242)
+        getattr(lib, name)(ctypes.byref(bi), ctypes.byref(bo), 16, 10.0, 1000.0, 2)
+        ref = oracle.ace(page, 10.0, 1000.0, 16, seed=4242, nb_threads=2)
+        assert_fp_parity(out, ref, name)
+
+
+def test_in_place_and_pinned_buffers(gpu, oracle):
+    from libpillowfight_b200 import _capi
+    lib = _capi.lib
+    page = synthetic_page(160, 100, 11)
+    n = page.nbytes
+    # in == out is allowed at the host-pointer boundary
+    buf = page.copy()
+    b = _capi.PfBitmap()
+    b.size.x, b.size.y, b.pixels = 160, 100, buf.ctypes.data
+    _capi.check(lib.pf_b200_sobel(ctypes.byref(b), ctypes.byref(b)))
+    assert np.array_equal(buf, oracle.sobel(page))
+    # pinned memory takes the direct-DMA path
+    pin = lib.pf_b200_host_alloc(2 * n)
+    assert pin
+    try:
+        ctypes.memmove(pin, page.ctypes.data, n)
+        bi = _capi.PfBitmap()
+        bi.size.x, bi.size.y, bi.pixels = 160, 100, pin
+        bo = _capi.PfBitmap()
+        bo.size.x, bo.size.y, bo.pixels = 160, 100, pin + n
+        _capi.check(lib.pf_b200_canny(ctypes.byref(bi), ctypes.byref(bo)))
+        got = np.ctypeslib.as_array((ctypes.c_uint8 * n).from_address(pin + n)).reshape(page.shape)
+        assert np.array_equal(got, oracle.canny(page))
+    finally:
+        lib.pf_b200_host_free(pin)
+
+
+def test_device_batch_entry_points(gpu, oracle):
+    import torch
+    from libpillowfight_b200.distributed import CudaChain
+    dev = torch.device("cuda:0")
+    pages = np.stack([synthetic_page(132, 90, i) for i in range(5)])
+    tin = torch.from_numpy(pages).to(dev)
+    chain = CudaChain()
+    g = chain.gaussian(tin, torch.empty_like(tin))
+    s = chain.sobel(g, torch.empty_like(tin))
+    c1 = chain.canny(tin, torch.empty_like(tin), pages_per_launch=1)
+    c5 = chain.canny(tin, torch.empty_like(tin), pages_per_launch=5)
+    torch.cuda.synchronize()
+    for i in range(5):
+        rg = oracle.gaussian(pages[i], 2.0, 5)
+        assert np.array_equal(g[i].cpu().numpy(), rg)
+        assert np.array_equal(s[i].cpu().numpy(), oracle.sobel(rg))
+        rc = oracle.canny(pages[i])
+        assert np.array_equal(c1[i].cpu().numpy(), rc)
+        assert np.array_equal(c5[i].cpu().numpy(), rc)
+
+
+def test_pil_images_round_trip(gpu, oracle):
+    from PIL import Image
+    page = synthetic_page(90, 70, 12)
+    img = Image.fromarray(page[..., :3], "RGB")          # converted to RGBA like upstream
+    out = gpu.sobel(img)
+    assert out.mode == "RGBA" and out.size == (90, 70)
+    assert np.array_equal(np.asarray(out), oracle.sobel(page))
+
+
+# ---- BASELINE.json's full sizes ----------------------------------------
+
+def test_full_a4_chain_against_oracle(gpu, oracle):
+    """configs[1] and [2]: Gaussian then Sobel, and Canny, on the A4 300-dpi page."""
+    page = synthetic_page(*A4_300DPI, page_index=0)
+    g = gpu.gaussian(page, 2.0, 5)
+    rg = oracle.gaussian(page, 2.0, 5)
+    assert np.array_equal(g, rg)
+    assert np.array_equal(gpu.sobel(g), oracle.sobel(rg))
+    assert np.array_equal(gpu.canny(page), oracle.canny(page))
+
+
+def test_full_a4_ace_against_oracle(gpu, oracle):
+    """configs[0]: ACE, A4 300 dpi, slope 10, limit 1000, 100 samples, fixed seed."""
+    import os
+    page = synthetic_page(*A4_300DPI, page_index=0)
+    w, h = A4_300DPI
+    xy = oracle.ace_draw_samples(100, w, h, 12345)
+    ref = oracle.ace_with_samples(page, xy, 10.0, 1000.0, nb_threads=os.cpu_count() or 8)
+    got = gpu.ace(page, 10, 1000, 100, seed=12345)
+    frac = assert_fp_parity(got, ref, "ace A4")
+    print("ACE A4: %.6f %% of channel values differ by 1 LSB" % (100 * frac))
+
+
+def test_size_independent_properties(gpu):
+    """Properties that hold at any size, checked at A4 without the oracle."""
+    page = synthetic_page(*A4_300DPI, page_index=1)
+    c = gpu.canny(page)
+    assert set(np.unique(c[..., 0])) <= {0, 255}
+    assert (c[..., 0] == c[..., 1]).all() and (c[..., 1] == c[..., 2]).all()
+    assert (c[..., 3] == 255).all()
+    # determinism: hysteresis is a fixed point, independent of scheduling
+    assert np.array_equal(c, gpu.canny(page))
+    # Sobel of a constant page is zero away from the border
+    flat = np.full((500, 700, 4), 77, dtype=np.uint8)
+    s = gpu.sobel(flat)
+    assert not s[1:-1, 1:-1, :3].any() and s[0, 5, 0] > 0
+    # ACE output spans the full range per channel and is reproducible per seed
+    a = gpu.ace(page, 10, 1000, 50, seed=3)
+    for ch in range(3):
+        assert a[..., ch].min() == 0 and a[..., ch].max() == 255
+    assert np.array_equal(a, gpu.ace(page, 10, 1000, 50, seed=3))
+    assert not np.array_equal(a, gpu.ace(page, 10, 1000, 50, seed=4))
