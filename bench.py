@@ -1,0 +1,531 @@
+#!/usr/bin/env python
+"""Benchmark of the libpillowfight hot path on B200 (contract: task prompt, section 4).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One STEP = the whole hot path over one synthetic A4 300-dpi page per GPU:
+    pf_apply_ace(slope 10, limit 1000, 100 samples, fixed seed)
+    pf_apply_gaussian(sigma 2.0, nb_stddev 5) -> pf_apply_sobel on its output
+    pf_apply_canny
+metric = page pixels through that step per second (Mpx/s), whole job.
+`value`: pages resident in HBM, C-ABI device entry points, CUDA-event timed.
+`e2e`:   the host-pointer entry points (pf_b200_ace/gaussian/sobel/canny) on
+         pinned host pages, copies inside the timed region.
+At N > 1 every rank runs the step on its own pages (pages are independent:
+no data-path collective, weak scaling); the row-band ACE split with its NCCL
+broadcast / all-reduce / all-gather (BASELINE.json config 4) is measured as
+`extras.ace_600dpi_row_bands`.
+"""
+import argparse
+import ctypes
+import json
+import os
+import socket
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+A4 = (2480, 3508)
+A4_600 = (4960, 7016)
+ACE_SEED = 12345
+FLOPS_PAIR = 22.0      # reference flops per pixel-sample pair that is not skipped
+FLOPS_SKIPPED = 5.0    # distance + test only
+N_SETS = 8             # page sets rotated through, > L2 in total
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true")
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------
+# helpers
+# --------------------------------------------------------------------------
+
+def count_pairs(w, h, xy):
+    """(#pairs not skipped, #pairs skipped) for the dist < h/5 rule."""
+    t2 = (h // 5) ** 2
+    ys = np.arange(h, dtype=np.int64)
+    skipped = 0
+    for sx, sy in zip(xy[0::2], xy[1::2]):
+        r2 = t2 - (ys - int(sy)) ** 2          # need dx^2 < r2
+        ok = r2 > 0
+        half = np.zeros(h, dtype=np.int64)
+        half[ok] = np.ceil(np.sqrt(r2[ok].astype(np.float64))).astype(np.int64) - 1
+        lo = np.maximum(int(sx) - half, 0)
+        hi = np.minimum(int(sx) + half, w - 1)
+        skipped += int(np.where(ok, np.maximum(hi - lo + 1, 0), 0).sum())
+    total = w * h * (len(xy) // 2)
+    return total - skipped, skipped
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the GPU is busy."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,utilization.gpu,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, reasons, power = [], None, set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 8:
+                continue
+            try:
+                clk, mx, util = float(r[0]), float(r[1]), float(r[3])
+            except ValueError:
+                continue
+            smax = mx
+            if util >= 50.0:
+                sm.append(clk)
+                try:
+                    power.append(float(r[2]))
+                except ValueError:
+                    pass
+                for n, v in zip(names, r[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+        allclk = [float(r[0]) for r in self.rows if len(r) >= 8 and r[0].replace(".", "").isdigit()]
+        return {"sm_mhz": float(np.median(sm)) if sm else (float(np.median(allclk)) if allclk else None),
+                "sm_max_mhz": smax, "reasons": sorted(reasons),
+                "samples_under_load": len(sm), "samples": len(self.rows),
+                "power_w_max": max(power) if power else None}
+
+
+def load_json(path):
+    try:
+        with open(path) as f:
+            return json.load(f)
+    except (OSError, ValueError):
+        return None
+
+
+def free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+# --------------------------------------------------------------------------
+# CPU side: the oracle as the reported baseline / the reference arm
+# --------------------------------------------------------------------------
+
+def cpu_step(o, pages, xy, cores):
+    """The same step on host cores with the CPU oracle: ACE with `cores`
+    pthreads page after page (the reference's own threading), then the stencil
+    chain of the pages on up to `cores` threads (one page per thread; the
+    reference's stencils are single-threaded).  Returns seconds."""
+    t0 = time.perf_counter()
+    for p in pages:
+        o.ace_with_samples(p, xy, 10.0, 1000.0, nb_threads=cores)
+
+    def chain(p):
+        g = o.gaussian(p, 2.0, 5)
+        o.sobel(g)
+        o.canny(p)
+
+    threads = [threading.Thread(target=chain, args=(p,)) for p in pages]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    return time.perf_counter() - t0
+
+
+def cpu_pages_per_step(cores):
+    return max(1, min(cores, 4))
+
+
+def run_reference(args):
+    """--impl reference: the CPU implementation of the path on the host cores.
+    The reference itself cannot be built (no sources in the mount), so this is
+    the oracle port (oracle/pf_oracle.c), kind "port"."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import pf_oracle as o
+    from libpillowfight_b200.pages import synthetic_page
+    o.lib()
+    cores = os.cpu_count() or 1
+    npg = cpu_pages_per_step(cores)
+    w, h = A4
+    pages = [synthetic_page(w, h, i) for i in range(npg)]
+    xy = o.ace_draw_samples(100, w, h, ACE_SEED)
+    for _ in range(args.warmup):
+        cpu_step(o, pages[:1], xy, cores)
+    t = 0.0
+    for _ in range(args.steps):
+        t += cpu_step(o, pages, xy, cores)
+    per = t / args.steps
+    val = npg * w * h / per / 1e6
+    sample = ("%d A4 300-dpi page(s) per step: ACE with %d pthreads page after page, then "
+              "Gaussian->Sobel and Canny one page per thread" % (npg, cores))
+    print(json.dumps({
+        "impl": "reference",
+        "metric": "ACE & Gauss+Sobel+Canny Mpx/s, A4@300dpi", "value": val, "unit": "Mpx/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": per * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "A4@300dpi page: ace(10,1000,100 samples)+gaussian(2.0,5)->sobel+canny",
+                   "width": w, "height": h, "pages_per_step": npg},
+        "cpu_baseline": {"value": val, "unit": "Mpx/s", "cores": cores, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": val, "unit": "Mpx/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# --------------------------------------------------------------------------
+# GPU side
+# --------------------------------------------------------------------------
+
+class Stage:
+    ACE, GAUSS, SOBEL, CANNY = range(4)
+    NAMES = ["ace", "gaussian", "sobel", "canny"]
+    LAUNCHES = [3, 1, 1, 4]
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.gpus > 1 and world == 1:
+        # convenience: re-launch under torchrun the way the driver does
+        os.execvp(sys.executable, [sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
+                                   "--nproc-per-node", str(args.gpus), "--master-addr", "127.0.0.1",
+                                   "--master-port", str(free_port()), os.path.abspath(__file__)]
+                  + sys.argv[1:])
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 path has no CPU fallback "
+                         "(use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    from libpillowfight_b200 import build as pf_build
+    if rank == 0:
+        pf_build.build()
+    if world > 1:
+        dist.barrier()
+    import libpillowfight_b200 as pf
+    from libpillowfight_b200 import _capi
+    from libpillowfight_b200.distributed import CudaAceCompute, CudaChain, ace_sharded, xy_tensor
+    from libpillowfight_b200.pages import synthetic_page
+    lib = _capi.lib
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    w, h = A4
+    npix = w * h
+    sampler = ClockSampler(local)
+
+    # ---- inputs resident in HBM: N_SETS distinct pages per rank --------------
+    host_pages = [synthetic_page(w, h, rank * 64 + i) for i in range(2)]
+    pages = torch.empty((N_SETS, h, w, 4), dtype=torch.uint8, device=dev)
+    for i in range(N_SETS):
+        # distinct content per set: page i%2 rolled by i rows (cheap to make)
+        pages[i] = torch.from_numpy(np.roll(host_pages[i % 2], 37 * i, axis=0)).to(dev)
+    xy_host = pf.ace_samples(100, w, h, ACE_SEED)
+    xy = xy_tensor(xy_host, dev)
+    out_ace = torch.empty_like(pages)
+    out_g = torch.empty_like(pages)
+    out_s = torch.empty_like(pages)
+    out_c = torch.empty_like(pages)
+    scores = torch.empty((3, h, w), dtype=torch.float64, device=dev)
+    minmax = torch.empty(6, dtype=torch.float64, device=dev)
+    scratch = torch.empty(lib.pf_b200_canny_scratch_bytes(w, h), dtype=torch.uint8, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    chk = _capi.check
+
+    def do_ace(i):
+        chk(lib.pf_b200_dev_ace_minmax_init(minmax.data_ptr(), st))
+        chk(lib.pf_b200_dev_ace_scores(pages[i].data_ptr(), w, h, 0, h, xy.data_ptr(), 100,
+                                       10.0, 1000.0, scores.data_ptr(), minmax.data_ptr(), st))
+        chk(lib.pf_b200_dev_ace_scale(scores.data_ptr(), minmax.data_ptr(), w, h,
+                                      out_ace[i].data_ptr(), st))
+
+    def do_gauss(i):
+        chk(lib.pf_b200_dev_gaussian(pages[i].data_ptr(), out_g[i].data_ptr(), w, h, 2.0, 5, st))
+
+    def do_sobel(i):
+        chk(lib.pf_b200_dev_sobel(out_g[i].data_ptr(), out_s[i].data_ptr(), w, h, st))
+
+    def do_canny(i):
+        chk(lib.pf_b200_dev_canny(pages[i].data_ptr(), out_c[i].data_ptr(), w, h, 1,
+                                  scratch.data_ptr(), scratch.numel(), st))
+
+    stage_fns = [do_ace, do_gauss, do_sobel, do_canny]
+
+    def step(i, marks=None):
+        s = i % N_SETS
+        for k, fn in enumerate(stage_fns):
+            if marks is not None:
+                marks[k][0].record()
+            fn(s)
+            if marks is not None:
+                marks[k][1].record()
+
+    # ---- main timed region ----------------------------------------------------
+    for i in range(args.warmup):
+        step(i)
+    torch.cuda.synchronize()
+    sampler.start()
+    K = args.steps
+    marks = [[[torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)]
+              for _ in range(4)] for _ in range(K)]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    for i in range(K):
+        step(args.warmup + i, marks[i])
+    e1.record()
+    torch.cuda.synchronize()
+    barrier()
+    ms_step = e0.elapsed_time(e1) / K
+    t = torch.tensor([ms_step], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item())
+    value = world * npix / (ms_step * 1e-3) / 1e6
+    stage_ms = [float(np.mean([marks[i][k][0].elapsed_time(marks[i][k][1]) for i in range(K)]))
+                for k in range(4)]
+
+    # ---- dominant kernel alone (ACE accumulation), for the roofline ----------
+    def time_fn(fn, iters, warm=3):
+        for i in range(warm):
+            fn(i % N_SETS)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        a.record()
+        for i in range(iters):
+            fn((warm + i) % N_SETS)
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / iters
+
+    def ace_scores_only(i):
+        chk(lib.pf_b200_dev_ace_scores(pages[i].data_ptr(), w, h, 0, h, xy.data_ptr(), 100,
+                                       10.0, 1000.0, scores.data_ptr(), minmax.data_ptr(), st))
+
+    def ace_scale_only(i):
+        chk(lib.pf_b200_dev_ace_scale(scores.data_ptr(), minmax.data_ptr(), w, h,
+                                      out_ace[i].data_ptr(), st))
+
+    iters = max(10, min(K, 50))
+    chk(lib.pf_b200_dev_ace_minmax_init(minmax.data_ptr(), st))
+    ms_ace_scores = time_fn(ace_scores_only, iters)
+    ms_ace_scale = time_fn(ace_scale_only, iters)
+    # stencil stages on cold inputs: each iteration reads a page set last
+    # touched N_SETS iterations (> 1 GB of traffic) ago
+    ms_cold = [None, time_fn(do_gauss, iters), time_fn(do_sobel, iters), time_fn(do_canny, iters)]
+
+    fp64_peak = lib.pf_b200_fp64_peak_tflops()
+    peaks = load_json(os.path.join(ROOT, "MEASURED_PEAKS.json"))
+    hbm_peak = float(peaks["hbm_gbs"]) if peaks and "hbm_gbs" in peaks else 6650.0
+    hbm_src = "MEASURED_PEAKS.json hbm_gbs" if peaks and "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    traffic = load_json(os.path.join(ROOT, "profiles", "traffic.json")) or {}
+
+    kept, skipped = count_pairs(w, h, xy_host)
+    ace_flops = kept * FLOPS_PAIR + skipped * FLOPS_SKIPPED
+    ace_tf = ace_flops / (ms_ace_scores * 1e-3) / 1e12
+    roofline = {"kernel": "ace_scores_kernel", "bound": "fp64", "achieved": ace_tf,
+                "peak": fp64_peak, "unit": "TFLOP/s", "frac": ace_tf / fp64_peak if fp64_peak > 0 else None,
+                "traffic": traffic.get("ace_scores_kernel"),
+                "peak_source": "pf_b200_fp64_peak_tflops(): DFMA probe run in this process "
+                               "(MEASURED_PEAKS.json has no FP64 figure)",
+                "algorithmic_flops_per_launch": ace_flops, "kernel_ms": ms_ace_scores,
+                "pairs_not_skipped": kept, "pairs_skipped": skipped}
+    stencils = {}
+    for k in (Stage.GAUSS, Stage.SOBEL, Stage.CANNY):
+        gbs = 8.0 * npix / (ms_cold[k] * 1e-3) / 1e9
+        stencils[Stage.NAMES[k]] = {
+            "bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak,
+            "traffic": traffic.get(Stage.NAMES[k]), "ms": ms_cold[k],
+            "mpx_s": npix / (ms_cold[k] * 1e-3) / 1e6, "algorithmic_bytes_per_launch": 8 * npix}
+
+    # ---- end to end through the host-pointer entry points ---------------------
+    nbytes = npix * 4
+    pin = lib.pf_b200_host_alloc(5 * nbytes)
+    if not pin:
+        raise SystemExit("pinned allocation failed: " + _capi.last_error()[1])
+
+    def host_view(k):
+        return np.ctypeslib.as_array((ctypes.c_uint8 * nbytes).from_address(pin + k * nbytes)
+                                     ).reshape(h, w, 4)
+
+    hv = [host_view(k) for k in range(5)]
+    hv[0][:] = host_pages[0]
+
+    def bm(k):
+        b = _capi.PfBitmap()
+        b.size.x, b.size.y, b.pixels = w, h, pin + k * nbytes
+        return b
+
+    b_in, b_ace, b_g, b_s, b_c = [bm(k) for k in range(5)]
+    xy_p = xy_host.ctypes.data_as(ctypes.POINTER(ctypes.c_int))
+
+    def e2e_step():
+        chk(lib.pf_b200_ace(ctypes.byref(b_in), ctypes.byref(b_ace), 100, xy_p, 10.0, 1000.0))
+        chk(lib.pf_b200_gaussian(ctypes.byref(b_in), ctypes.byref(b_g), 2.0, 5))
+        chk(lib.pf_b200_sobel(ctypes.byref(b_g), ctypes.byref(b_s)))
+        chk(lib.pf_b200_canny(ctypes.byref(b_in), ctypes.byref(b_c)))
+
+    for _ in range(max(3, args.warmup)):
+        e2e_step()
+    ke = max(5, min(K, 30))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(ke):
+        e2e_step()
+    t_e2e = (time.perf_counter() - t0) / ke
+    barrier()
+    te = torch.tensor([t_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    t_e2e = float(te.item())
+    e2e_value = world * npix / t_e2e / 1e6
+    # result check of the e2e path against the device-resident path (same kernels)
+    torch.cuda.synchronize()
+    e2e_ok = bool(np.array_equal(hv[4], pf.canny(hv[0])))
+    clocks = sampler.stop()
+
+    # ---- extras: ACE 600 dpi, 400 samples, row bands over the ranks -----------
+    extras = {}
+    if not args.no_extras:
+        w6, h6 = A4_600
+        big = torch.empty((h6, w6, 4), dtype=torch.uint8, device=dev)
+        if rank == 0:
+            small = torch.from_numpy(host_pages[0]).to(dev)
+            big[:] = small.repeat_interleave(2, dim=0).repeat_interleave(2, dim=1)[:h6, :w6]
+        xy6_host = pf.ace_samples(400, w6, h6, ACE_SEED)
+        xy6 = xy_tensor(xy6_host, dev)
+        comp = CudaAceCompute()
+        for _ in range(2):
+            ace_sharded(big, xy6, 10.0, 1000.0, comp)
+        n6 = 5
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        torch.cuda.synchronize()
+        a.record()
+        for _ in range(n6):
+            ace_sharded(big, xy6, 10.0, 1000.0, comp)
+        b.record()
+        torch.cuda.synchronize()
+        barrier()
+        t6 = torch.tensor([a.elapsed_time(b) / n6], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t6, op=dist.ReduceOp.MAX)
+        extras["ace_600dpi_row_bands"] = {
+            "workload": "pf_apply_ace 4960x7016, 400 samples, rows split over %d GPU(s); "
+                        "NCCL broadcast + min/max all-reduce + band all-gather inside the timed region"
+                        % world,
+            "ms": float(t6.item()), "mpx_s": w6 * h6 / (float(t6.item()) * 1e-3) / 1e6,
+            "scaling": "strong"}
+        del big
+
+    # ---- CPU baseline (rank 0, N = 1 only) ------------------------------------
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import pf_oracle as o
+        o.lib()
+        cores = os.cpu_count() or 1
+        npg = cpu_pages_per_step(cores)
+        cpu_pages = [host_pages[i % 2] for i in range(npg)]
+        secs = cpu_step(o, cpu_pages, xy_host, cores)
+        cpu_baseline = {
+            "value": npg * npix / secs / 1e6, "unit": "Mpx/s", "cores": cores, "kind": "port",
+            "sample": "one step of %d A4 300-dpi page(s), %.1f s: oracle ACE with %d pthreads page "
+                      "after page, then Gaussian->Sobel and Canny one page per thread "
+                      "(the reference's stencils are single-threaded)" % (npg, secs, cores)}
+
+    lib.pf_b200_host_free(pin)
+    if rank == 0:
+        line = {
+            "metric": "ACE & Gauss+Sobel+Canny Mpx/s, A4@300dpi", "value": value, "unit": "Mpx/s",
+            "n_gpus": world, "steps": K, "warmup": args.warmup, "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {
+                "workload": "A4@300dpi page per GPU: ace(slope 10, limit 1000, 100 samples, seed 12345)"
+                            " + gaussian(2.0, 5)->sobel + canny",
+                "width": w, "height": h, "pages_per_step": world,
+                "l2": "inputs rotate over %d page sets per GPU (%.1f GB in+out), so a page is not "
+                      "L2-resident when its step starts" % (N_SETS, N_SETS * 5 * nbytes / 1e9),
+                "hbm_peak_source": hbm_src},
+            "roofline": roofline,
+            "roofline_stencils": stencils,
+            "stages": {Stage.NAMES[k]: {"ms_in_step": stage_ms[k],
+                                        "mpx_s": npix / (stage_ms[k] * 1e-3) / 1e6,
+                                        "share": stage_ms[k] / sum(stage_ms)} for k in range(4)},
+            "ace_kernels_ms": {"scores": ms_ace_scores, "scale": ms_ace_scale},
+            "cpu_baseline": cpu_baseline,
+            "e2e": {"value": e2e_value, "unit": "Mpx/s", "h2d_bytes_per_step": 4 * nbytes + xy_host.nbytes,
+                    "d2h_bytes_per_step": 4 * nbytes, "ms_per_step": t_e2e * 1e3,
+                    "api": "pf_b200_ace/gaussian/sobel/canny on pinned host bitmaps",
+                    "result_checked": e2e_ok},
+            "gpu_launches": K * sum(Stage.LAUNCHES),
+            "clocks": clocks,
+            "extras": extras,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -190,8 +190,8 @@ __device__ void stage_samples(AceShared &sh, const AceConst &cs,
 template <bool FAST, bool NEWTON, bool TEST>
 __device__ __forceinline__ void accumulate_sample(const AceShared &sh, int j, int x,
 		const uint32_t (&pix)[kRowsPerThread], const uint32_t (&pk)[kRowsPerThread / 2][3],
-		uint32_t lo2, uint32_t hi2, double too_close2,
-		double (&acc)[kRowsPerThread][3], double (&wsum)[kRowsPerThread])
+		uint32_t lo2, uint32_t hi2, double too_close2, double top_value,
+		double (&acc)[kRowsPerThread][3], double (&top)[kRowsPerThread])
 {
 	constexpr int P = kRowsPerThread;
 	const SampleEntry se = sh.tbl[j];
@@ -205,7 +205,9 @@ __device__ __forceinline__ void accumulate_sample(const AceShared &sh, int j, in
 		if (TEST && d2 < too_close2)
 			wv = 0.0;
 		wgt[r] = wv;
-		wsum[r] += wv;
+		// the channel that saturates high on every sample: same FMA sequence
+		// as acc[], so a pixel that does saturate everywhere gets acc == top
+		top[r] = fma(wv, top_value, top[r]);
 	}
 	if (FAST) {
 #pragma unroll
@@ -272,6 +274,7 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 	const uint32_t lo2 = (uint32_t)(1152 - cs.clamp_l) * 0x00010001u;
 	const uint32_t hi2 = (uint32_t)(1152 + cs.clamp_l) * 0x00010001u;
 	const double too_close2 = (double)cs.too_close2;
+	const double top_value = FAST ? kBias + (double)cs.clamp_l : cs.limit;
 
 	double mn[3] = { DBL_MAX, DBL_MAX, DBL_MAX };
 	double mx[3] = { -DBL_MAX, -DBL_MAX, -DBL_MAX };
@@ -294,10 +297,10 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 				pk[g][c] = ((pix[2 * g] >> (8 * c)) & 0xFF)
 					| (((pix[2 * g + 1] >> (8 * c)) & 0xFF) << 16);
 
-		double acc[P][3], wsum[P];
+		double acc[P][3], top[P];
 #pragma unroll
 		for (int r = 0; r < P; r++) {
-			wsum[r] = 0.0;
+			top[r] = 0.0;
 #pragma unroll
 			for (int c = 0; c < 3; c++)
 				acc[r][c] = 0.0;
@@ -327,26 +330,30 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 			const int n_far = sh.n_far;
 			for (int j = 0; j < n_far; j++)
 				accumulate_sample<FAST, NEWTON, false>(sh, j, x, pix, pk, lo2, hi2,
-						too_close2, acc, wsum);
+						too_close2, top_value, acc, top);
 			for (int j = n_far; j < n_act; j++)
 				accumulate_sample<FAST, NEWTON, true>(sh, j, x, pix, pk, lo2, hi2,
-						too_close2, acc, wsum);
+						too_close2, top_value, acc, top);
 		}
 
-		// score = sum(sat/dist) / sum(limit/dist)
+		// score = sum(sat/dist) / sum(limit/dist).  `top` is the numerator of a
+		// channel saturated high on every sample, i.e. limit * sum(1/dist) up
+		// to the common factor, accumulated by the same FMA sequence as acc.
+		// The reference gets exactly 1.0 for every such pixel (numerator and
+		// denominator are the same sum); acc == top reproduces that tie.
 #pragma unroll
 		for (int r = 0; r < P; r++) {
 			const int y = y0 + r;
 			if (y >= cs.row_begin && y < cs.row_end && y < tile_y1 && x < cs.w) {
 				const size_t o = (size_t)(y - cs.row_begin) * cs.w + x;
-				const double inv = 1.0 / wsum[r];
+				const double inv = 1.0 / top[r];
 #pragma unroll
 				for (int c = 0; c < 3; c++) {
-					double s;
-					if (FAST)
-						s = fma(-kBias, wsum[r], acc[r][c]) * inv * cs.ratio;
-					else
-						s = acc[r][c] * inv / cs.limit;
+					double s = (acc[r][c] == top[r]) ? 1.0 : acc[r][c] * inv;
+					if (!(top[r] > 0.0))    // every sample skipped: 0/0 like the reference
+						s = __longlong_as_double(0x7FF8000000000000LL);
+					if (FAST)   // back from the biased value (kBias + c) / (kBias + L)
+						s = fma(top_value, s, -kBias) * cs.ratio;
 					scores[c * plane + o] = s;
 					if (s < mn[c]) mn[c] = s;     // NaN never enters
 					if (s > mx[c]) mx[c] = s;

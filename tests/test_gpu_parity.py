@@ -99,12 +99,12 @@ def test_canny_long_weak_chains(gpu, oracle):
     g = np.zeros((h, w), dtype=np.uint8)
     g[:, 100:] = 50            # |g_x| = 200: weak (174.9 < 200 <= 349.9)
     g[:30, 100:] = 120         # |g_x| = 480: strong near the top
-    g[60:, 200:] = np.minimum(g[60:, 200:] + 50, 255)   # second weak edge, isolated
+    g[60:640, 200:260] += 50   # a weak-contrast rectangle touching nothing strong
     page = np.stack([g, g, g, np.full_like(g, 255)], axis=-1)
     got, ref = gpu.canny(page), oracle.canny(page)
     assert np.array_equal(got, ref)
     assert ref[600, 99:101, 0].any()        # the chain reached the bottom
-    assert not ref[100:600, 198:202, 0].any()
+    assert not ref[100:600, 198:202, 0].any() and not ref[100:600, 258:262, 0].any()
 
 
 def test_canny_snake_fills_queues(gpu, oracle):
