@@ -143,11 +143,13 @@ int pf_b200_dev_gaussian(const uint32_t *d_in, uint32_t *d_out,
 int pf_b200_dev_sobel(const uint32_t *d_in, uint32_t *d_out,
 		int width, int height, void *stream);
 
-/* Canny needs scratch for the hysteresis work lists:
+/* Canny needs scratch for the hysteresis work list (the weak-edge candidates
+ * and their union-find links, 8 bytes per pixel in the worst case):
  * pf_b200_canny_scratch_bytes(width, height) bytes, 256-byte aligned.
  * nb_pages pages of the same size, stored back to back, are processed by one
- * call (page batches, BASELINE.json config 5); scratch is per call, not per
- * page. */
+ * call (page batches, BASELINE.json config 5).  Scratch is per call, not per
+ * page: with the minimum size pages go through one at a time; a scratch k
+ * times larger lets k pages share each kernel launch. */
 size_t pf_b200_canny_scratch_bytes(int width, int height);
 int pf_b200_dev_canny(const uint32_t *d_in, uint32_t *d_out,
 		int width, int height, int nb_pages,

@@ -30,7 +30,7 @@ namespace {
 
 constexpr int kAceBlock = 128;      // threads = columns per block
 constexpr int kRowsPerThread = 4;   // P: pixels a thread carries (same column)
-constexpr int kTileRows = 32;       // rows a block walks (8 row groups)
+constexpr int kTileRows = 16;       // rows a block walks (4 row groups)
 constexpr int kChunk = 512;         // samples staged in shared memory at a time
 constexpr double kBias = 4224.0;    // 4096 + 128: value spliced around c
 
@@ -120,67 +120,86 @@ struct AceConst {
 // classified against the tile rectangle: "far" ones can never be skipped,
 // "inside" ones always are (dropped here), the rest straddle the skip circle.
 // Order inside each class is the sample order, so sums are reproducible.
+// 1 = far (never skipped on this tile), 2 = straddles the skip circle, 0 = inside
+__device__ __forceinline__ int classify_sample(int sx, int sy, int x_lo, int x_hi,
+		int y_lo, int y_hi, int too_close2)
+{
+	const int dxm = max(max(x_lo - sx, sx - x_hi), 0);
+	const int dym = max(max(y_lo - sy, sy - y_hi), 0);
+	if (dxm * dxm + dym * dym >= too_close2)
+		return 1;
+	const int dxM = max(abs(sx - x_lo), abs(sx - x_hi));
+	const int dyM = max(abs(sy - y_lo), abs(sy - y_hi));
+	return (dxM * dxM + dyM * dyM >= too_close2) ? 2 : 0;
+}
+
 template <bool FAST>
-__device__ void stage_samples(AceShared &sh, const AceConst &cs,
+__device__ __noinline__ void stage_samples(AceShared &sh, const AceConst &cs,
 		const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
 		int k0, int kn, int x_lo, int x_hi, int y_lo, int y_hi)
 {
-	const int lane = threadIdx.x & 31;
-	if (threadIdx.x < 32) {
-		int n_far = 0, n_str = 0;
-		// pass 1: count far samples so that straddling ones go after them
-		for (int b = 0; b < kn; b += 32) {
-			const int k = b + lane;
-			bool far_ = false;
-			if (k < kn) {
-				const int sx = samples_xy[2 * (k0 + k)], sy = samples_xy[2 * (k0 + k) + 1];
-				const int dxm = max(max(x_lo - sx, sx - x_hi), 0);
-				const int dym = max(max(y_lo - sy, sy - y_hi), 0);
-				far_ = dxm * dxm + dym * dym >= cs.too_close2;
-			}
-			n_far += __popc(__ballot_sync(0xFFFFFFFFu, far_));
+	constexpr int kWarps = kAceBlock / 32;
+	constexpr int kPasses = kChunk / kAceBlock;
+	__shared__ int counts[kPasses][kWarps][2];
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const int2 *xy = reinterpret_cast<const int2 *>(samples_xy) + k0;
+	// sweep 1: how many far / straddling samples each warp holds per pass
+	for (int p = 0; p < kPasses; p++) {
+		const int k = p * kAceBlock + threadIdx.x;
+		int cls = 0;
+		if (k < kn) {
+			const int2 s = __ldg(xy + k);
+			cls = classify_sample(s.x, s.y, x_lo, x_hi, y_lo, y_hi, cs.too_close2);
 		}
-		int pos_far = 0, pos_str = n_far;
-		for (int b = 0; b < kn; b += 32) {
-			const int k = b + lane;
-			bool far_ = false, str_ = false;
-			int sx = 0, sy = 0;
-			if (k < kn) {
-				sx = samples_xy[2 * (k0 + k)];
-				sy = samples_xy[2 * (k0 + k) + 1];
-				const int dxm = max(max(x_lo - sx, sx - x_hi), 0);
-				const int dym = max(max(y_lo - sy, sy - y_hi), 0);
-				const int dxM = max(abs(sx - x_lo), abs(sx - x_hi));
-				const int dyM = max(abs(sy - y_lo), abs(sy - y_hi));
-				far_ = dxm * dxm + dym * dym >= cs.too_close2;
-				str_ = !far_ && (dxM * dxM + dyM * dyM >= cs.too_close2);
-			}
-			const unsigned mf = __ballot_sync(0xFFFFFFFFu, far_);
-			const unsigned ms = __ballot_sync(0xFFFFFFFFu, str_);
-			const unsigned below = (1u << lane) - 1;
-			int dst = -1;
-			if (far_)
-				dst = pos_far + __popc(mf & below);
-			else if (str_)
-				dst = pos_str + __popc(ms & below);
-			if (dst >= 0) {
-				const uint32_t p = __ldg(in + (size_t)sy * cs.w + sx);
-				sh.tbl[dst].sx = sx;
-				sh.sy[dst] = sy;
-#pragma unroll
-				for (int c = 0; c < 3; c++) {
-					const uint32_t s = (p >> (8 * c)) & 0xFF;
-					sh.tbl[dst].bias[c] = FAST ? (1152u - s) * 0x00010001u : s;
-				}
-			}
-			pos_far += __popc(mf);
-			pos_str += __popc(ms);
-			n_str += __popc(ms);
-		}
+		const unsigned mf = __ballot_sync(0xFFFFFFFFu, cls == 1);
+		const unsigned ms = __ballot_sync(0xFFFFFFFFu, cls == 2);
 		if (lane == 0) {
-			sh.n_far = n_far;
-			sh.n_str = n_str;
+			counts[p][warp][0] = __popc(mf);
+			counts[p][warp][1] = __popc(ms);
 		}
+	}
+	__syncthreads();
+	int n_far = 0;
+	for (int i = 0; i < kPasses * kWarps; i++)
+		n_far += counts[0][i][0];
+	// sweep 2: ordered compaction -- far samples first, then straddling, each
+	// class in sample order, so sums are reproducible
+	int off_far = 0, off_str = n_far;
+	for (int p = 0; p < kPasses; p++) {
+		for (int wv = 0; wv < warp; wv++) {
+			off_far += counts[p][wv][0];
+			off_str += counts[p][wv][1];
+		}
+		const int k = p * kAceBlock + threadIdx.x;
+		int cls = 0;
+		int2 s = make_int2(0, 0);
+		if (k < kn) {
+			s = __ldg(xy + k);
+			cls = classify_sample(s.x, s.y, x_lo, x_hi, y_lo, y_hi, cs.too_close2);
+		}
+		const unsigned mf = __ballot_sync(0xFFFFFFFFu, cls == 1);
+		const unsigned ms = __ballot_sync(0xFFFFFFFFu, cls == 2);
+		if (cls != 0) {
+			const unsigned below = (1u << lane) - 1;
+			const int dst = (cls == 1) ? off_far + __popc(mf & below)
+			                           : off_str + __popc(ms & below);
+			const uint32_t px = __ldg(in + (size_t)s.y * cs.w + s.x);
+			sh.tbl[dst].sx = s.x;
+			sh.sy[dst] = s.y;
+#pragma unroll
+			for (int c = 0; c < 3; c++) {
+				const uint32_t v = (px >> (8 * c)) & 0xFF;
+				sh.tbl[dst].bias[c] = FAST ? (1152u - v) * 0x00010001u : v;
+			}
+		}
+		for (int wv = warp; wv < kWarps; wv++) {
+			off_far += counts[p][wv][0];
+			off_str += counts[p][wv][1];
+		}
+	}
+	if (threadIdx.x == kAceBlock - 1) {     // last thread: offsets are the totals
+		sh.n_far = n_far;
+		sh.n_str = off_str - n_far;
 	}
 	__syncthreads();
 }
@@ -240,7 +259,7 @@ __device__ __forceinline__ void accumulate_sample(const AceShared &sh, int j, in
 // FAST: L = limit/slope is an integer <= 127, clamp on the integer pipe.
 // !FAST: any slope/limit, saturation values read from a 511-entry table.
 template <bool FAST, bool NEWTON>
-__global__ void __launch_bounds__(kAceBlock)
+__global__ void __launch_bounds__(kAceBlock, 6)
 ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
 		const AceConst cs, double *__restrict__ scores, double *__restrict__ minmax)
 {

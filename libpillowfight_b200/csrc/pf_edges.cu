@@ -1,0 +1,503 @@
+// Sobel and Canny kernels for sm_100a.
+//
+// Reference semantics (upstream src/pillowfight/_sobel.c, _canny.c, util.c --
+// not in the mount): grayscale = (r+g+b)/3, g_x / g_y by
+// true convolution with the 3x3 Sobel kernels (taps outside the page skipped
+// = zero padding), intensity = hypot(g_x, g_y).  g_x and g_y are small
+// integers, so everything the reference does in double is reproduced exactly
+// in int32: floor(hypot) = isqrt(g_x^2+g_y^2), intensity comparisons compare
+// g_x^2+g_y^2, the direction sector is an exact integer test.
+//
+// Layout: a warp marches down a strip of rows.  Each lane owns 4 adjacent
+// columns (one 16-byte load / store per row); lanes 0 and 31 are halo lanes
+// whose values only feed their neighbours through shuffles, so a warp emits
+// 120 columns.  The vertical window lives in registers, rotated by unrolling
+// the row loop by 3.  Per stage a pixel is read once and written once.
+#include "pf_common.cuh"
+
+namespace pfb {
+
+namespace {
+
+constexpr int kWarpsPerBlock = 4;
+constexpr int kOutLanes = 30;
+constexpr int kWarpCols = kOutLanes * 4;        // 120 output columns per warp
+constexpr unsigned kFull = 0xFFFFFFFFu;
+
+constexpr uint32_t kWhite = 0xFFFFFFFFu;   // kept edge
+constexpr uint32_t kBlack = 0xFF000000u;   // no edge
+// A weak candidate is stored as its index in the work list; every index is
+// below kBlack, so "value < kBlack" tags a weak pixel until pass C resolves it.
+
+struct StripGeom {
+	int w, h;
+	int rows_per_strip;
+	int warp_cols;       // ceil(w / 120)
+	int strips;          // ceil(h / rows_per_strip)
+	int aligned;         // rows can be accessed as uint4
+};
+
+// (r + g + b) / 3: one SAD against zero sums the three bytes, IMAD.HI divides.
+__device__ __forceinline__ int gray_of(uint32_t p)
+{
+	return (int)__umulhi(__vsadu4(p & 0x00FFFFFFu, 0u), 0x55555556u);
+}
+
+__device__ __forceinline__ uint4 load_px4(const uint32_t *__restrict__ img,
+		const StripGeom &g, int r, int x0)
+{
+	uint4 v = make_uint4(0u, 0u, 0u, 0u);
+	if (r < 0 || r >= g.h)
+		return v;
+	const uint32_t *row = img + (size_t)r * g.w;
+	if (g.aligned && x0 >= 0 && x0 + 3 < g.w)
+		return __ldg(reinterpret_cast<const uint4 *>(row + x0));
+	if (x0 >= 0 && x0 < g.w) v.x = __ldg(row + x0);
+	if (x0 + 1 >= 0 && x0 + 1 < g.w) v.y = __ldg(row + x0 + 1);
+	if (x0 + 2 >= 0 && x0 + 2 < g.w) v.z = __ldg(row + x0 + 2);
+	if (x0 + 3 >= 0 && x0 + 3 < g.w) v.w = __ldg(row + x0 + 3);
+	return v;
+}
+
+__device__ __forceinline__ void store_px4(uint32_t *__restrict__ img,
+		const StripGeom &g, int r, int x0, const uint32_t (&v)[4])
+{
+	uint32_t *row = img + (size_t)r * g.w;
+	if (g.aligned && x0 + 3 < g.w) {
+		*reinterpret_cast<uint4 *>(row + x0) = make_uint4(v[0], v[1], v[2], v[3]);
+		return;
+	}
+#pragma unroll
+	for (int i = 0; i < 4; i++)
+		if (x0 + i < g.w)
+			row[x0 + i] = v[i];
+}
+
+// Horizontal parts of the two Sobel kernels for the lane's 4 columns:
+//   hd = g(x-1) - g(x+1)            (g_x row term, kernel flipped)
+//   hs = g(x-1) + 2 g(x) + g(x+1)   (g_y row term)
+struct HRow {
+	int hd[4], hs[4];
+};
+
+__device__ __forceinline__ void hrow_from_pixels(const uint4 px, HRow &o)
+{
+	int g[6];
+	g[1] = gray_of(px.x);
+	g[2] = gray_of(px.y);
+	g[3] = gray_of(px.z);
+	g[4] = gray_of(px.w);
+	g[0] = __shfl_up_sync(kFull, g[4], 1);      // left lane's last column
+	g[5] = __shfl_down_sync(kFull, g[1], 1);    // right lane's first column
+#pragma unroll
+	for (int i = 0; i < 4; i++) {
+		o.hd[i] = g[i] - g[i + 2];
+		o.hs[i] = g[i] + 2 * g[i + 1] + g[i + 2];
+	}
+}
+
+// min(255, floor(sqrt(m))).  sqrt(m + 0.5) sits at least 1/(4*255) away from
+// every integer for m < 2^16, far more than MUFU.SQRT's error, so the
+// truncation is exact.
+__device__ __forceinline__ uint32_t isqrt_cap255(int m)
+{
+	float r;
+	asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"((float)min(m, 65535) + 0.5f));
+	return (uint32_t)min(__float2int_rz(r), 255);
+}
+
+// ---------------------------------------------------------------------------
+// Sobel
+// ---------------------------------------------------------------------------
+
+// rows r-2, r-1, r of the horizontal terms sit in slots (J+1)%3, (J+2)%3, J
+template <int J>
+__device__ __forceinline__ void sobel_step(const uint32_t *__restrict__ in,
+		uint32_t *__restrict__ out, const StripGeom &g, int r, int r_last,
+		int x0, bool out_lane, int ys, uint4 &nxt, HRow (&hr)[3])
+{
+	if (r > r_last)
+		return;
+	const uint4 cur = nxt;
+	nxt = load_px4(in, g, r + 1, x0);            // in flight during this row's math
+	hrow_from_pixels(cur, hr[J]);
+	const int y = r - 1;
+	if (y < ys || !out_lane || x0 >= g.w)
+		return;
+	const HRow &a = hr[(J + 1) % 3], &b = hr[(J + 2) % 3], &c = hr[J];
+	uint32_t res[4];
+#pragma unroll
+	for (int i = 0; i < 4; i++) {
+		const int gx = c.hd[i] + 2 * b.hd[i] + a.hd[i];
+		const int gy = a.hs[i] - c.hs[i];
+		res[i] = kBlack + isqrt_cap255(gx * gx + gy * gy) * 0x010101u;
+	}
+	store_px4(out, g, y, x0, res);
+}
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+sobel_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
+		const StripGeom g)
+{
+	const int gw = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+	const int strip = gw / g.warp_cols;
+	if (strip >= g.strips)
+		return;
+	const int lane = threadIdx.x & 31;
+	const int x0 = (gw - strip * g.warp_cols) * kWarpCols - 4 + lane * 4;
+	const bool out_lane = lane >= 1 && lane <= kOutLanes;
+	const size_t page = (size_t)blockIdx.y * g.w * g.h;
+	in += page;
+	out += page;
+	const int ys = strip * g.rows_per_strip;
+	const int ye = min(g.h, ys + g.rows_per_strip);
+
+	HRow hr[3];
+	uint4 nxt = load_px4(in, g, ys - 1, x0);
+	// gray rows ys-1 .. ye; row r yields output row r-1
+	const int r_last = ye;
+	for (int r = ys - 1; r <= r_last; r += 3) {
+		sobel_step<0>(in, out, g, r, r_last, x0, out_lane, ys, nxt, hr);
+		sobel_step<1>(in, out, g, r + 1, r_last, x0, out_lane, ys, nxt, hr);
+		sobel_step<2>(in, out, g, r + 2, r_last, x0, out_lane, ys, nxt, hr);
+	}
+}
+
+// ---------------------------------------------------------------------------
+// Canny pass A: gradients, non-maximum suppression, double threshold
+// ---------------------------------------------------------------------------
+
+// One gradient row for the lane's 4 columns plus the two neighbouring columns.
+struct GRow {
+	int m[6];          // g_x^2 + g_y^2 at columns x0-1 .. x0+4, 0 outside the page
+	int sector[4];     // 0: E-W, 1: SE-NW, 2: N-S, 3: SW-NE neighbours
+};
+
+__device__ __forceinline__ void grow_from_hrows(const HRow &a, const HRow &b,
+		const HRow &c, bool row_inside, int x0, int w, GRow &o)
+{
+#pragma unroll
+	for (int i = 0; i < 4; i++) {
+		const int gx = c.hd[i] + 2 * b.hd[i] + a.hd[i];
+		const int gy = a.hs[i] - c.hs[i];
+		const int gx2 = gx * gx, gy2 = gy * gy;
+		const int x = x0 + i;
+		o.m[i + 1] = (row_inside && x >= 0 && x < w) ? gx2 + gy2 : 0;
+		// |angle| < 22.5 deg  <=>  (|gx|+|gy|)^2 < 2 gx^2  <=>  2|gx gy| < gx^2 - gy^2
+		const int q = gx * gy;
+		const int p2 = 2 * abs(q);
+		const int d = gx2 - gy2;
+		o.sector[i] = (p2 < d) ? 0 : ((p2 < -d) ? 2 : ((q >= 0) ? 1 : 3));
+	}
+	o.m[0] = __shfl_up_sync(kFull, o.m[4], 1);
+	o.m[5] = __shfl_down_sync(kFull, o.m[1], 1);
+}
+
+template <int J>
+__device__ __forceinline__ void canny_step(const uint32_t *__restrict__ in,
+		uint32_t *__restrict__ out, const StripGeom &g, int r, int r_last,
+		int x0, bool out_lane, int ys, int page_base, CannyThresholds thr,
+		int *__restrict__ hdr, int *__restrict__ list, int *__restrict__ parent,
+		uint4 &nxt, HRow (&hr)[3], GRow (&gr)[3])
+{
+	if (r > r_last)
+		return;
+	const uint4 cur = nxt;
+	nxt = load_px4(in, g, r + 1, x0);
+	hrow_from_pixels(cur, hr[J]);
+	if (r < ys)
+		return;                  // gray rows r-2, r-1, r are needed
+	// gradient row r-1 goes to the slot of gray row r
+	const int grow = r - 1;
+	grow_from_hrows(hr[(J + 1) % 3], hr[(J + 2) % 3], hr[J],
+			grow >= 0 && grow < g.h, x0, g.w, gr[J]);
+	const int y = r - 2;
+	if (y < ys)
+		return;                  // gradient rows y-1, y, y+1 are needed
+	const GRow &up = gr[(J + 1) % 3], &mid = gr[(J + 2) % 3], &dn = gr[J];
+	uint32_t res[4];
+	int nweak = 0;
+#pragma unroll
+	for (int i = 0; i < 4; i++) {
+		const int m = mid.m[i + 1];
+		const int s = mid.sector[i];
+		const int ew = max(mid.m[i], mid.m[i + 2]);
+		const int ns = max(up.m[i + 1], dn.m[i + 1]);
+		const int d1 = max(dn.m[i + 2], up.m[i]);       // (x+1,y+1), (x-1,y-1)
+		const int d3 = max(dn.m[i], up.m[i + 2]);       // (x-1,y+1), (x+1,y-1)
+		const int nb = (s == 0) ? ew : ((s == 2) ? ns : ((s == 1) ? d1 : d3));
+		uint32_t v = kBlack;
+		if (m >= nb && m >= thr.weak_min) {
+			v = kWhite;
+			if (m < thr.strong_min && out_lane && x0 + i < g.w) {
+				v = 0u;          // weak: index filled in below
+				nweak++;
+			}
+		}
+		res[i] = v;
+	}
+	// warp-aggregated append of this row's weak pixels to the work list
+	const unsigned any = __ballot_sync(kFull, nweak > 0);
+	if (any) {
+		const int lane = threadIdx.x & 31;
+		int pre = nweak;
+#pragma unroll
+		for (int dlt = 1; dlt < 32; dlt <<= 1) {
+			const int t = __shfl_up_sync(kFull, pre, dlt);
+			if (lane >= dlt)
+				pre += t;
+		}
+		int base = 0;
+		if (lane == 31)
+			base = atomicAdd(&hdr[0], pre);
+		base = __shfl_sync(kFull, base, 31) + pre - nweak;
+		if (nweak > 0) {
+			const int pix0 = page_base + y * g.w + x0;
+#pragma unroll
+			for (int i = 0; i < 4; i++) {
+				if (res[i] == 0u) {
+					res[i] = (uint32_t)base;
+					list[base] = pix0 + i;
+					parent[base] = base;
+					base++;
+				}
+			}
+		}
+	}
+	if (out_lane && x0 < g.w)
+		store_px4(out, g, y, x0, res);
+}
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+canny_classify_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
+		const StripGeom g, CannyThresholds thr,
+		int *__restrict__ hdr, int *__restrict__ list, int *__restrict__ parent)
+{
+	const int gw = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+	const int strip = gw / g.warp_cols;
+	if (strip >= g.strips)
+		return;
+	const int lane = threadIdx.x & 31;
+	const int x0 = (gw - strip * g.warp_cols) * kWarpCols - 4 + lane * 4;
+	const bool out_lane = lane >= 1 && lane <= kOutLanes;
+	const int npix = g.w * g.h;
+	const size_t page = (size_t)blockIdx.y * npix;
+	in += page;
+	out += page;
+	const int ys = strip * g.rows_per_strip;
+	const int ye = min(g.h, ys + g.rows_per_strip);
+
+	HRow hr[3];
+	GRow gr[3];
+	uint4 nxt = load_px4(in, g, ys - 2, x0);
+	// gray rows ys-2 .. ye+1; row r yields gradient row r-1 and output row r-2
+	const int r_last = ye + 1;
+	const int page_base = (int)blockIdx.y * npix;
+	// start so that (r - start) % 3 == J matches the slot arithmetic above
+	for (int r = ys - 2; r <= r_last; r += 3) {
+		canny_step<0>(in, out, g, r, r_last, x0, out_lane, ys, page_base, thr, hdr, list, parent, nxt, hr, gr);
+		canny_step<1>(in, out, g, r + 1, r_last, x0, out_lane, ys, page_base, thr, hdr, list, parent, nxt, hr, gr);
+		canny_step<2>(in, out, g, r + 2, r_last, x0, out_lane, ys, page_base, thr, hdr, list, parent, nxt, hr, gr);
+	}
+}
+
+// ---------------------------------------------------------------------------
+// Canny pass B: hysteresis as connected components over the weak work list.
+// A weak pixel is kept iff its 8-connected component of weak pixels touches a
+// strong pixel.  Union-find over list indices (hook the larger root under the
+// smaller with atomicCAS, path halving), so the cost does not depend on how
+// long a weak chain is and the result does not depend on scheduling.
+// ---------------------------------------------------------------------------
+
+struct PageGeom {
+	int w, h, npix;
+};
+
+__device__ __forceinline__ int uf_find(int *parent, int i)
+{
+	// L2 loads/stores: other SMs hook roots with atomics while this runs
+	int p = __ldcg(parent + i);
+	while (p != i) {
+		const int gp = __ldcg(parent + p);
+		if (gp != p)
+			__stcg(parent + i, gp);      // path halving; races only shorten paths
+		i = p;
+		p = gp;
+	}
+	return i;
+}
+
+__device__ __forceinline__ void uf_union(int *parent, int a, int b)
+{
+	for (;;) {
+		a = uf_find(parent, a);
+		b = uf_find(parent, b);
+		if (a == b)
+			return;
+		if (a < b) {
+			const int t = a;
+			a = b;
+			b = t;
+		}
+		// a > b: hang root a under b
+		const int old = atomicCAS(&parent[a], a, b);
+		if (old == a)
+			return;
+	}
+}
+
+constexpr int kStrongBit = (int)0x80000000;   // in list[root]: component touches a strong pixel
+
+// B1: join every weak pixel with its weak neighbours.  Each undirected edge is
+// taken once, from the pixel with the smaller address (E, SW, S, SE).
+__global__ void __launch_bounds__(256)
+canny_link_kernel(const uint32_t *__restrict__ out, PageGeom pg,
+		const int *__restrict__ list, int *__restrict__ parent, const int *__restrict__ hdr)
+{
+	const int count = hdr[0];
+	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count;
+			i += gridDim.x * blockDim.x) {
+		const int idx = list[i];
+		const int p = idx % pg.npix;
+		const int y = p / pg.w, x = p - y * pg.w;
+		const bool has_e = x + 1 < pg.w, has_w = x > 0, has_s = y + 1 < pg.h;
+		uint32_t v;
+		if (has_e && (v = out[idx + 1]) < kBlack)
+			uf_union(parent, i, (int)v);
+		if (has_s) {
+			if (has_w && (v = out[idx + pg.w - 1]) < kBlack)
+				uf_union(parent, i, (int)v);
+			if ((v = out[idx + pg.w]) < kBlack)
+				uf_union(parent, i, (int)v);
+			if (has_e && (v = out[idx + pg.w + 1]) < kBlack)
+				uf_union(parent, i, (int)v);
+		}
+	}
+}
+
+// B2: a weak pixel next to a strong one marks its component's root.
+__global__ void __launch_bounds__(256)
+canny_seed_kernel(const uint32_t *__restrict__ out, PageGeom pg,
+		int *__restrict__ list, int *__restrict__ parent, const int *__restrict__ hdr)
+{
+	const int count = hdr[0];
+	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count;
+			i += gridDim.x * blockDim.x) {
+		const int idx = list[i] & ~kStrongBit;
+		const int p = idx % pg.npix;
+		const int y = p / pg.w, x = p - y * pg.w;
+		bool strong = false;
+#pragma unroll
+		for (int dy = -1; dy <= 1; dy++) {
+#pragma unroll
+			for (int dx = -1; dx <= 1; dx++) {
+				if (dx == 0 && dy == 0)
+					continue;
+				if (x + dx < 0 || x + dx >= pg.w || y + dy < 0 || y + dy >= pg.h)
+					continue;
+				strong |= out[idx + dy * pg.w + dx] == kWhite;
+			}
+		}
+		if (strong)
+			atomicOr(&list[uf_find(parent, i)], kStrongBit);
+	}
+}
+
+// C: every weak pixel takes its component's verdict.
+__global__ void __launch_bounds__(256)
+canny_resolve_kernel(uint32_t *__restrict__ out, const int *__restrict__ list,
+		int *__restrict__ parent, const int *__restrict__ hdr)
+{
+	const int count = hdr[0];
+	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count;
+			i += gridDim.x * blockDim.x) {
+		const int root = uf_find(parent, i);
+		const bool keep = (list[root] & kStrongBit) != 0;
+		out[list[i] & ~kStrongBit] = keep ? kWhite : kBlack;
+	}
+}
+
+StripGeom make_geom(const uint32_t *in, const uint32_t *out, int w, int h, int pages,
+		int target_warps_per_sm, int min_rows)
+{
+	StripGeom g;
+	g.w = w;
+	g.h = h;
+	g.warp_cols = (w + kWarpCols - 1) / kWarpCols;
+	// about target_warps_per_sm warps per SM in one wave, strips no shorter than min_rows
+	long want = (long)sm_count() * target_warps_per_sm / ((long)g.warp_cols * pages);
+	if (want < 1)
+		want = 1;
+	int rows = (int)((h + want - 1) / want);
+	if (rows < min_rows)
+		rows = min_rows;
+	g.rows_per_strip = rows;
+	g.strips = (h + rows - 1) / rows;
+	g.aligned = (w % 4 == 0) && (((uintptr_t)in | (uintptr_t)out) % 16 == 0);
+	return g;
+}
+
+}  // namespace
+
+int launch_sobel(const uint32_t *in, uint32_t *out, int w, int h, int pages,
+		cudaStream_t st)
+{
+	const StripGeom g = make_geom(in, out, w, h, pages, 32, 16);
+	const int warps = g.warp_cols * g.strips;
+	dim3 grid((warps + kWarpsPerBlock - 1) / kWarpsPerBlock, pages);
+	sobel_kernel<<<grid, kWarpsPerBlock * 32, 0, st>>>(in, out, g);
+	PFB_CUDA(cudaGetLastError());
+	return PF_B200_OK;
+}
+
+// scratch: 256-byte header, then per pixel of the largest batch the work list
+// entry and the union-find parent (2 ints)
+size_t canny_scratch_bytes(int w, int h)
+{
+	return 256 + 2 * sizeof(int) * (size_t)w * h;
+}
+
+int launch_canny(const uint32_t *in, uint32_t *out, int w, int h, int pages,
+		CannyThresholds thr, void *scratch, size_t scratch_bytes,
+		cudaStream_t st)
+{
+	const size_t npix = (size_t)w * h;
+	if (npix >= 0x7F000000ull)
+		return fail(PF_B200_ETOOBIG, "canny: page of %d x %d is too large", w, h);
+	if (scratch == nullptr || scratch_bytes < canny_scratch_bytes(w, h))
+		return fail(PF_B200_EINVAL, "canny: scratch of %zu bytes, need %zu",
+				scratch_bytes, canny_scratch_bytes(w, h));
+	if (((uintptr_t)scratch & 255) != 0)
+		return fail(PF_B200_EINVAL, "canny: scratch must be 256-byte aligned");
+	// pages per launch: what the scratch holds and an int (below kBlack) can index
+	size_t cap_pages = (scratch_bytes - 256) / (2 * sizeof(int) * npix);
+	const size_t idx_pages = 0x7F000000ull / npix;
+	if (cap_pages > idx_pages)
+		cap_pages = idx_pages;
+	if (cap_pages > 65535)
+		cap_pages = 65535;
+	int *hdr = static_cast<int *>(scratch);
+	int *list = hdr + 64;
+	const PageGeom pg = { w, h, (int)npix };
+	const int sparse_blocks = sm_count() * 2;
+
+	for (int p0 = 0; p0 < pages; p0 += (int)cap_pages) {
+		const int np = (pages - p0 < (int)cap_pages) ? pages - p0 : (int)cap_pages;
+		const uint32_t *pin = in + (size_t)p0 * npix;
+		uint32_t *pout = out + (size_t)p0 * npix;
+		int *parent = list + (size_t)np * npix;
+		PFB_CUDA(cudaMemsetAsync(hdr, 0, 256, st));
+		const StripGeom g = make_geom(pin, pout, w, h, np, 24, 24);
+		const int warps = g.warp_cols * g.strips;
+		dim3 grid((warps + kWarpsPerBlock - 1) / kWarpsPerBlock, np);
+		canny_classify_kernel<<<grid, kWarpsPerBlock * 32, 0, st>>>(pin, pout, g, thr,
+				hdr, list, parent);
+		canny_link_kernel<<<sparse_blocks, 256, 0, st>>>(pout, pg, list, parent, hdr);
+		canny_seed_kernel<<<sparse_blocks, 256, 0, st>>>(pout, pg, list, parent, hdr);
+		canny_resolve_kernel<<<sparse_blocks, 256, 0, st>>>(pout, list, parent, hdr);
+		PFB_CUDA(cudaGetLastError());
+	}
+	return PF_B200_OK;
+}
+
+}  // namespace pfb

@@ -1,0 +1,240 @@
+// Gaussian kernel for sm_100a (Sobel and Canny are in pf_edges.cu).
+//
+// A "column-march" stencil: a thread owns a few adjacent columns of a
+// horizontal strip of the page and walks down the rows, keeping the vertical
+// window of the stencil in registers.  Every RGBA8 pixel is read from HBM
+// once (row halos come out of L1/L2) and written once: 8 algorithmic bytes
+// per pixel.
+//
+// Reference semantics (upstream src/pillowfight/util.c pf_dbl_matrix_convolution,
+// _gaussian.c -- not in the mount):
+// true convolution with the kernel centre at size/2, taps outside the page
+// skipped.  Skipping a tap and adding +0.0 give the same double, so the
+// kernels zero-pad.
+#include "pf_common.cuh"
+
+namespace pfb {
+
+namespace {
+
+constexpr int kBlock = 128;
+
+__device__ __forceinline__ uint32_t load_px(const uint32_t *row, int x, int w)
+{
+	return (row != nullptr && x >= 0 && x < w) ? __ldg(row + x) : 0u;
+}
+
+// ---------------------------------------------------------------------------
+// Gaussian
+// ---------------------------------------------------------------------------
+
+// uint8 -> double without the conversion pipe: 2^52 + v is exact, minus 2^52.
+__device__ __forceinline__ double u8_to_double(uint32_t v)
+{
+	return __dadd_rn(__hiloint2double(0x43300000, (int)v), -4503599627370496.0);
+}
+
+// trunc(v) for 0 <= v < 2^31 with one DADD (round toward zero into 2^52's ulp)
+__device__ __forceinline__ int trunc_nonneg(double v)
+{
+	return __double2loint(__dadd_rz(v, 4503599627370496.0));
+}
+
+template <int N>
+struct TapsN {
+	double t[N];
+};
+
+// Strict-order separable convolution in FP64.  Each thread produces PX
+// adjacent pixels per row.  N taps, centre N/2.  The horizontal sums of the
+// last N rows sit in a register ring; __dmul_rn/__dadd_rn keep the compiler
+// from contracting to FMA so that every rounding matches the C reference.
+template <int N, int PX>
+__global__ void __launch_bounds__(kBlock)
+gaussian_march_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
+		int w, int h, int rows_per_strip, const TapsN<N> tp)
+{
+	constexpr int C = N / 2;             // taps reach x+C ... x-(N-1-C)
+	constexpr int L = N - 1 - C;         // left / up reach
+	constexpr int NPIX = PX + N - 1;     // input pixels a thread needs per row
+
+	const int x0 = (blockIdx.x * kBlock + threadIdx.x) * PX;
+	if (x0 >= w)
+		return;
+	const size_t page = (size_t)blockIdx.z * w * h;
+	in += page;
+	out += page;
+	const int ys = blockIdx.y * rows_per_strip;
+	const int ye = min(h, ys + rows_per_strip);
+
+	double taps[N];
+#pragma unroll
+	for (int k = 0; k < N; k++)
+		taps[k] = tp.t[k];
+
+	double ring[N][PX * 3];
+
+	// row r of the horizontal pass lands in ring slot (r - (ys - L)) % N
+	for (int r0 = ys - L; r0 < ye + C; r0 += N) {
+#pragma unroll
+		for (int j = 0; j < N; j++) {
+			const int r = r0 + j;
+			if (r < ye + C) {
+				// ---- horizontal pass of row r into ring[j] ----
+				const uint32_t *row = (r >= 0 && r < h) ? in + (size_t)r * w : nullptr;
+				double px[NPIX][3];
+#pragma unroll
+				for (int i = 0; i < NPIX; i++) {
+					const uint32_t p = load_px(row, x0 - L + i, w);
+					px[i][0] = u8_to_double(p & 0xFF);
+					px[i][1] = u8_to_double((p >> 8) & 0xFF);
+					px[i][2] = u8_to_double((p >> 16) & 0xFF);
+				}
+#pragma unroll
+				for (int o = 0; o < PX; o++) {
+#pragma unroll
+					for (int c = 0; c < 3; c++) {
+						// tap k multiplies pixel x - k + C = index (o + L) - k + C
+						double v = __dmul_rn(px[o + N - 1][c], taps[0]);
+#pragma unroll
+						for (int k = 1; k < N; k++)
+							v = __dadd_rn(v, __dmul_rn(px[o + N - 1 - k][c], taps[k]));
+						ring[j][o * 3 + c] = v;
+					}
+				}
+				// ---- vertical pass for output row y = r - C ----
+				const int y = r - C;
+				if (y >= ys) {
+					uint32_t res[PX];
+#pragma unroll
+					for (int o = 0; o < PX; o++) {
+						uint32_t rgba = 0xFF000000u;
+#pragma unroll
+						for (int c = 0; c < 3; c++) {
+							// tap k multiplies row y - k + C = r - k: slot (j - k) mod N
+							double v = __dmul_rn(ring[j][o * 3 + c], taps[0]);
+#pragma unroll
+							for (int k = 1; k < N; k++)
+								v = __dadd_rn(v, __dmul_rn(
+										ring[(j - k + N) % N][o * 3 + c], taps[k]));
+							const int q = min(trunc_nonneg(v), 255);
+							rgba |= (uint32_t)q << (8 * c);
+						}
+						res[o] = rgba;
+					}
+					uint32_t *orow = out + (size_t)y * w;
+					if (PX == 2 && x0 + 1 < w && ((w & 1) == 0)) {
+						*reinterpret_cast<uint2 *>(orow + x0) = make_uint2(res[0], res[PX - 1]);
+					} else {
+#pragma unroll
+						for (int o = 0; o < PX; o++)
+							if (x0 + o < w)
+								orow[x0 + o] = res[o];
+					}
+				}
+			}
+		}
+	}
+}
+
+// Any tap count: one thread per pixel, N*N multiply-adds, same rounding order.
+__global__ void __launch_bounds__(kBlock)
+gaussian_generic_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
+		int w, int h, const Taps tp)
+{
+	const int n = tp.n;
+	const int x = blockIdx.x * kBlock + threadIdx.x;
+	const int y = blockIdx.y;
+	if (x >= w)
+		return;
+	const size_t page = (size_t)blockIdx.z * w * h;
+	in += page;
+	out += page;
+	const int c0 = n / 2;
+	double acc[3] = { 0.0, 0.0, 0.0 };
+	bool first_row = true;
+	for (int ky = 0; ky < n; ky++) {
+		const int iy = y - ky + c0;
+		if (iy < 0 || iy >= h)
+			continue;
+		const uint32_t *row = in + (size_t)iy * w;
+		double hv[3] = { 0.0, 0.0, 0.0 };
+		bool first = true;
+		for (int kx = 0; kx < n; kx++) {
+			const int ix = x - kx + c0;
+			if (ix < 0 || ix >= w)
+				continue;
+			const uint32_t p = __ldg(row + ix);
+			const double t = tp.t[kx];
+			for (int c = 0; c < 3; c++) {
+				const double m = __dmul_rn(u8_to_double((p >> (8 * c)) & 0xFF), t);
+				hv[c] = first ? m : __dadd_rn(hv[c], m);
+			}
+			first = false;
+		}
+		const double tv = tp.t[ky];
+		for (int c = 0; c < 3; c++) {
+			const double m = __dmul_rn(hv[c], tv);
+			acc[c] = first_row ? m : __dadd_rn(acc[c], m);
+		}
+		first_row = false;
+	}
+	uint32_t rgba = 0xFF000000u;
+	for (int c = 0; c < 3; c++)
+		rgba |= (uint32_t)min(trunc_nonneg(acc[c]), 255) << (8 * c);
+	out[(size_t)y * w + x] = rgba;
+}
+
+int strips_for(int w_threads_blocks, int h, int pages, int blocks_per_sm, int min_rows)
+{
+	// about one full wave of blocks, but strips no shorter than min_rows
+	const long want = (long)sm_count() * blocks_per_sm;
+	long strips = want / ((long)w_threads_blocks * pages);
+	if (strips < 1)
+		strips = 1;
+	int rows = (int)((h + strips - 1) / strips);
+	if (rows < min_rows)
+		rows = min_rows;
+	return rows;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// launchers
+// ---------------------------------------------------------------------------
+
+template <int N>
+static void launch_gaussian_n(const uint32_t *in, uint32_t *out, int w, int h,
+		int pages, const Taps &taps, cudaStream_t st)
+{
+	TapsN<N> tp;
+	for (int k = 0; k < N; k++)
+		tp.t[k] = taps.t[k];
+	constexpr int PX = 2;
+	const int bx = ((w + PX - 1) / PX + kBlock - 1) / kBlock;
+	const int rows = strips_for(bx, h, pages, 4, 8 * N);
+	dim3 grid(bx, (h + rows - 1) / rows, pages);
+	gaussian_march_kernel<N, PX><<<grid, kBlock, 0, st>>>(in, out, w, h, rows, tp);
+}
+
+int launch_gaussian(const uint32_t *in, uint32_t *out, int w, int h, int pages,
+		const Taps &taps, cudaStream_t st)
+{
+	if (taps.n < 1 || taps.n > kMaxTaps)
+		return fail(PF_B200_EINVAL, "gaussian: nb_stddev must be in 1..%d", kMaxTaps);
+	switch (taps.n) {
+	case 3: launch_gaussian_n<3>(in, out, w, h, pages, taps, st); break;
+	case 5: launch_gaussian_n<5>(in, out, w, h, pages, taps, st); break;
+	case 7: launch_gaussian_n<7>(in, out, w, h, pages, taps, st); break;
+	case 9: launch_gaussian_n<9>(in, out, w, h, pages, taps, st); break;
+	default: {
+		dim3 grid((w + kBlock - 1) / kBlock, h, pages);
+		gaussian_generic_kernel<<<grid, kBlock, 0, st>>>(in, out, w, h, taps);
+	}
+	}
+	PFB_CUDA(cudaGetLastError());
+	return PF_B200_OK;
+}
+
+}  // namespace pfb

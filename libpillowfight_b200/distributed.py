@@ -122,7 +122,7 @@ class CudaChain:
 
     def canny(self, pages, out, pages_per_launch=1):
         n, h, w = pages.shape[0], pages.shape[1], pages.shape[2]
-        need = 256 + 4 * w * h * max(1, min(n, pages_per_launch))
+        need = 256 + 8 * w * h * max(1, min(n, pages_per_launch))
         if self._scratch is None or self._scratch.numel() < need \
                 or self._scratch.device != pages.device:
             self._scratch = torch.empty(need, dtype=torch.uint8, device=pages.device)
