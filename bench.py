@@ -246,9 +246,9 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    from libpillowfight_b200 import build as pf_build
+    from __graft_entry__ import load_build_module
     if rank == 0:
-        pf_build.build()
+        load_build_module().build()
     if world > 1:
         dist.barrier()
     import libpillowfight_b200 as pf

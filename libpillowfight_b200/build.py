@@ -1,6 +1,9 @@
 """Builds libpillowfight_b200.so in-tree with nvcc for sm_100a.
 
-    python -m libpillowfight_b200.build [--force] [--verbose]
+    python libpillowfight_b200/build.py [--force] [--verbose]
+
+(run it as a script, or load it by path as __graft_entry__.load_build_module
+does: importing the package binds the .so and refuses a missing or stale one)
 
 One shared library, CUDA runtime linked statically, no Python or torch
 dependency: the C-ABI in include/pillowfight_b200.h is all it exports.

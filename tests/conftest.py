@@ -23,7 +23,7 @@ def oracle():
 @pytest.fixture(scope="session")
 def pf():
     """The product package; builds libpillowfight_b200.so if it is stale."""
-    from libpillowfight_b200 import build
-    build.build()
+    from __graft_entry__ import load_build_module
+    load_build_module().build()
     import libpillowfight_b200
     return libpillowfight_b200
