@@ -155,6 +155,37 @@ int pf_b200_dev_canny(const uint32_t *d_in, uint32_t *d_out,
 		int width, int height, int nb_pages,
 		void *d_scratch, size_t scratch_bytes, void *stream);
 
+/* Canny for callers that must not allocate.  (No counterpart in the
+ * reference: it exists only because of how GPU memory is managed.)
+ *
+ * Some hosts cannot let a library call cudaMalloc on their behalf: a service
+ * that gave the whole GPU to its own memory pool when it started, so a later
+ * allocation would fail or eat into that pool; a latency-sensitive loop, where
+ * the device-wide synchronisation cudaMalloc/cudaFree imply would stall every
+ * stream; or a deployment that freezes its memory footprint after start-up.
+ * pf_b200_dev_canny already leaves the scratch to the caller; this variant
+ * needs no scratch argument at all.  The work list lives in an array compiled
+ * into the library (32 MiB + 256 B of HBM on every GPU that loads the library,
+ * held until the process exits), which bounds the page size:
+ *
+ *     width * height <= 4,194,304 pixels   (e.g. 2048 x 2048, or A4 at 200 dpi)
+ *
+ * Larger pages are refused with PF_B200_ETOOBIG and a message naming the
+ * limit.  One page per call; d_in / d_out / stream as for pf_b200_dev_canny.
+ * The call itself performs no cudaMalloc, cudaFree or other allocating call.
+ *
+ * The first call on each device looks up the array's device address (once
+ * per device, with that device current).  Make that first call during
+ * set-up, before any stream capture is started.
+ *
+ * Every call on a device shares the one array.  Each call clears the part
+ * that has to start at zero and overwrites the rest as it goes, so calls that
+ * run one after another (same stream, or ordered by events) are safe; two
+ * calls whose kernels can overlap on the GPU (different streams or host
+ * threads without ordering) race on the array and give wrong edges. */
+int pf_b200_dev_canny_noalloc(const uint32_t *d_in, uint32_t *d_out,
+		int width, int height, void *stream);
+
 /* Batched Gaussian / Sobel over nb_pages same-size pages stored back to back. */
 int pf_b200_dev_gaussian_batch(const uint32_t *d_in, uint32_t *d_out,
 		int width, int height, int nb_pages,

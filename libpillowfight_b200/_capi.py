@@ -2,7 +2,7 @@
 
 The shared library is the product; this file only declares its C-ABI to
 Python.  There is no fallback of any kind: if the library has not been built
-(python -m libpillowfight_b200.build) importing this module raises.
+(python libpillowfight_b200/build.py) importing this module raises.
 """
 import ctypes
 import os
@@ -35,7 +35,7 @@ class PfBitmap(ctypes.Structure):
 if not os.path.exists(SO_PATH):
     raise ImportError(
         "libpillowfight_b200.so is not built (expected at %s). Build it with "
-        "`python -m libpillowfight_b200.build`; there is no CPU fallback." % SO_PATH)
+        "`python libpillowfight_b200/build.py`; there is no CPU fallback." % SO_PATH)
 
 lib = ctypes.CDLL(SO_PATH)
 
@@ -70,6 +70,7 @@ SIGNATURES = {
     "pf_b200_canny_scratch_bytes": (ctypes.c_size_t, [ctypes.c_int, ctypes.c_int]),
     "pf_b200_dev_canny": (ctypes.c_int, [_u32p, _u32p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                          _vp, ctypes.c_size_t, _vp]),
+    "pf_b200_dev_canny_noalloc": (ctypes.c_int, [_u32p, _u32p, ctypes.c_int, ctypes.c_int, _vp]),
     "pf_b200_dev_gaussian_batch": (ctypes.c_int, [_u32p, _u32p, ctypes.c_int, ctypes.c_int,
                                                   ctypes.c_int, ctypes.c_double, ctypes.c_int, _vp]),
     "pf_b200_dev_sobel_batch": (ctypes.c_int, [_u32p, _u32p, ctypes.c_int, ctypes.c_int,

@@ -32,7 +32,7 @@ int fail(int code, const char *fmt, ...)
 	return code;
 }
 
-static void clear_error()
+void clear_error()
 {
 	t_err = PF_B200_OK;
 	t_msg[0] = '\0';
@@ -263,7 +263,7 @@ static int threshold_to_sq(double thr)
 	return (int)m;
 }
 
-static CannyThresholds canny_thresholds()
+CannyThresholds canny_thresholds()
 {
 	CannyThresholds t;
 	t.weak_min = threshold_to_sq(0.686 * 255.0);

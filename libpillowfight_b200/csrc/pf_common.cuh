@@ -16,6 +16,7 @@ int sm_count();
 
 // Records an error for the calling thread (pf_b200_last_error) and returns code.
 int fail(int code, const char *fmt, ...);
+void clear_error();
 
 #define PFB_CUDA(call)                                                        \
 	do {                                                                      \
@@ -42,6 +43,7 @@ struct CannyThresholds {
 	int weak_min;    // smallest g_x^2+g_y^2 whose hypot is  > LOW
 	int strong_min;  // smallest g_x^2+g_y^2 whose hypot is  > HIGH
 };
+CannyThresholds canny_thresholds();   // upstream _canny.c LOW / HIGH as integer tests
 size_t canny_scratch_bytes(int w, int h);
 int launch_canny(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 		CannyThresholds thr, void *scratch, size_t scratch_bytes,

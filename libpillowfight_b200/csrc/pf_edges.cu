@@ -13,6 +13,8 @@
 // whose values only feed their neighbours through shuffles, so a warp emits
 // 120 columns.  The vertical window lives in registers, rotated by unrolling
 // the row loop by 3.  Per stage a pixel is read once and written once.
+#include <mutex>
+
 #include "pf_common.cuh"
 
 namespace pfb {
@@ -501,3 +503,73 @@ int launch_canny(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 }
 
 }  // namespace pfb
+
+// ---------------------------------------------------------------------------
+// Canny without any allocation: the work list lives in a fixed device array.
+// ---------------------------------------------------------------------------
+
+namespace pfb {
+
+namespace {
+
+constexpr size_t kStaticMaxPixels = (size_t)4 << 20;       // 4,194,304 pixels per page
+constexpr size_t kStaticScratchBytes = 256 + 2 * sizeof(int) * kStaticMaxPixels;   // 32 MiB + 256 B
+constexpr int kStaticMaxDevices = 64;
+
+// One copy per GPU that loads this library, held until the process exits.
+// In host code this name is only a handle for cudaGetSymbolAddress; it is not
+// a device address and must never be handed to a kernel as it stands.
+static __device__ __align__(256) unsigned char g_canny_static_scratch[kStaticScratchBytes];
+
+std::mutex g_static_mutex;
+void *g_static_addr[kStaticMaxDevices] = {};   // device address of the array, per device
+
+// Looks the array's address up once per device, with that device current.
+int static_scratch_for_current_device(void **addr)
+{
+	int dev = -1;
+	PFB_CUDA(cudaGetDevice(&dev));
+	if (dev < 0 || dev >= kStaticMaxDevices)
+		return fail(PF_B200_EINVAL, "canny (no-alloc): device index %d outside 0..%d",
+				dev, kStaticMaxDevices - 1);
+	std::lock_guard<std::mutex> lock(g_static_mutex);
+	if (g_static_addr[dev] == nullptr) {
+		void *p = nullptr;
+		PFB_CUDA(cudaGetSymbolAddress(&p, g_canny_static_scratch));
+		g_static_addr[dev] = p;
+	}
+	*addr = g_static_addr[dev];
+	return PF_B200_OK;
+}
+
+}  // namespace
+
+}  // namespace pfb
+
+// See include/pillowfight_b200.h for the contract of this entry point.
+extern "C" int pf_b200_dev_canny_noalloc(const uint32_t *d_in, uint32_t *d_out,
+		int width, int height, void *stream)
+{
+	using namespace pfb;
+	clear_error();
+	if (!d_in || !d_out)
+		return fail(PF_B200_EINVAL, "NULL device pointer");
+	if (d_in == d_out)
+		return fail(PF_B200_EINVAL, "device entry points do not run in place");
+	if (width <= 0 || height <= 0)
+		return fail(PF_B200_EINVAL, "size %d x %d", width, height);
+	if ((size_t)width * (size_t)height > kStaticMaxPixels)
+		return fail(PF_B200_ETOOBIG,
+				"canny (no-alloc): %d x %d = %zu pixels, the built-in scratch holds at most %zu; "
+				"use pf_b200_dev_canny with caller-provided scratch for larger pages",
+				width, height, (size_t)width * (size_t)height, kStaticMaxPixels);
+	void *scratch = nullptr;
+	const int rc = static_scratch_for_current_device(&scratch);
+	if (rc)
+		return rc;
+	// launch_canny zeroes the 256-byte header (the work-list length) on the
+	// stream before the first kernel; list and parent slots are written before
+	// they are read, so whatever the previous call left behind is harmless.
+	return launch_canny(d_in, d_out, width, height, 1, canny_thresholds(),
+			scratch, kStaticScratchBytes, static_cast<cudaStream_t>(stream));
+}
