@@ -29,6 +29,7 @@ def nvcc_command(verbose=False):
            "-cudart", "static", "-shared", "-o", SO]
     if verbose:
         cmd += ["-Xptxas", "-v"]
+    cmd += os.environ.get("PF_B200_NVCC_EXTRA", "").split()     # experiments, e.g. -DPF_ACE_INPLACE=1
     cmd += [os.path.join(CSRC, s) for s in SOURCES]
     return cmd
 

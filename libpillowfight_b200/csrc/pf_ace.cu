@@ -21,6 +21,7 @@
 // whole tile are dropped per tile, those that cannot reach it skip the test.
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 
 #include "pf_common.cuh"
 
@@ -29,8 +30,7 @@ namespace pfb {
 namespace {
 
 constexpr int kAceBlock = 128;      // threads = columns per block
-constexpr int kRowsPerThread = 4;   // P: pixels a thread carries (same column)
-constexpr int kTileRows = 16;       // rows a block walks (4 row groups)
+constexpr int kMaxRowsPerThread = 8; // P: pixels a thread carries (same column), 2 / 4 / 8
 constexpr int kChunk = 512;         // samples staged in shared memory at a time
 constexpr double kBias = 4224.0;    // 4096 + 128: value spliced around c
 
@@ -41,7 +41,7 @@ struct SampleEntry {
 
 struct AceShared {
 	SampleEntry tbl[kChunk];                    // reordered: far samples, then straddling
-	double dy2[kChunk][kRowsPerThread];
+	double dy2[kChunk * kMaxRowsPerThread];     // [sample][row of the group], stride P
 	int sy[kChunk];
 	double lut[511];                            // general path only
 	int n_far, n_str;
@@ -54,7 +54,8 @@ __device__ __forceinline__ double rsqrt_approx(double x)
 	return y;
 }
 
-// 2/sqrt(d2) to ~2^-43 (NEWTON) or ~2^-22 relative; the factor 2 cancels.
+// 2/sqrt(d2) to ~2^-43 (NEWTON) or 1/sqrt(d2) to ~2^-22 relative; a common
+// factor on the weights cancels in the score.
 template <bool NEWTON>
 __device__ __forceinline__ double weight_of(double d2)
 {
@@ -70,13 +71,6 @@ __device__ __forceinline__ uint32_t umin16x2(uint32_t a, uint32_t b)
 {
 	uint32_t d;
 	asm("min.u16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
-	return d;
-}
-
-__device__ __forceinline__ uint32_t umax16x2(uint32_t a, uint32_t b)
-{
-	uint32_t d;
-	asm("max.u16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
 	return d;
 }
 
@@ -112,6 +106,7 @@ struct AceConst {
 	int nb_samples;
 	int too_close2;        // (h/5)^2: pairs with d^2 below this are skipped
 	int clamp_l;           // L = limit/slope when it is an integer <= 127 (fast path)
+	int tile_rows;         // rows a block walks; tiles sit on a page-wide grid of this pitch
 	double ratio;          // slope / limit
 	double slope, limit;
 };
@@ -206,20 +201,19 @@ __device__ __noinline__ void stage_samples(AceShared &sh, const AceConst &cs,
 
 // One sample against the P pixels of a thread.  TEST: the sample straddles the
 // skip circle on this tile, so each pair is tested (weight forced to 0).
-template <bool FAST, bool NEWTON, bool TEST>
+template <bool FAST, bool NEWTON, bool TEST, int P>
 __device__ __forceinline__ void accumulate_sample(const AceShared &sh, int j, int x,
-		const uint32_t (&pix)[kRowsPerThread], const uint32_t (&pk)[kRowsPerThread / 2][3],
+		const uint32_t (&pix)[P], const uint32_t (&pk)[P / 2][3],
 		uint32_t lo2, uint32_t hi2, double too_close2, double top_value,
-		double (&acc)[kRowsPerThread][3], double (&top)[kRowsPerThread])
+		double (&acc)[P][3], double (&top)[P])
 {
-	constexpr int P = kRowsPerThread;
 	const SampleEntry se = sh.tbl[j];
 	const int dx = x - se.sx;
 	const double dx2 = (double)(dx * dx);
 	double wgt[P];
 #pragma unroll
 	for (int r = 0; r < P; r++) {
-		const double d2 = dx2 + sh.dy2[j][r];
+		const double d2 = dx2 + sh.dy2[j * P + r];
 		double wv = weight_of<NEWTON>(d2);
 		if (TEST && d2 < too_close2)
 			wv = 0.0;
@@ -233,8 +227,8 @@ __device__ __forceinline__ void accumulate_sample(const AceShared &sh, int j, in
 		for (int g = 0; g < P / 2; g++) {
 #pragma unroll
 			for (int c = 0; c < 3; c++) {
-				uint32_t t = pk[g][c] + se.bias[c];
-				t = umin16x2(umax16x2(t, lo2), hi2);
+				// clamp(p - s) for two pixels: one fused add+max (VIADDMNMX), one min
+				const uint32_t t = umin16x2(__viaddmax_u16x2(pk[g][c], se.bias[c], lo2), hi2);
 				const double va = __hiloint2double(
 						(int)__byte_perm(t, 0x40B00000u, 0x7604), 0);
 				const double vb = __hiloint2double(
@@ -258,21 +252,22 @@ __device__ __forceinline__ void accumulate_sample(const AceShared &sh, int j, in
 // The accumulation pass.  Thread = one column, kRowsPerThread rows at a time.
 // FAST: L = limit/slope is an integer <= 127, clamp on the integer pipe.
 // !FAST: any slope/limit, saturation values read from a 511-entry table.
-template <bool FAST, bool NEWTON>
-__global__ void __launch_bounds__(kAceBlock, 6)
+#ifndef PF_ACE_MINBLOCKS_P8
+#define PF_ACE_MINBLOCKS_P8 3
+#endif
+template <bool FAST, bool NEWTON, int P>
+__global__ void __launch_bounds__(kAceBlock, (P == 2) ? 8 : ((P == 4) ? 6 : PF_ACE_MINBLOCKS_P8))
 ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
 		const AceConst cs, double *__restrict__ scores, double *__restrict__ minmax)
 {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	AceShared &sh = *reinterpret_cast<AceShared *>(smem_raw);
-	constexpr int P = kRowsPerThread;
-
 	const int x = blockIdx.x * kAceBlock + threadIdx.x;
 	const int xc = min(x, cs.w - 1);
-	// Tiles sit on a page-wide grid of kTileRows rows whatever the band is, so
+	// Tiles sit on a page-wide grid of tile_rows rows whatever the band is, so
 	// a band split (multi-GPU) classifies and sums exactly like the whole page.
-	const int tile_y0 = (cs.row_begin / kTileRows + blockIdx.y) * kTileRows;
-	const int tile_y1 = min(cs.h, tile_y0 + kTileRows);         // exclusive
+	const int tile_y0 = (cs.row_begin / cs.tile_rows + blockIdx.y) * cs.tile_rows;
+	const int tile_y1 = min(cs.h, tile_y0 + cs.tile_rows);      // exclusive
 	const int x_lo = blockIdx.x * kAceBlock;
 	const int x_hi = min(cs.w - 1, x_lo + kAceBlock - 1);
 	const int band_rows = cs.row_end - cs.row_begin;
@@ -341,17 +336,17 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 #pragma unroll
 				for (int r = 0; r < P; r++) {
 					const int dy = y0 + r - sh.sy[j];
-					sh.dy2[j][r] = (double)(dy * dy);
+					sh.dy2[j * P + r] = (double)(dy * dy);
 				}
 			}
 			__syncthreads();
 
 			const int n_far = sh.n_far;
 			for (int j = 0; j < n_far; j++)
-				accumulate_sample<FAST, NEWTON, false>(sh, j, x, pix, pk, lo2, hi2,
+				accumulate_sample<FAST, NEWTON, false, P>(sh, j, x, pix, pk, lo2, hi2,
 						too_close2, top_value, acc, top);
 			for (int j = n_far; j < n_act; j++)
-				accumulate_sample<FAST, NEWTON, true>(sh, j, x, pix, pk, lo2, hi2,
+				accumulate_sample<FAST, NEWTON, true, P>(sh, j, x, pix, pk, lo2, hi2,
 						too_close2, top_value, acc, top);
 		}
 
@@ -496,18 +491,32 @@ int launch_ace_scores(const uint32_t *in, const int *samples_xy,
 	const bool fast = l >= 1.0 && l <= 127.0 && l == floor(l) && p.slope * l == p.limit;
 	cs.clamp_l = fast ? (int)l : 0;
 
+	static const int tile_env = getenv("PF_B200_ACE_TILE_ROWS") ? atoi(getenv("PF_B200_ACE_TILE_ROWS")) : 16;
+	cs.tile_rows = (tile_env >= 8 && tile_env % 8 == 0) ? tile_env : 16;
 	dim3 grid((p.w + kAceBlock - 1) / kAceBlock,
-			(p.row_end - 1) / kTileRows - p.row_begin / kTileRows + 1);
+			(p.row_end - 1) / cs.tile_rows - p.row_begin / cs.tile_rows + 1);
 	const size_t smem = sizeof(AceShared);
-	if (fast) {
-		auto kern = ace_scores_kernel<true, true>;
-		PFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-		kern<<<grid, kAceBlock, smem, st>>>(in, samples_xy, cs, scores, minmax);
-	} else {
-		auto kern = ace_scores_kernel<false, true>;
-		PFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-		kern<<<grid, kAceBlock, smem, st>>>(in, samples_xy, cs, scores, minmax);
-	}
+	// Knobs (read once per process; tools/ace_time.py sweeps them).  Defaults
+	// are the measured best on B200 (profiles/README.md):
+	//   PF_B200_ACE_ROWS = 2 | 4 | 8   pixels per thread (default 8)
+	//   PF_B200_ACE_NEWTON = 1         one Newton step on MUFU.RSQ64H's 1/dist:
+	//       weights good to ~2^-43 instead of ~2^-22.  Off by default: both
+	//       settings sit three orders of magnitude inside the +-1 LSB / 0.1 %
+	//       bar (1.1e-4 % vs 3e-5 % of channel values differ on the test page)
+	//       and the step costs 3 of 8 FP64 instructions per pair.
+	static const int rows_env = getenv("PF_B200_ACE_ROWS") ? atoi(getenv("PF_B200_ACE_ROWS")) : 8;
+	static const int newton_env = getenv("PF_B200_ACE_NEWTON") ? atoi(getenv("PF_B200_ACE_NEWTON")) : 0;
+	void (*kern)(const uint32_t *, const int *, const AceConst, double *, double *) = nullptr;
+	if (!fast)
+		kern = ace_scores_kernel<false, true, 4>;
+	else if (newton_env)
+		kern = rows_env == 2 ? ace_scores_kernel<true, true, 2>
+			: rows_env == 8 ? ace_scores_kernel<true, true, 8> : ace_scores_kernel<true, true, 4>;
+	else
+		kern = rows_env == 2 ? ace_scores_kernel<true, false, 2>
+			: rows_env == 8 ? ace_scores_kernel<true, false, 8> : ace_scores_kernel<true, false, 4>;
+	PFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	kern<<<grid, kAceBlock, smem, st>>>(in, samples_xy, cs, scores, minmax);
 	PFB_CUDA(cudaGetLastError());
 	return PF_B200_OK;
 }

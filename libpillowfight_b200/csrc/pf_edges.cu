@@ -109,24 +109,119 @@ __device__ __forceinline__ uint32_t isqrt_cap255(int m)
 }
 
 // ---------------------------------------------------------------------------
+// Row access for the march.  FAST: the warp's 128 columns lie inside the page
+// and rows are 16-byte aligned, so a row is one LDG.128 / STG.128 through a
+// pointer that advances by the row pitch; only the row index needs a (warp-
+// uniform) test at the top and bottom of the page.  !FAST: page-edge warps and
+// odd widths, every pixel bounds-checked.
+// ---------------------------------------------------------------------------
+
+template <bool FAST>
+struct RowReader {
+	const uint32_t *img;      // page base (generic path)
+	const uint4 *p;           // (row, x0) of the next row to load (fast path)
+	int pitch4;               // row pitch in uint4
+	int r;                    // index of the next row to load
+	int x0;
+
+	__device__ __forceinline__ void init(const uint32_t *page, const StripGeom &g, int first_row, int x0_)
+	{
+		img = page;
+		x0 = x0_;
+		r = first_row;
+		pitch4 = g.w >> 2;
+		p = reinterpret_cast<const uint4 *>(page + (long)first_row * g.w + x0_);
+	}
+	__device__ __forceinline__ uint4 next(const StripGeom &g)
+	{
+		uint4 v;
+		if (FAST) {
+			v = make_uint4(0u, 0u, 0u, 0u);
+			if (r >= 0 && r < g.h)
+				v = __ldg(p);
+			p += pitch4;
+		} else {
+			v = load_px4(img, g, r, x0);
+		}
+		r++;
+		return v;
+	}
+};
+
+template <bool FAST>
+struct RowWriter {
+	uint32_t *img;
+	uint4 *p;                 // (row, x0) of the next row to store (fast path)
+	int pitch4;
+	int r;
+	int x0;
+
+	__device__ __forceinline__ void init(uint32_t *page, const StripGeom &g, int first_row, int x0_)
+	{
+		img = page;
+		x0 = x0_;
+		r = first_row;
+		pitch4 = g.w >> 2;
+		p = reinterpret_cast<uint4 *>(page + (long)first_row * g.w + x0_);
+	}
+	// stores row r for the lanes that own output columns, then moves down a row
+	__device__ __forceinline__ void put(const StripGeom &g, bool out_lane, const uint32_t (&v)[4])
+	{
+		if (FAST) {
+			if (out_lane)
+				*p = make_uint4(v[0], v[1], v[2], v[3]);
+			p += pitch4;
+		} else if (out_lane && x0 < g.w) {
+			store_px4(img, g, r, x0, v);
+		}
+		r++;
+	}
+};
+
+struct WarpPlace {
+	int x0;           // first column of this lane (may be -4 for a halo lane)
+	int ys, ye;       // output rows of the strip
+	bool out_lane;    // lanes 1..30
+	bool interior;    // all 128 columns inside the page
+	bool valid;
+};
+
+__device__ __forceinline__ WarpPlace place_warp(const StripGeom &g)
+{
+	WarpPlace wp;
+	const int gw = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+	const int strip = gw / g.warp_cols;
+	const int lane = threadIdx.x & 31;
+	const int wx = (gw - strip * g.warp_cols) * kWarpCols - 4;
+	wp.valid = strip < g.strips;
+	wp.x0 = wx + lane * 4;
+	wp.out_lane = lane >= 1 && lane <= kOutLanes;
+	wp.interior = g.aligned && wx >= 0 && wx + 128 <= g.w;
+	wp.ys = strip * g.rows_per_strip;
+	wp.ye = min(g.h, wp.ys + g.rows_per_strip);
+	return wp;
+}
+
+// ---------------------------------------------------------------------------
 // Sobel
 // ---------------------------------------------------------------------------
 
-// rows r-2, r-1, r of the horizontal terms sit in slots (J+1)%3, (J+2)%3, J
-template <int J>
-__device__ __forceinline__ void sobel_step(const uint32_t *__restrict__ in,
-		uint32_t *__restrict__ out, const StripGeom &g, int r, int r_last,
-		int x0, bool out_lane, int ys, uint4 &nxt, HRow (&hr)[3])
+// Step J of 6: gray row r arrives in pixel buffer J&1 (loaded one step
+// earlier), the next row's load is issued into the other buffer, and output
+// row r-1 leaves.  Horizontal terms of rows r-2, r-1, r sit in hr slots
+// (J+1)%3, (J+2)%3, J%3.
+template <bool FAST, int J>
+__device__ __forceinline__ void sobel_step(const StripGeom &g, int r, int r_last,
+		const WarpPlace &wp, RowReader<FAST> &rd, RowWriter<FAST> &wr,
+		uint4 (&buf)[2], HRow (&hr)[3])
 {
 	if (r > r_last)
 		return;
-	const uint4 cur = nxt;
-	nxt = load_px4(in, g, r + 1, x0);            // in flight during this row's math
-	hrow_from_pixels(cur, hr[J]);
-	const int y = r - 1;
-	if (y < ys || !out_lane || x0 >= g.w)
+	buf[(J + 1) & 1] = rd.next(g);            // in flight during this row's math
+	hrow_from_pixels(buf[J & 1], hr[J % 3]);
+	if (r - 1 < wp.ys)
 		return;
-	const HRow &a = hr[(J + 1) % 3], &b = hr[(J + 2) % 3], &c = hr[J];
+	const HRow &a = hr[(J + 1) % 3], &b = hr[(J + 2) % 3], &c = hr[J % 3];
 	uint32_t res[4];
 #pragma unroll
 	for (int i = 0; i < 4; i++) {
@@ -134,35 +229,44 @@ __device__ __forceinline__ void sobel_step(const uint32_t *__restrict__ in,
 		const int gy = a.hs[i] - c.hs[i];
 		res[i] = kBlack + isqrt_cap255(gx * gx + gy * gy) * 0x010101u;
 	}
-	store_px4(out, g, y, x0, res);
+	wr.put(g, wp.out_lane, res);
+}
+
+template <bool FAST>
+__device__ __forceinline__ void sobel_march(const uint32_t *__restrict__ in,
+		uint32_t *__restrict__ out, const StripGeom &g, const WarpPlace &wp)
+{
+	RowReader<FAST> rd;
+	RowWriter<FAST> wr;
+	rd.init(in, g, wp.ys - 1, wp.x0);
+	wr.init(out, g, wp.ys, wp.x0);
+	HRow hr[3];
+	uint4 buf[2];
+	buf[0] = rd.next(g);
+	// gray rows ys-1 .. ye; row r yields output row r-1
+	const int r_last = wp.ye;
+	for (int r = wp.ys - 1; r <= r_last; r += 6) {
+		sobel_step<FAST, 0>(g, r, r_last, wp, rd, wr, buf, hr);
+		sobel_step<FAST, 1>(g, r + 1, r_last, wp, rd, wr, buf, hr);
+		sobel_step<FAST, 2>(g, r + 2, r_last, wp, rd, wr, buf, hr);
+		sobel_step<FAST, 3>(g, r + 3, r_last, wp, rd, wr, buf, hr);
+		sobel_step<FAST, 4>(g, r + 4, r_last, wp, rd, wr, buf, hr);
+		sobel_step<FAST, 5>(g, r + 5, r_last, wp, rd, wr, buf, hr);
+	}
 }
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 sobel_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
 		const StripGeom g)
 {
-	const int gw = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
-	const int strip = gw / g.warp_cols;
-	if (strip >= g.strips)
+	const WarpPlace wp = place_warp(g);
+	if (!wp.valid)
 		return;
-	const int lane = threadIdx.x & 31;
-	const int x0 = (gw - strip * g.warp_cols) * kWarpCols - 4 + lane * 4;
-	const bool out_lane = lane >= 1 && lane <= kOutLanes;
 	const size_t page = (size_t)blockIdx.y * g.w * g.h;
-	in += page;
-	out += page;
-	const int ys = strip * g.rows_per_strip;
-	const int ye = min(g.h, ys + g.rows_per_strip);
-
-	HRow hr[3];
-	uint4 nxt = load_px4(in, g, ys - 1, x0);
-	// gray rows ys-1 .. ye; row r yields output row r-1
-	const int r_last = ye;
-	for (int r = ys - 1; r <= r_last; r += 3) {
-		sobel_step<0>(in, out, g, r, r_last, x0, out_lane, ys, nxt, hr);
-		sobel_step<1>(in, out, g, r + 1, r_last, x0, out_lane, ys, nxt, hr);
-		sobel_step<2>(in, out, g, r + 2, r_last, x0, out_lane, ys, nxt, hr);
-	}
+	if (wp.interior)
+		sobel_march<true>(in + page, out + page, g, wp);
+	else
+		sobel_march<false>(in + page, out + page, g, wp);
 }
 
 // ---------------------------------------------------------------------------
@@ -175,6 +279,7 @@ struct GRow {
 	int sector[4];     // 0: E-W, 1: SE-NW, 2: N-S, 3: SW-NE neighbours
 };
 
+template <bool FAST>
 __device__ __forceinline__ void grow_from_hrows(const HRow &a, const HRow &b,
 		const HRow &c, bool row_inside, int x0, int w, GRow &o)
 {
@@ -184,7 +289,8 @@ __device__ __forceinline__ void grow_from_hrows(const HRow &a, const HRow &b,
 		const int gy = a.hs[i] - c.hs[i];
 		const int gx2 = gx * gx, gy2 = gy * gy;
 		const int x = x0 + i;
-		o.m[i + 1] = (row_inside && x >= 0 && x < w) ? gx2 + gy2 : 0;
+		const bool inside = FAST ? row_inside : (row_inside && x >= 0 && x < w);
+		o.m[i + 1] = inside ? gx2 + gy2 : 0;
 		// |angle| < 22.5 deg  <=>  (|gx|+|gy|)^2 < 2 gx^2  <=>  2|gx gy| < gx^2 - gy^2
 		const int q = gx * gy;
 		const int p2 = 2 * abs(q);
@@ -195,28 +301,34 @@ __device__ __forceinline__ void grow_from_hrows(const HRow &a, const HRow &b,
 	o.m[5] = __shfl_down_sync(kFull, o.m[1], 1);
 }
 
-template <int J>
-__device__ __forceinline__ void canny_step(const uint32_t *__restrict__ in,
-		uint32_t *__restrict__ out, const StripGeom &g, int r, int r_last,
-		int x0, bool out_lane, int ys, int page_base, CannyThresholds thr,
-		int *__restrict__ hdr, int *__restrict__ list, int *__restrict__ parent,
-		uint4 &nxt, HRow (&hr)[3], GRow (&gr)[3])
+struct WeakSink {
+	int *hdr, *list, *parent;
+	int page_base;
+};
+
+// Step J of 6: gray row r arrives; gradient row r-1 is formed (slot J%3, from
+// horizontal rows r-2, r-1, r); output row r-2 is classified from gradient
+// rows r-3, r-2, r-1.
+template <bool FAST, int J>
+__device__ __forceinline__ void canny_step(const StripGeom &g, int r, int r_last,
+		const WarpPlace &wp, CannyThresholds thr, const WeakSink &ws,
+		RowReader<FAST> &rd, RowWriter<FAST> &wr,
+		uint4 (&buf)[2], HRow (&hr)[3], GRow (&gr)[3])
 {
 	if (r > r_last)
 		return;
-	const uint4 cur = nxt;
-	nxt = load_px4(in, g, r + 1, x0);
-	hrow_from_pixels(cur, hr[J]);
-	if (r < ys)
+	buf[(J + 1) & 1] = rd.next(g);
+	hrow_from_pixels(buf[J & 1], hr[J % 3]);
+	if (r < wp.ys)
 		return;                  // gray rows r-2, r-1, r are needed
-	// gradient row r-1 goes to the slot of gray row r
 	const int grow = r - 1;
-	grow_from_hrows(hr[(J + 1) % 3], hr[(J + 2) % 3], hr[J],
-			grow >= 0 && grow < g.h, x0, g.w, gr[J]);
+	grow_from_hrows<FAST>(hr[(J + 1) % 3], hr[(J + 2) % 3], hr[J % 3],
+			grow >= 0 && grow < g.h, wp.x0, g.w, gr[J % 3]);
 	const int y = r - 2;
-	if (y < ys)
+	if (y < wp.ys)
 		return;                  // gradient rows y-1, y, y+1 are needed
-	const GRow &up = gr[(J + 1) % 3], &mid = gr[(J + 2) % 3], &dn = gr[J];
+	const GRow &up = gr[(J + 1) % 3], &mid = gr[(J + 2) % 3], &dn = gr[J % 3];
+	const bool owns = wp.out_lane && (FAST || wp.x0 < g.w);
 	uint32_t res[4];
 	int nweak = 0;
 #pragma unroll
@@ -231,7 +343,7 @@ __device__ __forceinline__ void canny_step(const uint32_t *__restrict__ in,
 		uint32_t v = kBlack;
 		if (m >= nb && m >= thr.weak_min) {
 			v = kWhite;
-			if (m < thr.strong_min && out_lane && x0 + i < g.w) {
+			if (m < thr.strong_min && owns && (FAST || wp.x0 + i < g.w)) {
 				v = 0u;          // weak: index filled in below
 				nweak++;
 			}
@@ -239,8 +351,7 @@ __device__ __forceinline__ void canny_step(const uint32_t *__restrict__ in,
 		res[i] = v;
 	}
 	// warp-aggregated append of this row's weak pixels to the work list
-	const unsigned any = __ballot_sync(kFull, nweak > 0);
-	if (any) {
+	if (__ballot_sync(kFull, nweak > 0)) {
 		const int lane = threadIdx.x & 31;
 		int pre = nweak;
 #pragma unroll
@@ -251,23 +362,47 @@ __device__ __forceinline__ void canny_step(const uint32_t *__restrict__ in,
 		}
 		int base = 0;
 		if (lane == 31)
-			base = atomicAdd(&hdr[0], pre);
+			base = atomicAdd(&ws.hdr[0], pre);
 		base = __shfl_sync(kFull, base, 31) + pre - nweak;
 		if (nweak > 0) {
-			const int pix0 = page_base + y * g.w + x0;
+			const int pix0 = ws.page_base + y * g.w + wp.x0;
 #pragma unroll
 			for (int i = 0; i < 4; i++) {
 				if (res[i] == 0u) {
 					res[i] = (uint32_t)base;
-					list[base] = pix0 + i;
-					parent[base] = base;
+					ws.list[base] = pix0 + i;
+					ws.parent[base] = base;
 					base++;
 				}
 			}
 		}
 	}
-	if (out_lane && x0 < g.w)
-		store_px4(out, g, y, x0, res);
+	wr.put(g, wp.out_lane, res);
+}
+
+template <bool FAST>
+__device__ __forceinline__ void canny_march(const uint32_t *__restrict__ in,
+		uint32_t *__restrict__ out, const StripGeom &g, const WarpPlace &wp,
+		CannyThresholds thr, const WeakSink &ws)
+{
+	RowReader<FAST> rd;
+	RowWriter<FAST> wr;
+	rd.init(in, g, wp.ys - 2, wp.x0);
+	wr.init(out, g, wp.ys, wp.x0);
+	HRow hr[3];
+	GRow gr[3];
+	uint4 buf[2];
+	buf[0] = rd.next(g);
+	// gray rows ys-2 .. ye+1; row r yields gradient row r-1 and output row r-2
+	const int r_last = wp.ye + 1;
+	for (int r = wp.ys - 2; r <= r_last; r += 6) {
+		canny_step<FAST, 0>(g, r, r_last, wp, thr, ws, rd, wr, buf, hr, gr);
+		canny_step<FAST, 1>(g, r + 1, r_last, wp, thr, ws, rd, wr, buf, hr, gr);
+		canny_step<FAST, 2>(g, r + 2, r_last, wp, thr, ws, rd, wr, buf, hr, gr);
+		canny_step<FAST, 3>(g, r + 3, r_last, wp, thr, ws, rd, wr, buf, hr, gr);
+		canny_step<FAST, 4>(g, r + 4, r_last, wp, thr, ws, rd, wr, buf, hr, gr);
+		canny_step<FAST, 5>(g, r + 5, r_last, wp, thr, ws, rd, wr, buf, hr, gr);
+	}
 }
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
@@ -275,32 +410,16 @@ canny_classify_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ ou
 		const StripGeom g, CannyThresholds thr,
 		int *__restrict__ hdr, int *__restrict__ list, int *__restrict__ parent)
 {
-	const int gw = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
-	const int strip = gw / g.warp_cols;
-	if (strip >= g.strips)
+	const WarpPlace wp = place_warp(g);
+	if (!wp.valid)
 		return;
-	const int lane = threadIdx.x & 31;
-	const int x0 = (gw - strip * g.warp_cols) * kWarpCols - 4 + lane * 4;
-	const bool out_lane = lane >= 1 && lane <= kOutLanes;
 	const int npix = g.w * g.h;
 	const size_t page = (size_t)blockIdx.y * npix;
-	in += page;
-	out += page;
-	const int ys = strip * g.rows_per_strip;
-	const int ye = min(g.h, ys + g.rows_per_strip);
-
-	HRow hr[3];
-	GRow gr[3];
-	uint4 nxt = load_px4(in, g, ys - 2, x0);
-	// gray rows ys-2 .. ye+1; row r yields gradient row r-1 and output row r-2
-	const int r_last = ye + 1;
-	const int page_base = (int)blockIdx.y * npix;
-	// start so that (r - start) % 3 == J matches the slot arithmetic above
-	for (int r = ys - 2; r <= r_last; r += 3) {
-		canny_step<0>(in, out, g, r, r_last, x0, out_lane, ys, page_base, thr, hdr, list, parent, nxt, hr, gr);
-		canny_step<1>(in, out, g, r + 1, r_last, x0, out_lane, ys, page_base, thr, hdr, list, parent, nxt, hr, gr);
-		canny_step<2>(in, out, g, r + 2, r_last, x0, out_lane, ys, page_base, thr, hdr, list, parent, nxt, hr, gr);
-	}
+	const WeakSink ws = { hdr, list, parent, (int)blockIdx.y * npix };
+	if (wp.interior)
+		canny_march<true>(in + page, out + page, g, wp, thr, ws);
+	else
+		canny_march<false>(in + page, out + page, g, wp, thr, ws);
 }
 
 // ---------------------------------------------------------------------------
