@@ -31,6 +31,10 @@ namespace {
 
 constexpr int kAceBlock = 128;      // threads = columns per block
 constexpr int kMaxRowsPerThread = 8; // P: pixels a thread carries (same column), 2 / 4 / 8
+#ifndef PF_ACE_UNROLL
+#define PF_ACE_UNROLL 2
+#endif
+constexpr int kAceUnroll = PF_ACE_UNROLL;   // unroll of the sample loop
 constexpr int kChunk = 512;         // samples staged in shared memory at a time
 constexpr double kBias = 4224.0;    // 4096 + 128: value spliced around c
 
@@ -342,6 +346,7 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 			__syncthreads();
 
 			const int n_far = sh.n_far;
+#pragma unroll kAceUnroll
 			for (int j = 0; j < n_far; j++)
 				accumulate_sample<FAST, NEWTON, false, P>(sh, j, x, pix, pk, lo2, hi2,
 						too_close2, top_value, acc, top);

@@ -13,6 +13,8 @@
 // whose values only feed their neighbours through shuffles, so a warp emits
 // 120 columns.  The vertical window lives in registers, rotated by unrolling
 // the row loop by 3.  Per stage a pixel is read once and written once.
+#include <cooperative_groups.h>
+
 #include <mutex>
 
 #include "pf_common.cuh"
@@ -98,14 +100,17 @@ __device__ __forceinline__ void hrow_from_pixels(const uint4 px, HRow &o)
 	}
 }
 
-// min(255, floor(sqrt(m))).  sqrt(m + 0.5) sits at least 1/(4*255) away from
-// every integer for m < 2^16, far more than MUFU.SQRT's error, so the
-// truncation is exact.
-__device__ __forceinline__ uint32_t isqrt_cap255(int m)
+// 0xFF000000 + v * 0x010101 with v = min(255, floor(sqrt(m))): the gray pixel.
+// sqrt(m + 0.5) sits at least 1/(4*255) away from every integer for m < 2^16,
+// far more than MUFU.SQRT's error, so truncating it is exact.  The truncation
+// is a round-toward-zero add of 2^23 (the integer lands in the low mantissa
+// bits), and one IMAD replicates it into R, G, B: the 0x4B exponent byte
+// times 0x010101 wraps to itself, the addend turns it into alpha 0xFF.
+__device__ __forceinline__ uint32_t gray_pixel_of_mag2(int m)
 {
 	float r;
 	asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"((float)min(m, 65535) + 0.5f));
-	return (uint32_t)min(__float2int_rz(r), 255);
+	return __float_as_uint(__fadd_rz(r, 8388608.0f)) * 0x010101u + 0xB4000000u;
 }
 
 // ---------------------------------------------------------------------------
@@ -164,14 +169,16 @@ struct RowWriter {
 		pitch4 = g.w >> 2;
 		p = reinterpret_cast<uint4 *>(page + (long)first_row * g.w + x0_);
 	}
-	// stores row r for the lanes that own output columns, then moves down a row
-	__device__ __forceinline__ void put(const StripGeom &g, bool out_lane, const uint32_t (&v)[4])
+	// stores row r for the lanes that own output columns (if the row belongs
+	// to the strip), then moves down a row
+	__device__ __forceinline__ void put(const StripGeom &g, bool out_lane, int row_end,
+			const uint32_t (&v)[4])
 	{
 		if (FAST) {
-			if (out_lane)
+			if (out_lane && r < row_end)
 				*p = make_uint4(v[0], v[1], v[2], v[3]);
 			p += pitch4;
-		} else if (out_lane && x0 < g.w) {
+		} else if (out_lane && r < row_end && x0 < g.w) {
 			store_px4(img, g, r, x0, v);
 		}
 		r++;
@@ -206,20 +213,19 @@ __device__ __forceinline__ WarpPlace place_warp(const StripGeom &g)
 // Sobel
 // ---------------------------------------------------------------------------
 
-// Step J of 6: gray row r arrives in pixel buffer J&1 (loaded one step
-// earlier), the next row's load is issued into the other buffer, and output
-// row r-1 leaves.  Horizontal terms of rows r-2, r-1, r sit in hr slots
-// (J+1)%3, (J+2)%3, J%3.
-template <bool FAST, int J>
-__device__ __forceinline__ void sobel_step(const StripGeom &g, int r, int r_last,
-		const WarpPlace &wp, RowReader<FAST> &rd, RowWriter<FAST> &wr,
-		uint4 (&buf)[2], HRow (&hr)[3])
+// Step J of 6: a gray row arrives in pixel buffer J&1 (loaded one step
+// earlier), the next row's load is issued into the other buffer, and the
+// output row above leaves.  Horizontal terms of the last three rows sit in hr
+// slots (J+1)%3, (J+2)%3, J%3.  The march runs whole groups of 6 steps (strip
+// heights are chosen for that), so nothing but the store is conditional; in
+// the FIRST group the first two steps only fill the window.
+template <bool FAST, bool FIRST, int J>
+__device__ __forceinline__ void sobel_step(const StripGeom &g, const WarpPlace &wp,
+		RowReader<FAST> &rd, RowWriter<FAST> &wr, uint4 (&buf)[2], HRow (&hr)[3])
 {
-	if (r > r_last)
-		return;
 	buf[(J + 1) & 1] = rd.next(g);            // in flight during this row's math
 	hrow_from_pixels(buf[J & 1], hr[J % 3]);
-	if (r - 1 < wp.ys)
+	if (FIRST && J < 2)
 		return;
 	const HRow &a = hr[(J + 1) % 3], &b = hr[(J + 2) % 3], &c = hr[J % 3];
 	uint32_t res[4];
@@ -227,9 +233,21 @@ __device__ __forceinline__ void sobel_step(const StripGeom &g, int r, int r_last
 	for (int i = 0; i < 4; i++) {
 		const int gx = c.hd[i] + 2 * b.hd[i] + a.hd[i];
 		const int gy = a.hs[i] - c.hs[i];
-		res[i] = kBlack + isqrt_cap255(gx * gx + gy * gy) * 0x010101u;
+		res[i] = gray_pixel_of_mag2(gx * gx + gy * gy);
 	}
-	wr.put(g, wp.out_lane, res);
+	wr.put(g, wp.out_lane, wp.ye, res);
+}
+
+template <bool FAST, bool FIRST>
+__device__ __forceinline__ void sobel_group(const StripGeom &g, const WarpPlace &wp,
+		RowReader<FAST> &rd, RowWriter<FAST> &wr, uint4 (&buf)[2], HRow (&hr)[3])
+{
+	sobel_step<FAST, FIRST, 0>(g, wp, rd, wr, buf, hr);
+	sobel_step<FAST, FIRST, 1>(g, wp, rd, wr, buf, hr);
+	sobel_step<FAST, FIRST, 2>(g, wp, rd, wr, buf, hr);
+	sobel_step<FAST, FIRST, 3>(g, wp, rd, wr, buf, hr);
+	sobel_step<FAST, FIRST, 4>(g, wp, rd, wr, buf, hr);
+	sobel_step<FAST, FIRST, 5>(g, wp, rd, wr, buf, hr);
 }
 
 template <bool FAST>
@@ -243,16 +261,11 @@ __device__ __forceinline__ void sobel_march(const uint32_t *__restrict__ in,
 	HRow hr[3];
 	uint4 buf[2];
 	buf[0] = rd.next(g);
-	// gray rows ys-1 .. ye; row r yields output row r-1
-	const int r_last = wp.ye;
-	for (int r = wp.ys - 1; r <= r_last; r += 6) {
-		sobel_step<FAST, 0>(g, r, r_last, wp, rd, wr, buf, hr);
-		sobel_step<FAST, 1>(g, r + 1, r_last, wp, rd, wr, buf, hr);
-		sobel_step<FAST, 2>(g, r + 2, r_last, wp, rd, wr, buf, hr);
-		sobel_step<FAST, 3>(g, r + 3, r_last, wp, rd, wr, buf, hr);
-		sobel_step<FAST, 4>(g, r + 4, r_last, wp, rd, wr, buf, hr);
-		sobel_step<FAST, 5>(g, r + 5, r_last, wp, rd, wr, buf, hr);
-	}
+	// gray rows ys-1 .. ys+rows_per_strip: rows_per_strip + 2 steps, a multiple of 6
+	const int groups = (g.rows_per_strip + 2) / 6;
+	sobel_group<FAST, true>(g, wp, rd, wr, buf, hr);
+	for (int k = 1; k < groups; k++)
+		sobel_group<FAST, false>(g, wp, rd, wr, buf, hr);
 }
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
@@ -307,28 +320,27 @@ struct WeakSink {
 };
 
 // Step J of 6: gray row r arrives; gradient row r-1 is formed (slot J%3, from
-// horizontal rows r-2, r-1, r); output row r-2 is classified from gradient
-// rows r-3, r-2, r-1.
-template <bool FAST, int J>
-__device__ __forceinline__ void canny_step(const StripGeom &g, int r, int r_last,
-		const WarpPlace &wp, CannyThresholds thr, const WeakSink &ws,
-		RowReader<FAST> &rd, RowWriter<FAST> &wr,
+// horizontal rows r-2, r-1, r); output row y = r-2 is classified from gradient
+// rows r-3, r-2, r-1.  Whole groups of 6 steps, as for Sobel; in the FIRST
+// group steps 0-1 only fill the gray window and steps 2-3 the gradient window.
+template <bool FAST, bool FIRST, int J>
+__device__ __forceinline__ void canny_step(const StripGeom &g, const WarpPlace &wp,
+		CannyThresholds thr, const WeakSink &ws, RowReader<FAST> &rd, RowWriter<FAST> &wr,
 		uint4 (&buf)[2], HRow (&hr)[3], GRow (&gr)[3])
 {
-	if (r > r_last)
-		return;
+	const int r = rd.r - 1;      // the row sitting in buf[J & 1]
 	buf[(J + 1) & 1] = rd.next(g);
 	hrow_from_pixels(buf[J & 1], hr[J % 3]);
-	if (r < wp.ys)
-		return;                  // gray rows r-2, r-1, r are needed
+	if (FIRST && J < 2)
+		return;
 	const int grow = r - 1;
 	grow_from_hrows<FAST>(hr[(J + 1) % 3], hr[(J + 2) % 3], hr[J % 3],
 			grow >= 0 && grow < g.h, wp.x0, g.w, gr[J % 3]);
+	if (FIRST && J < 4)
+		return;
 	const int y = r - 2;
-	if (y < wp.ys)
-		return;                  // gradient rows y-1, y, y+1 are needed
 	const GRow &up = gr[(J + 1) % 3], &mid = gr[(J + 2) % 3], &dn = gr[J % 3];
-	const bool owns = wp.out_lane && (FAST || wp.x0 < g.w);
+	const bool owns = wp.out_lane && y < wp.ye && (FAST || wp.x0 < g.w);
 	uint32_t res[4];
 	int nweak = 0;
 #pragma unroll
@@ -377,7 +389,20 @@ __device__ __forceinline__ void canny_step(const StripGeom &g, int r, int r_last
 			}
 		}
 	}
-	wr.put(g, wp.out_lane, res);
+	wr.put(g, wp.out_lane, wp.ye, res);
+}
+
+template <bool FAST, bool FIRST>
+__device__ __forceinline__ void canny_group(const StripGeom &g, const WarpPlace &wp,
+		CannyThresholds thr, const WeakSink &ws, RowReader<FAST> &rd, RowWriter<FAST> &wr,
+		uint4 (&buf)[2], HRow (&hr)[3], GRow (&gr)[3])
+{
+	canny_step<FAST, FIRST, 0>(g, wp, thr, ws, rd, wr, buf, hr, gr);
+	canny_step<FAST, FIRST, 1>(g, wp, thr, ws, rd, wr, buf, hr, gr);
+	canny_step<FAST, FIRST, 2>(g, wp, thr, ws, rd, wr, buf, hr, gr);
+	canny_step<FAST, FIRST, 3>(g, wp, thr, ws, rd, wr, buf, hr, gr);
+	canny_step<FAST, FIRST, 4>(g, wp, thr, ws, rd, wr, buf, hr, gr);
+	canny_step<FAST, FIRST, 5>(g, wp, thr, ws, rd, wr, buf, hr, gr);
 }
 
 template <bool FAST>
@@ -393,16 +418,11 @@ __device__ __forceinline__ void canny_march(const uint32_t *__restrict__ in,
 	GRow gr[3];
 	uint4 buf[2];
 	buf[0] = rd.next(g);
-	// gray rows ys-2 .. ye+1; row r yields gradient row r-1 and output row r-2
-	const int r_last = wp.ye + 1;
-	for (int r = wp.ys - 2; r <= r_last; r += 6) {
-		canny_step<FAST, 0>(g, r, r_last, wp, thr, ws, rd, wr, buf, hr, gr);
-		canny_step<FAST, 1>(g, r + 1, r_last, wp, thr, ws, rd, wr, buf, hr, gr);
-		canny_step<FAST, 2>(g, r + 2, r_last, wp, thr, ws, rd, wr, buf, hr, gr);
-		canny_step<FAST, 3>(g, r + 3, r_last, wp, thr, ws, rd, wr, buf, hr, gr);
-		canny_step<FAST, 4>(g, r + 4, r_last, wp, thr, ws, rd, wr, buf, hr, gr);
-		canny_step<FAST, 5>(g, r + 5, r_last, wp, thr, ws, rd, wr, buf, hr, gr);
-	}
+	// gray rows ys-2 .. ys+rows_per_strip+1: rows_per_strip + 4 steps, a multiple of 6
+	const int groups = (g.rows_per_strip + 4) / 6;
+	canny_group<FAST, true>(g, wp, thr, ws, rd, wr, buf, hr, gr);
+	for (int k = 1; k < groups; k++)
+		canny_group<FAST, false>(g, wp, thr, ws, rd, wr, buf, hr, gr);
 }
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
@@ -422,6 +442,88 @@ canny_classify_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ ou
 		canny_march<false>(in + page, out + page, g, wp, thr, ws);
 }
 
+struct PageGeom {
+	int w, h, npix;
+};
+
+constexpr int kHystThreads = 1024;
+constexpr int kSmallList = 2 * kHystThreads;   // weak pixels one block resolves in shared memory
+
+__device__ __forceinline__ int sm_find(int *parent, int i)
+{
+	volatile int *vp = parent;
+	int p = vp[i];
+	while (p != i) {
+		const int gp = vp[p];
+		if (gp != p)
+			vp[i] = gp;
+		i = p;
+		p = gp;
+	}
+	return i;
+}
+
+__device__ __forceinline__ void sm_union(int *parent, int a, int b)
+{
+	for (;;) {
+		a = sm_find(parent, a);
+		b = sm_find(parent, b);
+		if (a == b)
+			return;
+		if (a < b) {
+			const int t = a;
+			a = b;
+			b = t;
+		}
+		if (atomicCAS(&parent[a], a, b) == a)
+			return;
+	}
+}
+
+// Hysteresis for a short work list (the usual case: a page has hundreds of
+// weak pixels), by one block, union-find in shared memory.
+__device__ void canny_resolve_small(uint32_t *out, PageGeom pg, const int *list, int count,
+		int *s_pix, int *s_parent, unsigned char *s_keep)
+{
+	const int nt = blockDim.x;
+	for (int i = threadIdx.x; i < count; i += nt) {
+		s_pix[i] = __ldcg(list + i);
+		s_parent[i] = i;
+		s_keep[i] = 0;
+	}
+	__syncthreads();
+	unsigned strong_mask = 0;     // bit k: this thread's k-th entry touches a strong pixel (k < 2)
+	int k = 0;
+	for (int i = threadIdx.x; i < count; i += nt, k++) {
+		const int idx = s_pix[i];
+		const int p = idx % pg.npix;
+		const int y = p / pg.w, x = p - y * pg.w;
+#pragma unroll
+		for (int dy = -1; dy <= 1; dy++) {
+#pragma unroll
+			for (int dx = -1; dx <= 1; dx++) {
+				if (dx == 0 && dy == 0)
+					continue;
+				if (x + dx < 0 || x + dx >= pg.w || y + dy < 0 || y + dy >= pg.h)
+					continue;
+				const uint32_t v = __ldcg(out + idx + dy * pg.w + dx);
+				if (v == kWhite)
+					strong_mask |= 1u << k;
+				else if (v < kBlack && (int)v > i)
+					sm_union(s_parent, i, (int)v);
+			}
+		}
+	}
+	__syncthreads();
+	k = 0;
+	for (int i = threadIdx.x; i < count; i += nt, k++)
+		if (strong_mask & (1u << k))
+			s_keep[sm_find(s_parent, i)] = 1;
+	__syncthreads();
+	for (int i = threadIdx.x; i < count; i += nt)
+		out[s_pix[i]] = s_keep[sm_find(s_parent, i)] ? kWhite : kBlack;
+}
+
 // ---------------------------------------------------------------------------
 // Canny pass B: hysteresis as connected components over the weak work list.
 // A weak pixel is kept iff its 8-connected component of weak pixels touches a
@@ -429,10 +531,6 @@ canny_classify_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ ou
 // smaller with atomicCAS, path halving), so the cost does not depend on how
 // long a weak chain is and the result does not depend on scheduling.
 // ---------------------------------------------------------------------------
-
-struct PageGeom {
-	int w, h, npix;
-};
 
 __device__ __forceinline__ int uf_find(int *parent, int i)
 {
@@ -469,42 +567,52 @@ __device__ __forceinline__ void uf_union(int *parent, int a, int b)
 
 constexpr int kStrongBit = (int)0x80000000;   // in list[root]: component touches a strong pixel
 
-// B1: join every weak pixel with its weak neighbours.  Each undirected edge is
-// taken once, from the pixel with the smaller address (E, SW, S, SE).
-__global__ void __launch_bounds__(256)
-canny_link_kernel(const uint32_t *__restrict__ out, PageGeom pg,
-		const int *__restrict__ list, int *__restrict__ parent, const int *__restrict__ hdr)
+// One cooperative launch resolves the weak pixels.  A short list is handled by
+// block 0 alone in shared memory; a long one by the whole grid in three steps
+// with grid-wide barriers between them:
+//   1. join every weak pixel with its weak neighbours (each undirected edge
+//      once, from the pixel with the smaller address: E, SW, S, SE);
+//   2. a weak pixel next to a strong one marks its component's root;
+//   3. every weak pixel takes its component's verdict.
+__global__ void __launch_bounds__(kHystThreads)
+canny_hysteresis_kernel(uint32_t *out, PageGeom pg, int *list, int *parent,
+		const int *__restrict__ hdr)
 {
+	__shared__ int s_pix[kSmallList];
+	__shared__ int s_parent[kSmallList];
+	__shared__ unsigned char s_keep[kSmallList];
 	const int count = hdr[0];
-	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count;
-			i += gridDim.x * blockDim.x) {
+	if (count == 0)
+		return;
+	if (count <= kSmallList) {
+		if (blockIdx.x == 0)
+			canny_resolve_small(out, pg, list, count, s_pix, s_parent, s_keep);
+		return;
+	}
+	cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+	const int first = blockIdx.x * blockDim.x + threadIdx.x;
+	const int step = gridDim.x * blockDim.x;
+
+	for (int i = first; i < count; i += step) {
 		const int idx = list[i];
 		const int p = idx % pg.npix;
 		const int y = p / pg.w, x = p - y * pg.w;
 		const bool has_e = x + 1 < pg.w, has_w = x > 0, has_s = y + 1 < pg.h;
 		uint32_t v;
-		if (has_e && (v = out[idx + 1]) < kBlack)
+		if (has_e && (v = __ldcg(out + idx + 1)) < kBlack)
 			uf_union(parent, i, (int)v);
 		if (has_s) {
-			if (has_w && (v = out[idx + pg.w - 1]) < kBlack)
+			if (has_w && (v = __ldcg(out + idx + pg.w - 1)) < kBlack)
 				uf_union(parent, i, (int)v);
-			if ((v = out[idx + pg.w]) < kBlack)
+			if ((v = __ldcg(out + idx + pg.w)) < kBlack)
 				uf_union(parent, i, (int)v);
-			if (has_e && (v = out[idx + pg.w + 1]) < kBlack)
+			if (has_e && (v = __ldcg(out + idx + pg.w + 1)) < kBlack)
 				uf_union(parent, i, (int)v);
 		}
 	}
-}
-
-// B2: a weak pixel next to a strong one marks its component's root.
-__global__ void __launch_bounds__(256)
-canny_seed_kernel(const uint32_t *__restrict__ out, PageGeom pg,
-		int *__restrict__ list, int *__restrict__ parent, const int *__restrict__ hdr)
-{
-	const int count = hdr[0];
-	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count;
-			i += gridDim.x * blockDim.x) {
-		const int idx = list[i] & ~kStrongBit;
+	grid.sync();
+	for (int i = first; i < count; i += step) {
+		const int idx = __ldcg(list + i) & ~kStrongBit;
 		const int p = idx % pg.npix;
 		const int y = p / pg.w, x = p - y * pg.w;
 		bool strong = false;
@@ -516,42 +624,47 @@ canny_seed_kernel(const uint32_t *__restrict__ out, PageGeom pg,
 					continue;
 				if (x + dx < 0 || x + dx >= pg.w || y + dy < 0 || y + dy >= pg.h)
 					continue;
-				strong |= out[idx + dy * pg.w + dx] == kWhite;
+				strong |= __ldcg(out + idx + dy * pg.w + dx) == kWhite;
 			}
 		}
 		if (strong)
 			atomicOr(&list[uf_find(parent, i)], kStrongBit);
 	}
-}
-
-// C: every weak pixel takes its component's verdict.
-__global__ void __launch_bounds__(256)
-canny_resolve_kernel(uint32_t *__restrict__ out, const int *__restrict__ list,
-		int *__restrict__ parent, const int *__restrict__ hdr)
-{
-	const int count = hdr[0];
-	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count;
-			i += gridDim.x * blockDim.x) {
+	grid.sync();
+	for (int i = first; i < count; i += step) {
 		const int root = uf_find(parent, i);
-		const bool keep = (list[root] & kStrongBit) != 0;
-		out[list[i] & ~kStrongBit] = keep ? kWhite : kBlack;
+		const bool keep = (__ldcg(list + root) & kStrongBit) != 0;
+		out[__ldcg(list + i) & ~kStrongBit] = keep ? kWhite : kBlack;
 	}
 }
 
-StripGeom make_geom(const uint32_t *in, const uint32_t *out, int w, int h, int pages,
-		int target_warps_per_sm, int min_rows)
+// Strip height so that the whole grid is resident at once (one wave): a grid
+// a few blocks over the resident capacity would run a second, nearly empty
+// wave and double the kernel time.
+template <typename Kernel>
+StripGeom make_geom(Kernel kern, const uint32_t *in, const uint32_t *out, int w, int h,
+		int pages, int halo_rows)
 {
 	StripGeom g;
 	g.w = w;
 	g.h = h;
 	g.warp_cols = (w + kWarpCols - 1) / kWarpCols;
-	// about target_warps_per_sm warps per SM in one wave, strips no shorter than min_rows
-	long want = (long)sm_count() * target_warps_per_sm / ((long)g.warp_cols * pages);
-	if (want < 1)
-		want = 1;
-	int rows = (int)((h + want - 1) / want);
-	if (rows < min_rows)
-		rows = min_rows;
+	int blocks_per_sm = 0;
+	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern,
+			kWarpsPerBlock * 32, 0) != cudaSuccess || blocks_per_sm < 1) {
+		cudaGetLastError();
+		blocks_per_sm = 4;
+	}
+	const long resident_warps = (long)sm_count() * blocks_per_sm * kWarpsPerBlock;
+	long strips = resident_warps / ((long)g.warp_cols * pages);
+	if (strips < 1)
+		strips = 1;
+	// rows + halo_rows steps per strip must be a whole number of 6-step groups
+	int rows = (int)((h + strips - 1) / strips);
+	int groups = (rows + halo_rows + 5) / 6;
+	if (groups < 3)
+		groups = 3;
+	rows = groups * 6 - halo_rows;
 	g.rows_per_strip = rows;
 	g.strips = (h + rows - 1) / rows;
 	g.aligned = (w % 4 == 0) && (((uintptr_t)in | (uintptr_t)out) % 16 == 0);
@@ -563,7 +676,7 @@ StripGeom make_geom(const uint32_t *in, const uint32_t *out, int w, int h, int p
 int launch_sobel(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 		cudaStream_t st)
 {
-	const StripGeom g = make_geom(in, out, w, h, pages, 32, 16);
+	const StripGeom g = make_geom(sobel_kernel, in, out, w, h, pages, 2);
 	const int warps = g.warp_cols * g.strips;
 	dim3 grid((warps + kWarpsPerBlock - 1) / kWarpsPerBlock, pages);
 	sobel_kernel<<<grid, kWarpsPerBlock * 32, 0, st>>>(in, out, g);
@@ -599,8 +712,15 @@ int launch_canny(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 		cap_pages = 65535;
 	int *hdr = static_cast<int *>(scratch);
 	int *list = hdr + 64;
-	const PageGeom pg = { w, h, (int)npix };
-	const int sparse_blocks = sm_count() * 2;
+	PageGeom pg = { w, h, (int)npix };
+	// the cooperative kernel's grid must be resident at once
+	int coop_per_sm = 0;
+	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&coop_per_sm,
+			canny_hysteresis_kernel, kHystThreads, 0) != cudaSuccess || coop_per_sm < 1) {
+		cudaGetLastError();
+		coop_per_sm = 1;
+	}
+	const int coop_blocks = sm_count();
 
 	for (int p0 = 0; p0 < pages; p0 += (int)cap_pages) {
 		const int np = (pages - p0 < (int)cap_pages) ? pages - p0 : (int)cap_pages;
@@ -608,15 +728,17 @@ int launch_canny(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 		uint32_t *pout = out + (size_t)p0 * npix;
 		int *parent = list + (size_t)np * npix;
 		PFB_CUDA(cudaMemsetAsync(hdr, 0, 256, st));
-		const StripGeom g = make_geom(pin, pout, w, h, np, 24, 24);
+		const StripGeom g = make_geom(canny_classify_kernel, pin, pout, w, h, np, 4);
 		const int warps = g.warp_cols * g.strips;
 		dim3 grid((warps + kWarpsPerBlock - 1) / kWarpsPerBlock, np);
 		canny_classify_kernel<<<grid, kWarpsPerBlock * 32, 0, st>>>(pin, pout, g, thr,
 				hdr, list, parent);
-		canny_link_kernel<<<sparse_blocks, 256, 0, st>>>(pout, pg, list, parent, hdr);
-		canny_seed_kernel<<<sparse_blocks, 256, 0, st>>>(pout, pg, list, parent, hdr);
-		canny_resolve_kernel<<<sparse_blocks, 256, 0, st>>>(pout, list, parent, hdr);
 		PFB_CUDA(cudaGetLastError());
+		const int *chdr = hdr;
+		void *args[] = { &pout, &pg, &list, &parent, &chdr };
+		PFB_CUDA(cudaLaunchCooperativeKernel(
+				reinterpret_cast<void *>(canny_hysteresis_kernel),
+				dim3(coop_blocks), dim3(kHystThreads), args, 0, st));
 	}
 	return PF_B200_OK;
 }
