@@ -111,6 +111,9 @@ struct AceConst {
 	int too_close2;        // (h/5)^2: pairs with d^2 below this are skipped
 	int clamp_l;           // L = limit/slope when it is an integer <= 127 (fast path)
 	int tile_rows;         // rows a block walks; tiles sit on a page-wide grid of this pitch
+	int score_row0;        // score row stored first in `scores`
+	long score_plane;      // doubles between the R, G, B score planes
+	const uint32_t *sample_px;   // samples' pixel values, or NULL: read them from the page
 	double ratio;          // slope / limit
 	double slope, limit;
 };
@@ -182,7 +185,8 @@ __device__ __noinline__ void stage_samples(AceShared &sh, const AceConst &cs,
 			const unsigned below = (1u << lane) - 1;
 			const int dst = (cls == 1) ? off_far + __popc(mf & below)
 			                           : off_str + __popc(ms & below);
-			const uint32_t px = __ldg(in + (size_t)s.y * cs.w + s.x);
+			const uint32_t px = cs.sample_px ? __ldg(cs.sample_px + k0 + k)
+			                                 : __ldg(in + (size_t)s.y * cs.w + s.x);
 			sh.tbl[dst].sx = s.x;
 			sh.sy[dst] = s.y;
 #pragma unroll
@@ -274,8 +278,7 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 	const int tile_y1 = min(cs.h, tile_y0 + cs.tile_rows);      // exclusive
 	const int x_lo = blockIdx.x * kAceBlock;
 	const int x_hi = min(cs.w - 1, x_lo + kAceBlock - 1);
-	const int band_rows = cs.row_end - cs.row_begin;
-	const size_t plane = (size_t)band_rows * cs.w;
+	const size_t plane = (size_t)cs.score_plane;
 
 	if (!FAST) {
 		for (int i = threadIdx.x; i < 511; i += kAceBlock) {
@@ -364,7 +367,7 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 		for (int r = 0; r < P; r++) {
 			const int y = y0 + r;
 			if (y >= cs.row_begin && y < cs.row_end && y < tile_y1 && x < cs.w) {
-				const size_t o = (size_t)(y - cs.row_begin) * cs.w + x;
+				const size_t o = (size_t)(y - cs.score_row0) * cs.w + x;
 				const double inv = 1.0 / top[r];
 #pragma unroll
 				for (int c = 0; c < 3; c++) {
@@ -420,7 +423,7 @@ __global__ void ace_minmax_init_kernel(double *minmax)
 // Same operation order as the reference's linear scaling, true FP64 divide.
 __global__ void __launch_bounds__(256)
 ace_scale_kernel(const double *__restrict__ scores, const double *__restrict__ minmax,
-		size_t npix, uint32_t *__restrict__ out)
+		size_t npix, size_t plane, uint32_t *__restrict__ out)
 {
 	double mn[3], span[3];
 #pragma unroll
@@ -433,7 +436,7 @@ ace_scale_kernel(const double *__restrict__ scores, const double *__restrict__ m
 		uint32_t rgba = 0xFF000000u;
 #pragma unroll
 		for (int c = 0; c < 3; c++) {
-			const double s = __ldcs(scores + c * npix + i);
+			const double s = __ldcs(scores + c * plane + i);
 			const double v = __ddiv_rn(__dmul_rn(255.0, __dadd_rn(s, -mn[c])), span[c]);
 			uint32_t q = 0;
 			if (v > 0.0)        // false for NaN
@@ -490,6 +493,9 @@ int launch_ace_scores(const uint32_t *in, const int *samples_xy,
 	cs.too_close2 = tc * tc;
 	cs.slope = p.slope;
 	cs.limit = p.limit;
+	cs.sample_px = p.sample_px;
+	cs.score_row0 = p.score_row0 >= 0 ? p.score_row0 : p.row_begin;
+	cs.score_plane = p.score_plane >= 0 ? p.score_plane : (long)(p.row_end - p.row_begin) * p.w;
 	cs.ratio = p.slope / p.limit;
 	// fast path: saturate(slope*d) == slope*clamp(d, -L, L) with integer L <= 127
 	const double l = p.limit / p.slope;
@@ -527,12 +533,13 @@ int launch_ace_scores(const uint32_t *in, const int *samples_xy,
 }
 
 int launch_ace_scale(const double *scores, const double *minmax, int w,
-		int rows, uint32_t *out, cudaStream_t st)
+		int rows, uint32_t *out, cudaStream_t st, long plane)
 {
 	const size_t npix = (size_t)w * rows;
 	const int blocks = (int)((npix + 255) / 256 < (size_t)sm_count() * 16
 			? (npix + 255) / 256 : (size_t)sm_count() * 16);
-	ace_scale_kernel<<<blocks, 256, 0, st>>>(scores, minmax, npix, out);
+	ace_scale_kernel<<<blocks, 256, 0, st>>>(scores, minmax, npix,
+			plane >= 0 ? (size_t)plane : npix, out);
 	PFB_CUDA(cudaGetLastError());
 	return PF_B200_OK;
 }

@@ -62,9 +62,15 @@ struct Buffer {
 	size_t cap = 0;
 };
 
+constexpr int kMaxBands = 16;      // row bands a streamed call is cut into, at most
+
 struct Context {
 	int dev = -1;
-	cudaStream_t st = nullptr;
+	cudaStream_t st = nullptr;           // kernels
+	cudaStream_t st_up = nullptr;        // host -> device copies of a streamed call
+	cudaStream_t st_down = nullptr;      // device -> host copies of a streamed call
+	cudaEvent_t ev_up[kMaxBands] = {};   // band b is in HBM
+	cudaEvent_t ev_done[kMaxBands] = {}; // band b's result is ready
 	Buffer d_in, d_out, d_scratch, d_scores, d_small;
 	Buffer h_stage;   // pinned
 
@@ -81,6 +87,16 @@ struct Context {
 				cudaFree(b->p);
 		if (h_stage.p)
 			cudaFreeHost(h_stage.p);
+		for (int i = 0; i < kMaxBands; i++) {
+			if (ev_up[i])
+				cudaEventDestroy(ev_up[i]);
+			if (ev_done[i])
+				cudaEventDestroy(ev_done[i]);
+		}
+		if (st_up)
+			cudaStreamDestroy(st_up);
+		if (st_down)
+			cudaStreamDestroy(st_down);
 		if (st)
 			cudaStreamDestroy(st);
 	}
@@ -103,6 +119,12 @@ static int ctx_init(Context &c)
 				"one device per host thread", c.dev, dev);
 	c.dev = dev;
 	PFB_CUDA(cudaStreamCreateWithFlags(&c.st, cudaStreamNonBlocking));
+	PFB_CUDA(cudaStreamCreateWithFlags(&c.st_up, cudaStreamNonBlocking));
+	PFB_CUDA(cudaStreamCreateWithFlags(&c.st_down, cudaStreamNonBlocking));
+	for (int i = 0; i < kMaxBands; i++) {
+		PFB_CUDA(cudaEventCreateWithFlags(&c.ev_up[i], cudaEventDisableTiming));
+		PFB_CUDA(cudaEventCreateWithFlags(&c.ev_done[i], cudaEventDisableTiming));
+	}
 	return PF_B200_OK;
 }
 
@@ -273,6 +295,54 @@ CannyThresholds canny_thresholds()
 
 enum Op { OP_GAUSSIAN, OP_SOBEL, OP_CANNY };
 
+// Row bands of a streamed call: at least 256 rows each, at most kMaxBands.
+static int band_rows_for(int h)
+{
+	int rows = (h + 7) / 8;
+	if (rows < 256)
+		rows = 256;
+	if ((h + rows - 1) / rows > kMaxBands)
+		rows = (h + kMaxBands - 1) / kMaxBands;
+	return rows;
+}
+
+// Gaussian / Sobel on pinned caller memory: the page goes up band by band on
+// one stream, each band is filtered on the kernel stream as soon as it and
+// the band below it (the stencil's reach) have arrived, and comes back on a
+// third stream -- PCIe carries both directions at once instead of one after
+// the other.  Returns after the last band is in the caller's memory.
+static int run_stencil_streamed(Context &c, Op op, const struct pf_bitmap *in,
+		struct pf_bitmap *out, const Taps &taps)
+{
+	const int w = in->size.x, h = in->size.y;
+	const int rows = band_rows_for(h);
+	const int nb = (h + rows - 1) / rows;
+	const uint32_t *src = reinterpret_cast<const uint32_t *>(in->pixels);
+	uint32_t *dst = reinterpret_cast<uint32_t *>(out->pixels);
+	const uint32_t *din = static_cast<const uint32_t *>(c.d_in.p);
+	uint32_t *dout = static_cast<uint32_t *>(c.d_out.p);
+	for (int b = 0; b < nb; b++) {
+		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
+		PFB_CUDA(cudaMemcpyAsync(const_cast<uint32_t *>(din) + (size_t)y0 * w, src + (size_t)y0 * w,
+				(size_t)(y1 - y0) * w * sizeof(uint32_t), cudaMemcpyHostToDevice, c.st_up));
+		PFB_CUDA(cudaEventRecord(c.ev_up[b], c.st_up));
+	}
+	for (int b = 0; b < nb; b++) {
+		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
+		PFB_CUDA(cudaStreamWaitEvent(c.st, c.ev_up[b + 1 < nb ? b + 1 : b], 0));
+		int rc = (op == OP_GAUSSIAN) ? launch_gaussian(din, dout, w, h, 1, taps, c.st, y0, y1)
+		                             : launch_sobel(din, dout, w, h, 1, c.st, y0, y1);
+		if (rc)
+			return rc;
+		PFB_CUDA(cudaEventRecord(c.ev_done[b], c.st));
+		PFB_CUDA(cudaStreamWaitEvent(c.st_down, c.ev_done[b], 0));
+		PFB_CUDA(cudaMemcpyAsync(dst + (size_t)y0 * w, dout + (size_t)y0 * w,
+				(size_t)(y1 - y0) * w * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.st_down));
+	}
+	PFB_CUDA(cudaStreamSynchronize(c.st_down));
+	return PF_B200_OK;
+}
+
 static int run_stencil(Op op, const struct pf_bitmap *in, struct pf_bitmap *out,
 		double sigma, int nb_stddev)
 {
@@ -290,6 +360,9 @@ static int run_stencil(Op op, const struct pf_bitmap *in, struct pf_bitmap *out,
 	const size_t bytes = (size_t)w * h * sizeof(uint32_t);
 	if ((rc = grow(c.d_in, bytes, false)) || (rc = grow(c.d_out, bytes, false)))
 		return rc;
+	// (bands are >= 256 rows, further than any stencil here reaches: <= 31 rows)
+	if (op != OP_CANNY && h >= 512 && is_pinned(in->pixels) && is_pinned(out->pixels))
+		return run_stencil_streamed(c, op, in, out, taps);
 	if ((rc = upload(c, c.d_in.p, in->pixels, bytes)))
 		return rc;
 	const uint32_t *din = static_cast<const uint32_t *>(c.d_in.p);
@@ -335,26 +408,75 @@ static int run_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
 		return rc;
 	const size_t npix = (size_t)w * h;
 	const size_t bytes = npix * sizeof(uint32_t);
-	const size_t small = 64 + sizeof(int) * 2 * (size_t)nb_samples;
+	const size_t small = 64 + sizeof(int) * 3 * (size_t)nb_samples;
 	if ((rc = grow(c.d_in, bytes, false)) || (rc = grow(c.d_out, bytes, false))
 			|| (rc = grow(c.d_scores, 3 * npix * sizeof(double), false))
 			|| (rc = grow(c.d_small, small, false)))
 		return rc;
 	double *minmax = static_cast<double *>(c.d_small.p);
 	int *d_xy = reinterpret_cast<int *>(static_cast<char *>(c.d_small.p) + 64);
-	// the table is tiny; a synchronous copy keeps the caller's array free to reuse
+	uint32_t *d_spx = reinterpret_cast<uint32_t *>(d_xy + 2 * (size_t)nb_samples);
+	const uint32_t *din = static_cast<const uint32_t *>(c.d_in.p);
+	uint32_t *dout = static_cast<uint32_t *>(c.d_out.p);
+	double *scores = static_cast<double *>(c.d_scores.p);
+	// the table is tiny; pageable copies are staged by the runtime before it
+	// returns, so the caller's array is free to reuse
 	PFB_CUDA(cudaMemcpyAsync(d_xy, sample_xy, sizeof(int) * 2 * (size_t)nb_samples,
 			cudaMemcpyHostToDevice, c.st));
-	if ((rc = upload(c, c.d_in.p, in->pixels, bytes)))
-		return rc;
 	AceParams p = { w, h, 0, h, nb_samples, slope, limit };
 	if ((rc = launch_ace_minmax_init(minmax, c.st)))
 		return rc;
-	if ((rc = launch_ace_scores(static_cast<const uint32_t *>(c.d_in.p), d_xy, p,
-			static_cast<double *>(c.d_scores.p), minmax, c.st)))
+
+	if (h >= 512 && nb_samples <= 4096 && is_pinned(in->pixels) && is_pinned(out->pixels)) {
+		// Streamed: with the samples' pixel values sent ahead (gathered here
+		// from the caller's page), a band of rows can be accumulated as soon
+		// as it has arrived; the rescale needs the page-wide min/max, so it
+		// starts after the last band and overlaps the way back.
+		const uint32_t *src = reinterpret_cast<const uint32_t *>(in->pixels);
+		uint32_t *dst = reinterpret_cast<uint32_t *>(out->pixels);
+		uint32_t spx[4096];
+		for (int i = 0; i < nb_samples; i++)
+			spx[i] = src[(size_t)sample_xy[2 * i + 1] * w + sample_xy[2 * i]];
+		PFB_CUDA(cudaMemcpyAsync(d_spx, spx, sizeof(uint32_t) * (size_t)nb_samples,
+				cudaMemcpyHostToDevice, c.st));
+		const int rows = band_rows_for(h);
+		const int nb = (h + rows - 1) / rows;
+		for (int b = 0; b < nb; b++) {
+			const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
+			PFB_CUDA(cudaMemcpyAsync(const_cast<uint32_t *>(din) + (size_t)y0 * w,
+					src + (size_t)y0 * w, (size_t)(y1 - y0) * w * sizeof(uint32_t),
+					cudaMemcpyHostToDevice, c.st_up));
+			PFB_CUDA(cudaEventRecord(c.ev_up[b], c.st_up));
+		}
+		p.sample_px = d_spx;
+		p.score_row0 = 0;
+		p.score_plane = (long)npix;
+		for (int b = 0; b < nb; b++) {
+			p.row_begin = b * rows;
+			p.row_end = (p.row_begin + rows < h) ? p.row_begin + rows : h;
+			PFB_CUDA(cudaStreamWaitEvent(c.st, c.ev_up[b], 0));
+			if ((rc = launch_ace_scores(din, d_xy, p, scores, minmax, c.st)))
+				return rc;
+		}
+		for (int b = 0; b < nb; b++) {
+			const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
+			if ((rc = launch_ace_scale(scores + (size_t)y0 * w, minmax, w, y1 - y0,
+					dout + (size_t)y0 * w, c.st, (long)npix)))
+				return rc;
+			PFB_CUDA(cudaEventRecord(c.ev_done[b], c.st));
+			PFB_CUDA(cudaStreamWaitEvent(c.st_down, c.ev_done[b], 0));
+			PFB_CUDA(cudaMemcpyAsync(dst + (size_t)y0 * w, dout + (size_t)y0 * w,
+					(size_t)(y1 - y0) * w * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.st_down));
+		}
+		PFB_CUDA(cudaStreamSynchronize(c.st_down));
+		return PF_B200_OK;
+	}
+
+	if ((rc = upload(c, c.d_in.p, in->pixels, bytes)))
 		return rc;
-	if ((rc = launch_ace_scale(static_cast<const double *>(c.d_scores.p), minmax, w, h,
-			static_cast<uint32_t *>(c.d_out.p), c.st)))
+	if ((rc = launch_ace_scores(din, d_xy, p, scores, minmax, c.st)))
+		return rc;
+	if ((rc = launch_ace_scale(scores, minmax, w, h, dout, c.st)))
 		return rc;
 	return download(c, out->pixels, c.d_out.p, bytes);
 }

@@ -33,11 +33,15 @@ struct Taps {
 	double t[kMaxTaps];
 };
 
-// ---- stencil launchers (pf_stencil.cu); all asynchronous on `st` ----------
+// ---- stencil launchers (pf_gaussian.cu, pf_edges.cu); asynchronous on `st` --
+// [y_begin, y_end) restricts the OUTPUT rows (y_end < 0: the whole page);
+// input rows up to the stencil's reach outside that range are read, so they
+// must already be in place -- this is what lets the host-pointer entry points
+// overlap the upload of one band with the work on another.
 int launch_gaussian(const uint32_t *in, uint32_t *out, int w, int h, int pages,
-		const Taps &taps, cudaStream_t st);
+		const Taps &taps, cudaStream_t st, int y_begin = 0, int y_end = -1);
 int launch_sobel(const uint32_t *in, uint32_t *out, int w, int h, int pages,
-		cudaStream_t st);
+		cudaStream_t st, int y_begin = 0, int y_end = -1);
 
 struct CannyThresholds {
 	int weak_min;    // smallest g_x^2+g_y^2 whose hypot is  > LOW
@@ -55,12 +59,22 @@ struct AceParams {
 	int row_begin, row_end;
 	int nb_samples;
 	double slope, limit;
+	// Optional (host-pointer streaming path): the samples' pixel values, so
+	// that the accumulation of a band does not need the rest of the page;
+	// NULL = read them from the page.
+	const uint32_t *sample_px = nullptr;
+	// Where score row `score_row0` lives and how far apart the planes are.
+	// Defaults (< 0): a band-local buffer, row_begin first, planes of
+	// (row_end-row_begin)*w doubles.
+	int score_row0 = -1;
+	long score_plane = -1;
 };
 int launch_ace_minmax_init(double *minmax, cudaStream_t st);
 int launch_ace_scores(const uint32_t *in, const int *samples_xy,
 		const AceParams &p, double *scores, double *minmax, cudaStream_t st);
+// plane < 0: planes of rows*w doubles (a band-local buffer)
 int launch_ace_scale(const double *scores, const double *minmax, int w,
-		int rows, uint32_t *out, cudaStream_t st);
+		int rows, uint32_t *out, cudaStream_t st, long plane = -1);
 double measure_fp64_peak_tflops();
 
 }  // namespace pfb

@@ -35,9 +35,10 @@ constexpr uint32_t kBlack = 0xFF000000u;   // no edge
 
 struct StripGeom {
 	int w, h;
+	int y_begin, y_end;  // output rows of this launch
 	int rows_per_strip;
 	int warp_cols;       // ceil(w / 120)
-	int strips;          // ceil(h / rows_per_strip)
+	int strips;          // ceil((y_end - y_begin) / rows_per_strip)
 	int aligned;         // rows can be accessed as uint4
 };
 
@@ -204,8 +205,8 @@ __device__ __forceinline__ WarpPlace place_warp(const StripGeom &g)
 	wp.x0 = wx + lane * 4;
 	wp.out_lane = lane >= 1 && lane <= kOutLanes;
 	wp.interior = g.aligned && wx >= 0 && wx + 128 <= g.w;
-	wp.ys = strip * g.rows_per_strip;
-	wp.ye = min(g.h, wp.ys + g.rows_per_strip);
+	wp.ys = g.y_begin + strip * g.rows_per_strip;
+	wp.ye = min(g.y_end, wp.ys + g.rows_per_strip);
 	return wp;
 }
 
@@ -643,11 +644,14 @@ canny_hysteresis_kernel(uint32_t *out, PageGeom pg, int *list, int *parent,
 // wave and double the kernel time.
 template <typename Kernel>
 StripGeom make_geom(Kernel kern, const uint32_t *in, const uint32_t *out, int w, int h,
-		int pages, int halo_rows)
+		int pages, int halo_rows, int y_begin = 0, int y_end = -1)
 {
 	StripGeom g;
 	g.w = w;
 	g.h = h;
+	g.y_begin = y_begin;
+	g.y_end = y_end < 0 ? h : y_end;
+	const int nrows = g.y_end - g.y_begin;
 	g.warp_cols = (w + kWarpCols - 1) / kWarpCols;
 	int blocks_per_sm = 0;
 	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern,
@@ -660,13 +664,13 @@ StripGeom make_geom(Kernel kern, const uint32_t *in, const uint32_t *out, int w,
 	if (strips < 1)
 		strips = 1;
 	// rows + halo_rows steps per strip must be a whole number of 6-step groups
-	int rows = (int)((h + strips - 1) / strips);
+	int rows = (int)((nrows + strips - 1) / strips);
 	int groups = (rows + halo_rows + 5) / 6;
 	if (groups < 3)
 		groups = 3;
 	rows = groups * 6 - halo_rows;
 	g.rows_per_strip = rows;
-	g.strips = (h + rows - 1) / rows;
+	g.strips = (nrows + rows - 1) / rows;
 	g.aligned = (w % 4 == 0) && (((uintptr_t)in | (uintptr_t)out) % 16 == 0);
 	return g;
 }
@@ -674,9 +678,13 @@ StripGeom make_geom(Kernel kern, const uint32_t *in, const uint32_t *out, int w,
 }  // namespace
 
 int launch_sobel(const uint32_t *in, uint32_t *out, int w, int h, int pages,
-		cudaStream_t st)
+		cudaStream_t st, int y_begin, int y_end)
 {
-	const StripGeom g = make_geom(sobel_kernel, in, out, w, h, pages, 2);
+	if (y_end < 0)
+		y_end = h;
+	if (y_begin < 0 || y_begin >= y_end || y_end > h)
+		return fail(PF_B200_EINVAL, "sobel: bad row range [%d, %d) of %d", y_begin, y_end, h);
+	const StripGeom g = make_geom(sobel_kernel, in, out, w, h, pages, 2, y_begin, y_end);
 	const int warps = g.warp_cols * g.strips;
 	dim3 grid((warps + kWarpsPerBlock - 1) / kWarpsPerBlock, pages);
 	sobel_kernel<<<grid, kWarpsPerBlock * 32, 0, st>>>(in, out, g);

@@ -52,7 +52,7 @@ struct TapsN {
 template <int N, int PX>
 __global__ void __launch_bounds__(kBlock)
 gaussian_march_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
-		int w, int h, int rows_per_strip, const TapsN<N> tp)
+		int w, int h, int y_begin, int y_end, int rows_per_strip, const TapsN<N> tp)
 {
 	constexpr int C = N / 2;             // taps reach x+C ... x-(N-1-C)
 	constexpr int L = N - 1 - C;         // left / up reach
@@ -64,8 +64,8 @@ gaussian_march_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ ou
 	const size_t page = (size_t)blockIdx.z * w * h;
 	in += page;
 	out += page;
-	const int ys = blockIdx.y * rows_per_strip;
-	const int ye = min(h, ys + rows_per_strip);
+	const int ys = y_begin + blockIdx.y * rows_per_strip;
+	const int ye = min(y_end, ys + rows_per_strip);
 
 	double taps[N];
 #pragma unroll
@@ -140,11 +140,11 @@ gaussian_march_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ ou
 // Any tap count: one thread per pixel, N*N multiply-adds, same rounding order.
 __global__ void __launch_bounds__(kBlock)
 gaussian_generic_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
-		int w, int h, const Taps tp)
+		int w, int h, int y_begin, const Taps tp)
 {
 	const int n = tp.n;
 	const int x = blockIdx.x * kBlock + threadIdx.x;
-	const int y = blockIdx.y;
+	const int y = y_begin + blockIdx.y;
 	if (x >= w)
 		return;
 	const size_t page = (size_t)blockIdx.z * w * h;
@@ -206,31 +206,36 @@ int strips_for(int w_threads_blocks, int h, int pages, int blocks_per_sm, int mi
 
 template <int N>
 static void launch_gaussian_n(const uint32_t *in, uint32_t *out, int w, int h,
-		int pages, const Taps &taps, cudaStream_t st)
+		int pages, const Taps &taps, cudaStream_t st, int y_begin, int y_end)
 {
 	TapsN<N> tp;
 	for (int k = 0; k < N; k++)
 		tp.t[k] = taps.t[k];
 	constexpr int PX = 2;
 	const int bx = ((w + PX - 1) / PX + kBlock - 1) / kBlock;
-	const int rows = strips_for(bx, h, pages, 4, 8 * N);
-	dim3 grid(bx, (h + rows - 1) / rows, pages);
-	gaussian_march_kernel<N, PX><<<grid, kBlock, 0, st>>>(in, out, w, h, rows, tp);
+	const int nrows = y_end - y_begin;
+	const int rows = strips_for(bx, nrows, pages, 4, 8 * N);
+	dim3 grid(bx, (nrows + rows - 1) / rows, pages);
+	gaussian_march_kernel<N, PX><<<grid, kBlock, 0, st>>>(in, out, w, h, y_begin, y_end, rows, tp);
 }
 
 int launch_gaussian(const uint32_t *in, uint32_t *out, int w, int h, int pages,
-		const Taps &taps, cudaStream_t st)
+		const Taps &taps, cudaStream_t st, int y_begin, int y_end)
 {
+	if (y_end < 0)
+		y_end = h;
+	if (y_begin < 0 || y_begin >= y_end || y_end > h)
+		return fail(PF_B200_EINVAL, "gaussian: bad row range [%d, %d) of %d", y_begin, y_end, h);
 	if (taps.n < 1 || taps.n > kMaxTaps)
 		return fail(PF_B200_EINVAL, "gaussian: nb_stddev must be in 1..%d", kMaxTaps);
 	switch (taps.n) {
-	case 3: launch_gaussian_n<3>(in, out, w, h, pages, taps, st); break;
-	case 5: launch_gaussian_n<5>(in, out, w, h, pages, taps, st); break;
-	case 7: launch_gaussian_n<7>(in, out, w, h, pages, taps, st); break;
-	case 9: launch_gaussian_n<9>(in, out, w, h, pages, taps, st); break;
+	case 3: launch_gaussian_n<3>(in, out, w, h, pages, taps, st, y_begin, y_end); break;
+	case 5: launch_gaussian_n<5>(in, out, w, h, pages, taps, st, y_begin, y_end); break;
+	case 7: launch_gaussian_n<7>(in, out, w, h, pages, taps, st, y_begin, y_end); break;
+	case 9: launch_gaussian_n<9>(in, out, w, h, pages, taps, st, y_begin, y_end); break;
 	default: {
-		dim3 grid((w + kBlock - 1) / kBlock, h, pages);
-		gaussian_generic_kernel<<<grid, kBlock, 0, st>>>(in, out, w, h, taps);
+		dim3 grid((w + kBlock - 1) / kBlock, y_end - y_begin, pages);
+		gaussian_generic_kernel<<<grid, kBlock, 0, st>>>(in, out, w, h, y_begin, taps);
 	}
 	}
 	PFB_CUDA(cudaGetLastError());

@@ -273,6 +273,52 @@ def test_in_place_and_pinned_buffers(gpu, oracle):
         lib.pf_b200_host_free(pin)
 
 
+def test_streamed_paths_on_pinned_pages(gpu, oracle):
+    """Pinned caller memory and >= 512 rows: the page is uploaded, processed
+    and returned band by band on three streams.  Same results, also in place."""
+    from libpillowfight_b200 import _capi
+    lib = _capi.lib
+    w, h = 700, 1500                     # 6 bands of 256 rows, the last one short
+    page = synthetic_page(w, h, 13)
+    n = page.nbytes
+    pin = lib.pf_b200_host_alloc(2 * n)
+    assert pin
+    try:
+        def view(k):
+            return np.ctypeslib.as_array((ctypes.c_uint8 * n).from_address(pin + k * n)).reshape(page.shape)
+
+        def bm(k):
+            b = _capi.PfBitmap()
+            b.size.x, b.size.y, b.pixels = w, h, pin + k * n
+            return b
+
+        src, dst = view(0), view(1)
+        b_src, b_dst = bm(0), bm(1)
+        src[:] = page
+        _capi.check(lib.pf_b200_gaussian(ctypes.byref(b_src), ctypes.byref(b_dst), 2.0, 5))
+        ref_g = oracle.gaussian(page, 2.0, 5)
+        assert np.array_equal(dst, ref_g)
+        _capi.check(lib.pf_b200_gaussian(ctypes.byref(b_src), ctypes.byref(b_dst), 3.0, 9))
+        assert np.array_equal(dst, oracle.gaussian(page, 3.0, 9))
+        _capi.check(lib.pf_b200_sobel(ctypes.byref(b_src), ctypes.byref(b_dst)))
+        assert np.array_equal(dst, oracle.sobel(page))
+        xy = oracle.ace_draw_samples(60, w, h, 31)
+        _capi.check(lib.pf_b200_ace(ctypes.byref(b_src), ctypes.byref(b_dst), 60,
+                                    xy.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), 10.0, 1000.0))
+        ref_a = oracle.ace_with_samples(page, xy, 10.0, 1000.0, nb_threads=8)
+        assert_fp_parity(dst, ref_a, "streamed ace")
+        # the streamed and the plain path run the same kernels on the same tiles
+        assert np.array_equal(dst, gpu.ace(page, 10, 1000, 60, seed=31))
+        # in place
+        _capi.check(lib.pf_b200_sobel(ctypes.byref(b_src), ctypes.byref(b_src)))
+        assert np.array_equal(src, oracle.sobel(page))
+        src[:] = page
+        _capi.check(lib.pf_b200_gaussian(ctypes.byref(b_src), ctypes.byref(b_src), 2.0, 5))
+        assert np.array_equal(src, ref_g)
+    finally:
+        lib.pf_b200_host_free(pin)
+
+
 def test_device_batch_entry_points(gpu, oracle):
     import torch
     from libpillowfight_b200.distributed import CudaChain
