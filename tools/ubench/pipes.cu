@@ -134,7 +134,7 @@ void run_mix(const char *name, K kern, int sms, double clk_ghz, int instr_per_it
 	const double cyc = best * 1e-3 * clk_ghz * 1e9;
 	const double per_smsp = cyc / ((double)(threads / 32) * 4 / 4 * ITERS);   // 4 blocks/SM, 16 warps each, 4 SMSPs
 	printf("%-16s %8.3f ms  %6.2f cycles per SMSP per (warp x iteration of %d instr)\n", name, best,
-			per_smsp / 4.0, instr_per_iter);
+			per_smsp, instr_per_iter);
 	cudaFree(sink);
 }
 
