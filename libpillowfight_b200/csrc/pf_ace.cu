@@ -32,7 +32,7 @@ namespace {
 constexpr int kAceBlock = 128;      // threads = columns per block
 constexpr int kMaxRowsPerThread = 8; // P: pixels a thread carries (same column), 2 / 4 / 8
 #ifndef PF_ACE_UNROLL
-#define PF_ACE_UNROLL 2
+#define PF_ACE_UNROLL 4
 #endif
 constexpr int kAceUnroll = PF_ACE_UNROLL;   // unroll of the sample loop
 constexpr int kChunk = 512;         // samples staged in shared memory at a time

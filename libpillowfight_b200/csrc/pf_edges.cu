@@ -8,74 +8,28 @@
 // in int32: floor(hypot) = isqrt(g_x^2+g_y^2), intensity comparisons compare
 // g_x^2+g_y^2, the direction sector is an exact integer test.
 //
-// Layout: a warp marches down a strip of rows.  Each lane owns 4 adjacent
-// columns (one 16-byte load / store per row); lanes 0 and 31 are halo lanes
-// whose values only feed their neighbours through shuffles, so a warp emits
-// 120 columns.  The vertical window lives in registers, rotated by unrolling
-// the row loop by 3.  Per stage a pixel is read once and written once.
+// Layout: the warp march of pf_march.cuh (4 columns per lane, halo lanes,
+// register-resident 3-row windows).  Per stage a pixel is read once and
+// written once.
 #include <cooperative_groups.h>
 
 #include <mutex>
 
-#include "pf_common.cuh"
+#include "pf_march.cuh"
 
 namespace pfb {
 
 namespace {
-
-constexpr int kWarpsPerBlock = 4;
-constexpr int kOutLanes = 30;
-constexpr int kWarpCols = kOutLanes * 4;        // 120 output columns per warp
-constexpr unsigned kFull = 0xFFFFFFFFu;
 
 constexpr uint32_t kWhite = 0xFFFFFFFFu;   // kept edge
 constexpr uint32_t kBlack = 0xFF000000u;   // no edge
 // A weak candidate is stored as its index in the work list; every index is
 // below kBlack, so "value < kBlack" tags a weak pixel until pass C resolves it.
 
-struct StripGeom {
-	int w, h;
-	int y_begin, y_end;  // output rows of this launch
-	int rows_per_strip;
-	int warp_cols;       // ceil(w / 120)
-	int strips;          // ceil((y_end - y_begin) / rows_per_strip)
-	int aligned;         // rows can be accessed as uint4
-};
-
 // (r + g + b) / 3: one SAD against zero sums the three bytes, IMAD.HI divides.
 __device__ __forceinline__ int gray_of(uint32_t p)
 {
 	return (int)__umulhi(__vsadu4(p & 0x00FFFFFFu, 0u), 0x55555556u);
-}
-
-__device__ __forceinline__ uint4 load_px4(const uint32_t *__restrict__ img,
-		const StripGeom &g, int r, int x0)
-{
-	uint4 v = make_uint4(0u, 0u, 0u, 0u);
-	if (r < 0 || r >= g.h)
-		return v;
-	const uint32_t *row = img + (size_t)r * g.w;
-	if (g.aligned && x0 >= 0 && x0 + 3 < g.w)
-		return __ldg(reinterpret_cast<const uint4 *>(row + x0));
-	if (x0 >= 0 && x0 < g.w) v.x = __ldg(row + x0);
-	if (x0 + 1 >= 0 && x0 + 1 < g.w) v.y = __ldg(row + x0 + 1);
-	if (x0 + 2 >= 0 && x0 + 2 < g.w) v.z = __ldg(row + x0 + 2);
-	if (x0 + 3 >= 0 && x0 + 3 < g.w) v.w = __ldg(row + x0 + 3);
-	return v;
-}
-
-__device__ __forceinline__ void store_px4(uint32_t *__restrict__ img,
-		const StripGeom &g, int r, int x0, const uint32_t (&v)[4])
-{
-	uint32_t *row = img + (size_t)r * g.w;
-	if (g.aligned && x0 + 3 < g.w) {
-		*reinterpret_cast<uint4 *>(row + x0) = make_uint4(v[0], v[1], v[2], v[3]);
-		return;
-	}
-#pragma unroll
-	for (int i = 0; i < 4; i++)
-		if (x0 + i < g.w)
-			row[x0 + i] = v[i];
 }
 
 // Horizontal parts of the two Sobel kernels for the lane's 4 columns:
@@ -115,120 +69,24 @@ __device__ __forceinline__ uint32_t gray_pixel_of_mag2(int m)
 }
 
 // ---------------------------------------------------------------------------
-// Row access for the march.  FAST: the warp's 128 columns lie inside the page
-// and rows are 16-byte aligned, so a row is one LDG.128 / STG.128 through a
-// pointer that advances by the row pitch; only the row index needs a (warp-
-// uniform) test at the top and bottom of the page.  !FAST: page-edge warps and
-// odd widths, every pixel bounds-checked.
-// ---------------------------------------------------------------------------
-
-template <bool FAST>
-struct RowReader {
-	const uint32_t *img;      // page base (generic path)
-	const uint4 *p;           // (row, x0) of the next row to load (fast path)
-	int pitch4;               // row pitch in uint4
-	int r;                    // index of the next row to load
-	int x0;
-
-	__device__ __forceinline__ void init(const uint32_t *page, const StripGeom &g, int first_row, int x0_)
-	{
-		img = page;
-		x0 = x0_;
-		r = first_row;
-		pitch4 = g.w >> 2;
-		p = reinterpret_cast<const uint4 *>(page + (long)first_row * g.w + x0_);
-	}
-	__device__ __forceinline__ uint4 next(const StripGeom &g)
-	{
-		uint4 v;
-		if (FAST) {
-			v = make_uint4(0u, 0u, 0u, 0u);
-			if (r >= 0 && r < g.h)
-				v = __ldg(p);
-			p += pitch4;
-		} else {
-			v = load_px4(img, g, r, x0);
-		}
-		r++;
-		return v;
-	}
-};
-
-template <bool FAST>
-struct RowWriter {
-	uint32_t *img;
-	uint4 *p;                 // (row, x0) of the next row to store (fast path)
-	int pitch4;
-	int r;
-	int x0;
-
-	__device__ __forceinline__ void init(uint32_t *page, const StripGeom &g, int first_row, int x0_)
-	{
-		img = page;
-		x0 = x0_;
-		r = first_row;
-		pitch4 = g.w >> 2;
-		p = reinterpret_cast<uint4 *>(page + (long)first_row * g.w + x0_);
-	}
-	// stores row r for the lanes that own output columns (if the row belongs
-	// to the strip), then moves down a row
-	__device__ __forceinline__ void put(const StripGeom &g, bool out_lane, int row_end,
-			const uint32_t (&v)[4])
-	{
-		if (FAST) {
-			if (out_lane && r < row_end)
-				*p = make_uint4(v[0], v[1], v[2], v[3]);
-			p += pitch4;
-		} else if (out_lane && r < row_end && x0 < g.w) {
-			store_px4(img, g, r, x0, v);
-		}
-		r++;
-	}
-};
-
-struct WarpPlace {
-	int x0;           // first column of this lane (may be -4 for a halo lane)
-	int ys, ye;       // output rows of the strip
-	bool out_lane;    // lanes 1..30
-	bool interior;    // all 128 columns inside the page
-	bool valid;
-};
-
-__device__ __forceinline__ WarpPlace place_warp(const StripGeom &g)
-{
-	WarpPlace wp;
-	const int gw = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
-	const int strip = gw / g.warp_cols;
-	const int lane = threadIdx.x & 31;
-	const int wx = (gw - strip * g.warp_cols) * kWarpCols - 4;
-	wp.valid = strip < g.strips;
-	wp.x0 = wx + lane * 4;
-	wp.out_lane = lane >= 1 && lane <= kOutLanes;
-	wp.interior = g.aligned && wx >= 0 && wx + 128 <= g.w;
-	wp.ys = g.y_begin + strip * g.rows_per_strip;
-	wp.ye = min(g.y_end, wp.ys + g.rows_per_strip);
-	return wp;
-}
-
-// ---------------------------------------------------------------------------
 // Sobel
 // ---------------------------------------------------------------------------
 
-// Step J of 6: a gray row arrives in pixel buffer J&1 (loaded one step
-// earlier), the next row's load is issued into the other buffer, and the
-// output row above leaves.  Horizontal terms of the last three rows sit in hr
-// slots (J+1)%3, (J+2)%3, J%3.  The march runs whole groups of 6 steps (strip
-// heights are chosen for that), so nothing but the store is conditional; in
-// the FIRST group the first two steps only fill the window.
-template <bool FAST, bool FIRST, int J>
-__device__ __forceinline__ void sobel_step(const StripGeom &g, const WarpPlace &wp,
-		RowReader<FAST> &rd, RowWriter<FAST> &wr, uint4 (&buf)[2], HRow (&hr)[3])
+// Step J of 3 (s = steps since the top of the strip): the gray row at the
+// head of the 3-deep row queue is consumed, its slot is refilled with the row
+// 3 below, and the output row above leaves.  Horizontal terms of the last
+// three rows sit in hr slots (J+1)%3, (J+2)%3, J.  The first two steps of a
+// strip only fill the window.
+template <bool FAST, int J>
+__device__ __forceinline__ void sobel_step(const StripGeom &g, const WarpPlace &wp, int s,
+		RowReader<FAST> &rd, RowWriter<FAST> &wr, uint4 (&q)[3], HRow (&hr)[3])
 {
-	buf[(J + 1) & 1] = rd.next(g);            // in flight during this row's math
-	hrow_from_pixels(buf[J & 1], hr[J % 3]);
-	if (FIRST && J < 2)
+	const uint4 cur = q[J];
+	q[J] = rd.next(g);
+	hrow_from_pixels(cur, hr[J]);
+	if (s < 2)
 		return;
-	const HRow &a = hr[(J + 1) % 3], &b = hr[(J + 2) % 3], &c = hr[J % 3];
+	const HRow &a = hr[(J + 1) % 3], &b = hr[(J + 2) % 3], &c = hr[J];
 	uint32_t res[4];
 #pragma unroll
 	for (int i = 0; i < 4; i++) {
@@ -236,19 +94,7 @@ __device__ __forceinline__ void sobel_step(const StripGeom &g, const WarpPlace &
 		const int gy = a.hs[i] - c.hs[i];
 		res[i] = gray_pixel_of_mag2(gx * gx + gy * gy);
 	}
-	wr.put(g, wp.out_lane, wp.ye, res);
-}
-
-template <bool FAST, bool FIRST>
-__device__ __forceinline__ void sobel_group(const StripGeom &g, const WarpPlace &wp,
-		RowReader<FAST> &rd, RowWriter<FAST> &wr, uint4 (&buf)[2], HRow (&hr)[3])
-{
-	sobel_step<FAST, FIRST, 0>(g, wp, rd, wr, buf, hr);
-	sobel_step<FAST, FIRST, 1>(g, wp, rd, wr, buf, hr);
-	sobel_step<FAST, FIRST, 2>(g, wp, rd, wr, buf, hr);
-	sobel_step<FAST, FIRST, 3>(g, wp, rd, wr, buf, hr);
-	sobel_step<FAST, FIRST, 4>(g, wp, rd, wr, buf, hr);
-	sobel_step<FAST, FIRST, 5>(g, wp, rd, wr, buf, hr);
+	wr.put(g, wp.ye, res);
 }
 
 template <bool FAST>
@@ -258,15 +104,19 @@ __device__ __forceinline__ void sobel_march(const uint32_t *__restrict__ in,
 	RowReader<FAST> rd;
 	RowWriter<FAST> wr;
 	rd.init(in, g, wp.ys - 1, wp.x0);
-	wr.init(out, g, wp.ys, wp.x0);
+	wr.init(out, g, wp.ys, wp.x0, wp.out_lane);
 	HRow hr[3];
-	uint4 buf[2];
-	buf[0] = rd.next(g);
-	// gray rows ys-1 .. ys+rows_per_strip: rows_per_strip + 2 steps, a multiple of 6
-	const int groups = (g.rows_per_strip + 2) / 6;
-	sobel_group<FAST, true>(g, wp, rd, wr, buf, hr);
-	for (int k = 1; k < groups; k++)
-		sobel_group<FAST, false>(g, wp, rd, wr, buf, hr);
+	uint4 q[3];
+	q[0] = rd.next(g);
+	q[1] = rd.next(g);
+	q[2] = rd.next(g);
+	// gray rows ys-1 .. ys+rows_per_strip: rows_per_strip + 2 steps, a multiple of 3
+	const int steps = g.rows_per_strip + 2;
+	for (int s = 0; s < steps; s += 3) {
+		sobel_step<FAST, 0>(g, wp, s, rd, wr, q, hr);
+		sobel_step<FAST, 1>(g, wp, s + 1, rd, wr, q, hr);
+		sobel_step<FAST, 2>(g, wp, s + 2, rd, wr, q, hr);
+	}
 }
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
@@ -277,7 +127,7 @@ sobel_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
 	if (!wp.valid)
 		return;
 	const size_t page = (size_t)blockIdx.y * g.w * g.h;
-	if (wp.interior)
+	if (g.aligned)
 		sobel_march<true>(in + page, out + page, g, wp);
 	else
 		sobel_march<false>(in + page, out + page, g, wp);
@@ -293,6 +143,8 @@ struct GRow {
 	int sector[4];     // 0: E-W, 1: SE-NW, 2: N-S, 3: SW-NE neighbours
 };
 
+// `row_inside`: the gradient row is inside the page; for FAST launches it
+// already includes "this lane's columns are inside the page".
 template <bool FAST>
 __device__ __forceinline__ void grow_from_hrows(const HRow &a, const HRow &b,
 		const HRow &c, bool row_inside, int x0, int w, GRow &o)
@@ -320,39 +172,41 @@ struct WeakSink {
 	int page_base;
 };
 
-// Step J of 6: gray row r arrives; gradient row r-1 is formed (slot J%3, from
-// horizontal rows r-2, r-1, r); output row y = r-2 is classified from gradient
-// rows r-3, r-2, r-1.  Whole groups of 6 steps, as for Sobel; in the FIRST
-// group steps 0-1 only fill the gray window and steps 2-3 the gradient window.
-template <bool FAST, bool FIRST, int J>
-__device__ __forceinline__ void canny_step(const StripGeom &g, const WarpPlace &wp,
+// Step J of 3 (s = steps since the top of the strip): gray row r = ys-2+s
+// leaves the row queue; gradient row r-1 is formed (slot J, from horizontal
+// rows r-2, r-1, r); output row y = r-2 is classified from gradient rows r-3,
+// r-2, r-1.  Steps 0-1 of a strip only fill the gray window, steps 2-3 the
+// gradient window.
+template <bool FAST, int J>
+__device__ __forceinline__ void canny_step(const StripGeom &g, const WarpPlace &wp, int s,
 		CannyThresholds thr, const WeakSink &ws, RowReader<FAST> &rd, RowWriter<FAST> &wr,
-		uint4 (&buf)[2], HRow (&hr)[3], GRow (&gr)[3])
+		uint4 (&q)[3], HRow (&hr)[3], GRow (&gr)[3])
 {
-	const int r = rd.r - 1;      // the row sitting in buf[J & 1]
-	buf[(J + 1) & 1] = rd.next(g);
-	hrow_from_pixels(buf[J & 1], hr[J % 3]);
-	if (FIRST && J < 2)
+	const uint4 cur = q[J];
+	q[J] = rd.next(g);
+	hrow_from_pixels(cur, hr[J]);
+	if (s < 2)
 		return;
+	const int r = wp.ys - 2 + s;
 	const int grow = r - 1;
-	grow_from_hrows<FAST>(hr[(J + 1) % 3], hr[(J + 2) % 3], hr[J % 3],
-			grow >= 0 && grow < g.h, wp.x0, g.w, gr[J % 3]);
-	if (FIRST && J < 4)
+	grow_from_hrows<FAST>(hr[(J + 1) % 3], hr[(J + 2) % 3], hr[J],
+			grow >= 0 && grow < g.h && (!FAST || rd.lane_in), wp.x0, g.w, gr[J]);
+	if (s < 4)
 		return;
 	const int y = r - 2;
-	const GRow &up = gr[(J + 1) % 3], &mid = gr[(J + 2) % 3], &dn = gr[J % 3];
-	const bool owns = wp.out_lane && y < wp.ye && (FAST || wp.x0 < g.w);
+	const GRow &up = gr[(J + 1) % 3], &mid = gr[(J + 2) % 3], &dn = gr[J];
+	const bool owns = wr.lane_out && y < wp.ye;
 	uint32_t res[4];
 	int nweak = 0;
 #pragma unroll
 	for (int i = 0; i < 4; i++) {
 		const int m = mid.m[i + 1];
-		const int s = mid.sector[i];
+		const int sc = mid.sector[i];
 		const int ew = max(mid.m[i], mid.m[i + 2]);
 		const int ns = max(up.m[i + 1], dn.m[i + 1]);
 		const int d1 = max(dn.m[i + 2], up.m[i]);       // (x+1,y+1), (x-1,y-1)
 		const int d3 = max(dn.m[i], up.m[i + 2]);       // (x-1,y+1), (x+1,y-1)
-		const int nb = (s == 0) ? ew : ((s == 2) ? ns : ((s == 1) ? d1 : d3));
+		const int nb = (sc == 0) ? ew : ((sc == 2) ? ns : ((sc == 1) ? d1 : d3));
 		uint32_t v = kBlack;
 		if (m >= nb && m >= thr.weak_min) {
 			v = kWhite;
@@ -390,20 +244,7 @@ __device__ __forceinline__ void canny_step(const StripGeom &g, const WarpPlace &
 			}
 		}
 	}
-	wr.put(g, wp.out_lane, wp.ye, res);
-}
-
-template <bool FAST, bool FIRST>
-__device__ __forceinline__ void canny_group(const StripGeom &g, const WarpPlace &wp,
-		CannyThresholds thr, const WeakSink &ws, RowReader<FAST> &rd, RowWriter<FAST> &wr,
-		uint4 (&buf)[2], HRow (&hr)[3], GRow (&gr)[3])
-{
-	canny_step<FAST, FIRST, 0>(g, wp, thr, ws, rd, wr, buf, hr, gr);
-	canny_step<FAST, FIRST, 1>(g, wp, thr, ws, rd, wr, buf, hr, gr);
-	canny_step<FAST, FIRST, 2>(g, wp, thr, ws, rd, wr, buf, hr, gr);
-	canny_step<FAST, FIRST, 3>(g, wp, thr, ws, rd, wr, buf, hr, gr);
-	canny_step<FAST, FIRST, 4>(g, wp, thr, ws, rd, wr, buf, hr, gr);
-	canny_step<FAST, FIRST, 5>(g, wp, thr, ws, rd, wr, buf, hr, gr);
+	wr.put(g, wp.ye, res);
 }
 
 template <bool FAST>
@@ -414,16 +255,20 @@ __device__ __forceinline__ void canny_march(const uint32_t *__restrict__ in,
 	RowReader<FAST> rd;
 	RowWriter<FAST> wr;
 	rd.init(in, g, wp.ys - 2, wp.x0);
-	wr.init(out, g, wp.ys, wp.x0);
+	wr.init(out, g, wp.ys, wp.x0, wp.out_lane);
 	HRow hr[3];
 	GRow gr[3];
-	uint4 buf[2];
-	buf[0] = rd.next(g);
-	// gray rows ys-2 .. ys+rows_per_strip+1: rows_per_strip + 4 steps, a multiple of 6
-	const int groups = (g.rows_per_strip + 4) / 6;
-	canny_group<FAST, true>(g, wp, thr, ws, rd, wr, buf, hr, gr);
-	for (int k = 1; k < groups; k++)
-		canny_group<FAST, false>(g, wp, thr, ws, rd, wr, buf, hr, gr);
+	uint4 q[3];
+	q[0] = rd.next(g);
+	q[1] = rd.next(g);
+	q[2] = rd.next(g);
+	// gray rows ys-2 .. ys+rows_per_strip+1: rows_per_strip + 4 steps, a multiple of 3
+	const int steps = g.rows_per_strip + 4;
+	for (int s = 0; s < steps; s += 3) {
+		canny_step<FAST, 0>(g, wp, s, thr, ws, rd, wr, q, hr, gr);
+		canny_step<FAST, 1>(g, wp, s + 1, thr, ws, rd, wr, q, hr, gr);
+		canny_step<FAST, 2>(g, wp, s + 2, thr, ws, rd, wr, q, hr, gr);
+	}
 }
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
@@ -437,7 +282,7 @@ canny_classify_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ ou
 	const int npix = g.w * g.h;
 	const size_t page = (size_t)blockIdx.y * npix;
 	const WeakSink ws = { hdr, list, parent, (int)blockIdx.y * npix };
-	if (wp.interior)
+	if (g.aligned)
 		canny_march<true>(in + page, out + page, g, wp, thr, ws);
 	else
 		canny_march<false>(in + page, out + page, g, wp, thr, ws);
@@ -639,42 +484,6 @@ canny_hysteresis_kernel(uint32_t *out, PageGeom pg, int *list, int *parent,
 	}
 }
 
-// Strip height so that the whole grid is resident at once (one wave): a grid
-// a few blocks over the resident capacity would run a second, nearly empty
-// wave and double the kernel time.
-template <typename Kernel>
-StripGeom make_geom(Kernel kern, const uint32_t *in, const uint32_t *out, int w, int h,
-		int pages, int halo_rows, int y_begin = 0, int y_end = -1)
-{
-	StripGeom g;
-	g.w = w;
-	g.h = h;
-	g.y_begin = y_begin;
-	g.y_end = y_end < 0 ? h : y_end;
-	const int nrows = g.y_end - g.y_begin;
-	g.warp_cols = (w + kWarpCols - 1) / kWarpCols;
-	int blocks_per_sm = 0;
-	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern,
-			kWarpsPerBlock * 32, 0) != cudaSuccess || blocks_per_sm < 1) {
-		cudaGetLastError();
-		blocks_per_sm = 4;
-	}
-	const long resident_warps = (long)sm_count() * blocks_per_sm * kWarpsPerBlock;
-	long strips = resident_warps / ((long)g.warp_cols * pages);
-	if (strips < 1)
-		strips = 1;
-	// rows + halo_rows steps per strip must be a whole number of 6-step groups
-	int rows = (int)((nrows + strips - 1) / strips);
-	int groups = (rows + halo_rows + 5) / 6;
-	if (groups < 3)
-		groups = 3;
-	rows = groups * 6 - halo_rows;
-	g.rows_per_strip = rows;
-	g.strips = (nrows + rows - 1) / rows;
-	g.aligned = (w % 4 == 0) && (((uintptr_t)in | (uintptr_t)out) % 16 == 0);
-	return g;
-}
-
 }  // namespace
 
 int launch_sobel(const uint32_t *in, uint32_t *out, int w, int h, int pages,
@@ -684,7 +493,7 @@ int launch_sobel(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 		y_end = h;
 	if (y_begin < 0 || y_begin >= y_end || y_end > h)
 		return fail(PF_B200_EINVAL, "sobel: bad row range [%d, %d) of %d", y_begin, y_end, h);
-	const StripGeom g = make_geom(sobel_kernel, in, out, w, h, pages, 2, y_begin, y_end);
+	const StripGeom g = make_geom(sobel_kernel, in, out, w, h, pages, 2, y_begin, y_end, 3);
 	const int warps = g.warp_cols * g.strips;
 	dim3 grid((warps + kWarpsPerBlock - 1) / kWarpsPerBlock, pages);
 	sobel_kernel<<<grid, kWarpsPerBlock * 32, 0, st>>>(in, out, g);
@@ -736,7 +545,7 @@ int launch_canny(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 		uint32_t *pout = out + (size_t)p0 * npix;
 		int *parent = list + (size_t)np * npix;
 		PFB_CUDA(cudaMemsetAsync(hdr, 0, 256, st));
-		const StripGeom g = make_geom(canny_classify_kernel, pin, pout, w, h, np, 4);
+		const StripGeom g = make_geom(canny_classify_kernel, pin, pout, w, h, np, 4, 0, -1, 3);
 		const int warps = g.warp_cols * g.strips;
 		dim3 grid((warps + kWarpsPerBlock - 1) / kWarpsPerBlock, np);
 		canny_classify_kernel<<<grid, kWarpsPerBlock * 32, 0, st>>>(pin, pout, g, thr,

@@ -11,7 +11,9 @@
 // true convolution with the kernel centre at size/2, taps outside the page
 // skipped.  Skipping a tap and adding +0.0 give the same double, so the
 // kernels zero-pad.
-#include "pf_common.cuh"
+#include <cstdlib>
+
+#include "pf_march.cuh"
 
 namespace pfb {
 
@@ -137,19 +139,11 @@ gaussian_march_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ ou
 	}
 }
 
-// Any tap count: one thread per pixel, N*N multiply-adds, same rounding order.
-__global__ void __launch_bounds__(kBlock)
-gaussian_generic_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
-		int w, int h, int y_begin, const Taps tp)
+// One pixel by the reference's exact operation order (N*N multiply-adds, no
+// FMA): the slow path of the fast kernel below and the body of the generic one.
+__device__ __noinline__ uint32_t gaussian_exact_pixel(const uint32_t *__restrict__ in,
+		int w, int h, int x, int y, const double *__restrict__ t, int n)
 {
-	const int n = tp.n;
-	const int x = blockIdx.x * kBlock + threadIdx.x;
-	const int y = y_begin + blockIdx.y;
-	if (x >= w)
-		return;
-	const size_t page = (size_t)blockIdx.z * w * h;
-	in += page;
-	out += page;
 	const int c0 = n / 2;
 	double acc[3] = { 0.0, 0.0, 0.0 };
 	bool first_row = true;
@@ -165,14 +159,14 @@ gaussian_generic_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ 
 			if (ix < 0 || ix >= w)
 				continue;
 			const uint32_t p = __ldg(row + ix);
-			const double t = tp.t[kx];
+			const double tk = t[kx];
 			for (int c = 0; c < 3; c++) {
-				const double m = __dmul_rn(u8_to_double((p >> (8 * c)) & 0xFF), t);
+				const double m = __dmul_rn(u8_to_double((p >> (8 * c)) & 0xFF), tk);
 				hv[c] = first ? m : __dadd_rn(hv[c], m);
 			}
 			first = false;
 		}
-		const double tv = tp.t[ky];
+		const double tv = t[ky];
 		for (int c = 0; c < 3; c++) {
 			const double m = __dmul_rn(hv[c], tv);
 			acc[c] = first_row ? m : __dadd_rn(acc[c], m);
@@ -182,7 +176,181 @@ gaussian_generic_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ 
 	uint32_t rgba = 0xFF000000u;
 	for (int c = 0; c < 3; c++)
 		rgba |= (uint32_t)min(trunc_nonneg(acc[c]), 255) << (8 * c);
-	out[(size_t)y * w + x] = rgba;
+	return rgba;
+}
+
+// Any tap count: one thread per pixel.
+__global__ void __launch_bounds__(kBlock)
+gaussian_generic_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
+		int w, int h, int y_begin, const Taps tp)
+{
+	const int x = blockIdx.x * kBlock + threadIdx.x;
+	const int y = y_begin + blockIdx.y;
+	if (x >= w)
+		return;
+	const size_t page = (size_t)blockIdx.z * w * h;
+	out[page + (size_t)y * w + x] = gaussian_exact_pixel(in + page, w, h, x, y, tp.t, tp.n);
+}
+
+// ---------------------------------------------------------------------------
+// Fast kernel for 3 and 5 taps: FP64 with FMA, exactness by a guard band.
+//
+// The reference rounds after every multiply and every add; the result is then
+// truncated to an integer, so its last bits only matter when the value lies
+// within rounding distance of an integer (which happens for whole regions of
+// flat colour, where every value is "k * sum(taps)^2").  This kernel computes
+// the same sums with FMAs (about half the FP64 instructions; error ~1e-13),
+// truncates with one round-toward-zero add that also exposes 21 fraction
+// bits, and hands a pixel to gaussian_exact_pixel only when a channel lies
+// within 2e-6 of an integer.  Results are bit-identical to the reference.
+// ---------------------------------------------------------------------------
+
+constexpr double kFracMagic = 2147483648.0;        // 2^31: ulp 2^-21 for values < 2^31
+constexpr uint32_t kFracMask = (1u << 21) - 1;
+constexpr uint32_t kFracGuard = 4;                 // 4 * 2^-21 ~ 2e-6
+
+template <int N>
+struct GaussRing {
+	double h[N][12];       // horizontal sums of the last N rows: 4 columns x 3 channels
+};
+
+// Step J of N (s = steps since the top of the strip): the row at the head of
+// the N-deep row queue is filtered horizontally into ring slot J, its queue
+// slot is refilled with the row N below, and the output row C rows above
+// leaves.  The first N-1 steps of a strip only fill the ring.
+template <int N, int J>
+__device__ __forceinline__ void gauss_step(const uint32_t *__restrict__ in,
+		const StripGeom &g, const WarpPlace &wp, int s, const double (&t)[N],
+		RowReader<true> &rd, RowWriter<true> &wr, uint4 (&q)[N], GaussRing<N> &ring)
+{
+	constexpr int C = N / 2;
+	const uint4 cur = q[J];
+	q[J] = rd.next(g);
+	// pixels x0-C .. x0+3+C: own four plus C from each neighbouring lane
+	uint32_t px[4 + 2 * C];
+	px[C] = cur.x;
+	px[C + 1] = cur.y;
+	px[C + 2] = cur.z;
+	px[C + 3] = cur.w;
+	if (C >= 1) {
+		px[C - 1] = __shfl_up_sync(kFull, cur.w, 1);
+		px[C + 4] = __shfl_down_sync(kFull, cur.x, 1);
+	}
+	if (C >= 2) {
+		px[C - 2] = __shfl_up_sync(kFull, cur.z, 1);
+		px[C + 5] = __shfl_down_sync(kFull, cur.y, 1);
+	}
+	double v[4 + 2 * C][3];
+#pragma unroll
+	for (int i = 0; i < 4 + 2 * C; i++) {
+#pragma unroll
+		for (int c = 0; c < 3; c++) {
+			const uint32_t b = (px[i] >> (8 * c)) & 0xFF;
+			// own pixels through the conversion unit, neighbours through the
+			// FP64 pipe (2^52 trick): keeps both pipes below saturation
+			v[i][c] = (i >= C && i < C + 4) ? (double)b : u8_to_double(b);
+		}
+	}
+	double (&hrow)[12] = ring.h[J];
+#pragma unroll
+	for (int o = 0; o < 4; o++) {
+#pragma unroll
+		for (int c = 0; c < 3; c++) {
+			// tap k multiplies pixel x - k + C, i.e. px index o + 2C - k
+			double a = v[o + 2 * C][c] * t[0];
+#pragma unroll
+			for (int k = 1; k < N; k++)
+				a = fma(v[o + 2 * C - k][c], t[k], a);
+			hrow[o * 3 + c] = a;
+		}
+	}
+	if (s < N - 1)
+		return;
+	const int y = wp.ys + s - (N - 1);
+	uint32_t res[4];
+	bool risky = false;
+#pragma unroll
+	for (int o = 0; o < 4; o++) {
+		uint32_t rgba = 0xFF000000u;
+#pragma unroll
+		for (int c = 0; c < 3; c++) {
+			// tap k multiplies row y - k + C, which sits in slot (J - k) mod N
+			double a = ring.h[J][o * 3 + c] * t[0];
+#pragma unroll
+			for (int k = 1; k < N; k++)
+				a = fma(ring.h[(J - k + N) % N][o * 3 + c], t[k], a);
+			const uint32_t fx = (uint32_t)__double2loint(__dadd_rz(a, kFracMagic));
+			const uint32_t fr = fx & kFracMask;
+			risky |= (fr < kFracGuard) | (fr > kFracMask - kFracGuard);
+			rgba |= min(fx >> 21, 255u) << (8 * c);
+		}
+		res[o] = rgba;
+	}
+	if (risky && wr.lane_out && y < wp.ye) {
+		// some channel of some of the four pixels is too close to an integer
+		// to trust: redo the four in the reference's exact order
+		double tt[N];
+#pragma unroll
+		for (int k = 0; k < N; k++)
+			tt[k] = t[k];
+#pragma unroll
+		for (int o = 0; o < 4; o++)
+			res[o] = gaussian_exact_pixel(in, g.w, g.h, wp.x0 + o, y, tt, N);
+	}
+	wr.put(g, wp.ye, res);
+}
+
+template <int N, int J>
+struct GaussSteps {
+	static __device__ __forceinline__ void run(const uint32_t *__restrict__ in,
+			const StripGeom &g, const WarpPlace &wp, int s, const double (&t)[N],
+			RowReader<true> &rd, RowWriter<true> &wr, uint4 (&q)[N], GaussRing<N> &ring)
+	{
+		gauss_step<N, J>(in, g, wp, s + J, t, rd, wr, q, ring);
+		GaussSteps<N, J + 1>::run(in, g, wp, s, t, rd, wr, q, ring);
+	}
+};
+
+template <int N>
+struct GaussSteps<N, N> {
+	static __device__ __forceinline__ void run(const uint32_t *__restrict__,
+			const StripGeom &, const WarpPlace &, int, const double (&)[N],
+			RowReader<true> &, RowWriter<true> &, uint4 (&)[N], GaussRing<N> &)
+	{
+	}
+};
+
+// Needs rows that can be read as uint4 (width a multiple of 4, aligned pages);
+// other shapes take the strict kernel.
+template <int N>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+gaussian_fast_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
+		const StripGeom g, const TapsN<N> tp)
+{
+	constexpr int C = N / 2;
+	const WarpPlace wp = place_warp(g);
+	if (!wp.valid)
+		return;
+	const size_t page = (size_t)blockIdx.y * g.w * g.h;
+	in += page;
+	out += page;
+	double t[N];
+#pragma unroll
+	for (int k = 0; k < N; k++)
+		t[k] = tp.t[k];
+	RowReader<true> rd;
+	RowWriter<true> wr;
+	rd.init(in, g, wp.ys - (N - 1 - C), wp.x0);
+	wr.init(out, g, wp.ys, wp.x0, wp.out_lane);
+	GaussRing<N> ring;
+	uint4 q[N];
+#pragma unroll
+	for (int i = 0; i < N; i++)
+		q[i] = rd.next(g);
+	// rows_per_strip + N - 1 steps per strip, a multiple of N
+	const int steps = g.rows_per_strip + N - 1;
+	for (int s = 0; s < steps; s += N)
+		GaussSteps<N, 0>::run(in, g, wp, s, t, rd, wr, q, ring);
 }
 
 int strips_for(int w_threads_blocks, int h, int pages, int blocks_per_sm, int min_rows)
@@ -203,6 +371,20 @@ int strips_for(int w_threads_blocks, int h, int pages, int blocks_per_sm, int mi
 // ---------------------------------------------------------------------------
 // launchers
 // ---------------------------------------------------------------------------
+
+template <int N>
+static void launch_gaussian_fast(const uint32_t *in, uint32_t *out, int w, int h,
+		int pages, const Taps &taps, cudaStream_t st, int y_begin, int y_end)
+{
+	TapsN<N> tp;
+	for (int k = 0; k < N; k++)
+		tp.t[k] = taps.t[k];
+	const StripGeom g = make_geom(gaussian_fast_kernel<N>, in, out, w, h, pages, N - 1,
+			y_begin, y_end, N);
+	const int warps = g.warp_cols * g.strips;
+	dim3 grid((warps + kWarpsPerBlock - 1) / kWarpsPerBlock, pages);
+	gaussian_fast_kernel<N><<<grid, kWarpsPerBlock * 32, 0, st>>>(in, out, g, tp);
+}
 
 template <int N>
 static void launch_gaussian_n(const uint32_t *in, uint32_t *out, int w, int h,
@@ -228,6 +410,18 @@ int launch_gaussian(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 		return fail(PF_B200_EINVAL, "gaussian: bad row range [%d, %d) of %d", y_begin, y_end, h);
 	if (taps.n < 1 || taps.n > kMaxTaps)
 		return fail(PF_B200_EINVAL, "gaussian: nb_stddev must be in 1..%d", kMaxTaps);
+	// PF_B200_GAUSS_STRICT=1 keeps the all-strict kernel for 3 and 5 taps too
+	static const bool strict_env = getenv("PF_B200_GAUSS_STRICT") && atoi(getenv("PF_B200_GAUSS_STRICT"));
+	const bool strict = strict_env || (w % 4 != 0) || (((uintptr_t)in | (uintptr_t)out) % 16 != 0);
+	switch (strict ? 0 : taps.n) {
+	case 3: launch_gaussian_fast<3>(in, out, w, h, pages, taps, st, y_begin, y_end); break;
+	case 5: launch_gaussian_fast<5>(in, out, w, h, pages, taps, st, y_begin, y_end); break;
+	default: break;
+	}
+	if (!strict && (taps.n == 3 || taps.n == 5)) {
+		PFB_CUDA(cudaGetLastError());
+		return PF_B200_OK;
+	}
 	switch (taps.n) {
 	case 3: launch_gaussian_n<3>(in, out, w, h, pages, taps, st, y_begin, y_end); break;
 	case 5: launch_gaussian_n<5>(in, out, w, h, pages, taps, st, y_begin, y_end); break;
