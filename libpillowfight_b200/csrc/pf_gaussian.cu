@@ -179,6 +179,42 @@ __device__ __noinline__ uint32_t gaussian_exact_pixel(const uint32_t *__restrict
 	return rgba;
 }
 
+// The same for a compile-time tap count, with all N*N loads issued before the
+// arithmetic (one memory latency instead of N): the fast kernel's slow path.
+template <int N>
+__device__ __noinline__ uint32_t gaussian_exact_pixel_n(const uint32_t *__restrict__ in,
+		int w, int h, int x, int y, const double *__restrict__ t)
+{
+	constexpr int C = N / 2;
+	uint32_t p[N][N];
+#pragma unroll
+	for (int ky = 0; ky < N; ky++) {
+		const int iy = y - ky + C;
+#pragma unroll
+		for (int kx = 0; kx < N; kx++) {
+			const int ix = x - kx + C;
+			p[ky][kx] = (iy >= 0 && iy < h && ix >= 0 && ix < w) ? __ldg(in + (size_t)iy * w + ix) : 0u;
+		}
+	}
+	// a tap outside the page is skipped by the reference; adding +0.0 instead
+	// gives the same double (all terms are >= +0)
+	uint32_t rgba = 0xFF000000u;
+#pragma unroll
+	for (int c = 0; c < 3; c++) {
+		double acc = 0.0;
+#pragma unroll
+		for (int ky = 0; ky < N; ky++) {
+			double hv = 0.0;
+#pragma unroll
+			for (int kx = 0; kx < N; kx++)
+				hv = __dadd_rn(hv, __dmul_rn(u8_to_double((p[ky][kx] >> (8 * c)) & 0xFF), t[kx]));
+			acc = __dadd_rn(acc, __dmul_rn(hv, t[ky]));
+		}
+		rgba |= (uint32_t)min(trunc_nonneg(acc), 255) << (8 * c);
+	}
+	return rgba;
+}
+
 // Any tap count: one thread per pixel.
 __global__ void __launch_bounds__(kBlock)
 gaussian_generic_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
@@ -268,7 +304,7 @@ __device__ __forceinline__ void gauss_step(const uint32_t *__restrict__ in,
 		return;
 	const int y = wp.ys + s - (N - 1);
 	uint32_t res[4];
-	bool risky = false;
+	unsigned risky = 0;           // bit o: pixel o has a channel too close to an integer
 #pragma unroll
 	for (int o = 0; o < 4; o++) {
 		uint32_t rgba = 0xFF000000u;
@@ -280,22 +316,23 @@ __device__ __forceinline__ void gauss_step(const uint32_t *__restrict__ in,
 			for (int k = 1; k < N; k++)
 				a = fma(ring.h[(J - k + N) % N][o * 3 + c], t[k], a);
 			const uint32_t fx = (uint32_t)__double2loint(__dadd_rz(a, kFracMagic));
-			const uint32_t fr = fx & kFracMask;
-			risky |= (fr < kFracGuard) | (fr > kFracMask - kFracGuard);
+			// (fr + guard) mod 2^21 < 2*guard  <=>  fr within guard of 0 or of 2^21
+			if (((fx + kFracGuard) & kFracMask) < 2 * kFracGuard)
+				risky |= 1u << o;
 			rgba |= min(fx >> 21, 255u) << (8 * c);
 		}
 		res[o] = rgba;
 	}
 	if (risky && wr.lane_out && y < wp.ye) {
-		// some channel of some of the four pixels is too close to an integer
-		// to trust: redo the four in the reference's exact order
+		// redo those pixels in the reference's exact operation order
 		double tt[N];
 #pragma unroll
 		for (int k = 0; k < N; k++)
 			tt[k] = t[k];
 #pragma unroll
 		for (int o = 0; o < 4; o++)
-			res[o] = gaussian_exact_pixel(in, g.w, g.h, wp.x0 + o, y, tt, N);
+			if (risky & (1u << o))
+				res[o] = gaussian_exact_pixel_n<N>(in, g.w, g.h, wp.x0 + o, y, tt);
 	}
 	wr.put(g, wp.ye, res);
 }

@@ -81,3 +81,21 @@ def test_argument_errors_are_reported(pf):
     assert rc == _capi.PF_B200_EINVAL
     code, msg = _capi.last_error()
     assert code == _capi.PF_B200_EINVAL and "NULL" in msg
+
+
+def test_reference_module_name_and_signatures(pf):
+    """`import pillowfight` exposes the four functions with upstream's
+    parameter names and defaults."""
+    import inspect
+    import pillowfight
+    want = {
+        "ace": [("img_in", inspect.Parameter.empty), ("slope", 10), ("limit", 1000),
+                ("samples", 100), ("seed", None)],
+        "gaussian": [("img_in", inspect.Parameter.empty), ("sigma", 2.0), ("nb_stddev", 5)],
+        "sobel": [("img_in", inspect.Parameter.empty)],
+        "canny": [("img_in", inspect.Parameter.empty)],
+    }
+    for name, params in want.items():
+        sig = inspect.signature(getattr(pillowfight, name))
+        got = [(p.name, p.default) for p in sig.parameters.values()]
+        assert got == params, (name, got)
