@@ -36,11 +36,11 @@ constexpr int kMaxRowsPerThread = 8; // P: pixels a thread carries (same column)
 #endif
 constexpr int kAceUnroll = PF_ACE_UNROLL;   // unroll of the sample loop
 constexpr int kChunk = 512;         // samples staged in shared memory at a time
-constexpr double kBias = 4224.0;    // 4096 + 128: value spliced around c
+constexpr double kBase = 4096.0;    // 2^12: the clamp result is spliced in as kBase + (c + L)
 
 struct SampleEntry {
 	int sx;
-	uint32_t bias[3];   // (1152 - s_c) in both 16-bit halves
+	uint32_t bias[3];   // (L - s_c) as a signed 16-bit value in both halves (fast path)
 };
 
 struct AceShared {
@@ -58,24 +58,21 @@ __device__ __forceinline__ double rsqrt_approx(double x)
 	return y;
 }
 
-// 2/sqrt(d2) to ~2^-43 (NEWTON) or 1/sqrt(d2) to ~2^-22 relative; a common
-// factor on the weights cancels in the score.
+// 2/sqrt(d2) to ~2^-43 (NEWTON) or 1/sqrt(d2) to ~2^-20 relative; a common
+// factor on the weights cancels in the score.  MUFU.RSQ64H reads and writes
+// only the high word of a double; without the Newton step the low word is
+// left as it is (d2's own low word, at most 2^-20 of the value) rather than
+// zeroed with an extra instruction -- the same order as the unit's own error,
+// and the same weight feeds numerator and denominator.
 template <bool NEWTON>
 __device__ __forceinline__ double weight_of(double d2)
 {
 	const double y0 = rsqrt_approx(d2);
 	if (!NEWTON)
-		return y0;
+		return __hiloint2double(__double2hiint(y0), __double2loint(d2));
 	const double t = d2 * y0;
 	const double q = fma(-t, y0, 3.0);
 	return y0 * q;
-}
-
-__device__ __forceinline__ uint32_t umin16x2(uint32_t a, uint32_t b)
-{
-	uint32_t d;
-	asm("min.u16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
-	return d;
 }
 
 __device__ __forceinline__ void atomic_min_double(double *addr, double v)
@@ -192,7 +189,7 @@ __device__ __noinline__ void stage_samples(AceShared &sh, const AceConst &cs,
 #pragma unroll
 			for (int c = 0; c < 3; c++) {
 				const uint32_t v = (px >> (8 * c)) & 0xFF;
-				sh.tbl[dst].bias[c] = FAST ? (1152u - v) * 0x00010001u : v;
+				sh.tbl[dst].bias[c] = FAST ? (((uint32_t)(cs.clamp_l - (int)v)) & 0xFFFFu) * 0x00010001u : v;
 			}
 		}
 		for (int wv = warp; wv < kWarps; wv++) {
@@ -235,8 +232,9 @@ __device__ __forceinline__ void accumulate_sample(const AceShared &sh, int j, in
 		for (int g = 0; g < P / 2; g++) {
 #pragma unroll
 			for (int c = 0; c < 3; c++) {
-				// clamp(p - s) for two pixels: one fused add+max (VIADDMNMX), one min
-				const uint32_t t = umin16x2(__viaddmax_u16x2(pk[g][c], se.bias[c], lo2), hi2);
+				// clamp(p - s, -L, L) + L for two pixels in one instruction:
+				// VIADDMNMX.S16x2.RELU = max(min(p + (L - s), 2L), 0) per half
+				const uint32_t t = __viaddmin_s16x2_relu(pk[g][c], se.bias[c], hi2);
 				const double va = __hiloint2double(
 						(int)__byte_perm(t, 0x40B00000u, 0x7604), 0);
 				const double vb = __hiloint2double(
@@ -292,10 +290,11 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 		}
 	}
 
-	const uint32_t lo2 = (uint32_t)(1152 - cs.clamp_l) * 0x00010001u;
-	const uint32_t hi2 = (uint32_t)(1152 + cs.clamp_l) * 0x00010001u;
+	const uint32_t lo2 = 0u;
+	const uint32_t hi2 = (uint32_t)(2 * cs.clamp_l) * 0x00010001u;
 	const double too_close2 = (double)cs.too_close2;
-	const double top_value = FAST ? kBias + (double)cs.clamp_l : cs.limit;
+	const double top_value = FAST ? kBase + 2.0 * (double)cs.clamp_l : cs.limit;
+	const double mid_value = kBase + (double)cs.clamp_l;     // the value spliced in for c = 0
 
 	double mn[3] = { DBL_MAX, DBL_MAX, DBL_MAX };
 	double mx[3] = { -DBL_MAX, -DBL_MAX, -DBL_MAX };
@@ -374,8 +373,8 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 					double s = (acc[r][c] == top[r]) ? 1.0 : acc[r][c] * inv;
 					if (!(top[r] > 0.0))    // every sample skipped: 0/0 like the reference
 						s = __longlong_as_double(0x7FF8000000000000LL);
-					if (FAST)   // back from the biased value (kBias + c) / (kBias + L)
-						s = fma(top_value, s, -kBias) * cs.ratio;
+					if (FAST)   // back from (kBase + L + c) / (kBase + 2L) to c / L
+						s = fma(top_value, s, -mid_value) * cs.ratio;
 					scores[c * plane + o] = s;
 					if (s < mn[c]) mn[c] = s;     // NaN never enters
 					if (s > mx[c]) mx[c] = s;
