@@ -340,6 +340,102 @@ def test_device_batch_entry_points(gpu, oracle):
         assert np.array_equal(c5[i].cpu().numpy(), rc)
 
 
+@pytest.mark.parametrize("w,h", [(5, 4), (33, 17), (124, 61), (128, 40), (257, 129), (620, 300)])
+def test_no_writes_outside_the_output_page(gpu, oracle, w, h):
+    """compute-sanitizer is not available on this pool, so: guard bands of a
+    known pattern in front of and behind every output buffer (and the Canny
+    scratch) must come back untouched, and results must still match."""
+    import torch
+    from libpillowfight_b200 import _capi
+    lib, chk = _capi.lib, _capi.check
+    dev = torch.device("cuda:0")
+    page = uniform_random_page(w, h, seed=3 * w + h)
+    guard = 4096                                   # bytes, keeps 256-byte alignment
+    n = w * h * 4
+
+    def guarded(nbytes):
+        buf = torch.full((guard + nbytes + guard,), 0xA5, dtype=torch.uint8, device=dev)
+        return buf, buf[guard:guard + nbytes]
+
+    def intact(buf, nbytes):
+        return bool((buf[:guard] == 0xA5).all()) and bool((buf[guard + nbytes:] == 0xA5).all())
+
+    tin = torch.from_numpy(page).to(dev)
+    st = torch.cuda.current_stream().cuda_stream
+    for name in ("gaussian", "sobel", "canny", "ace"):
+        obuf, out = guarded(n)
+        if name == "gaussian":
+            chk(lib.pf_b200_dev_gaussian(tin.data_ptr(), out.data_ptr(), w, h, 2.0, 5, st))
+            ref = oracle.gaussian(page, 2.0, 5)
+        elif name == "sobel":
+            chk(lib.pf_b200_dev_sobel(tin.data_ptr(), out.data_ptr(), w, h, st))
+            ref = oracle.sobel(page)
+        elif name == "canny":
+            sbytes = lib.pf_b200_canny_scratch_bytes(w, h)
+            sbuf, scratch = guarded(sbytes)
+            chk(lib.pf_b200_dev_canny(tin.data_ptr(), out.data_ptr(), w, h, 1,
+                                      scratch.data_ptr(), sbytes, st))
+            ref = oracle.canny(page)
+        else:
+            if h < 5:
+                continue
+            xy = oracle.ace_draw_samples(10, w, h, 5)
+            from libpillowfight_b200.distributed import xy_tensor
+            txy = xy_tensor(xy, dev)
+            sc_buf, sc = guarded(3 * w * h * 8)
+            mm = torch.empty(6, dtype=torch.float64, device=dev)
+            chk(lib.pf_b200_dev_ace_minmax_init(mm.data_ptr(), st))
+            chk(lib.pf_b200_dev_ace_scores(tin.data_ptr(), w, h, 0, h, txy.data_ptr(), 10,
+                                           10.0, 1000.0, sc.data_ptr(), mm.data_ptr(), st))
+            chk(lib.pf_b200_dev_ace_scale(sc.data_ptr(), mm.data_ptr(), w, h, out.data_ptr(), st))
+            ref = oracle.ace_with_samples(page, xy, 10.0, 1000.0)
+        torch.cuda.synchronize()
+        assert intact(obuf, n), "%s wrote outside its output page" % name
+        if name == "canny":
+            assert intact(sbuf, sbytes), "canny wrote outside its scratch"
+        if name == "ace":
+            assert intact(sc_buf, 3 * w * h * 8), "ace wrote outside its score planes"
+            assert_fp_parity(out.cpu().numpy().reshape(h, w, 4), ref, "ace guarded")
+        else:
+            assert np.array_equal(out.cpu().numpy().reshape(h, w, 4), ref), name
+
+
+def test_concurrent_host_threads(gpu, oracle):
+    """Each host thread has its own context (stream, buffers): four threads
+    calling different entry points at once get the right answers."""
+    import threading
+    page = synthetic_page(400, 300, 14)
+    xy_seed = 9
+    refs = {"gaussian": oracle.gaussian(page, 2.0, 5), "sobel": oracle.sobel(page),
+            "canny": oracle.canny(page)}
+    errors = []
+
+    def work(name):
+        try:
+            for _ in range(5):
+                got = getattr(gpu, name)(page)
+                if not np.array_equal(got, refs[name]):
+                    errors.append(name)
+        except Exception as e:   # noqa: BLE001
+            errors.append("%s: %r" % (name, e))
+
+    def work_ace():
+        try:
+            a = gpu.ace(page, 10, 1000, 20, seed=xy_seed)
+            b = gpu.ace(page, 10, 1000, 20, seed=xy_seed)
+            if not np.array_equal(a, b):
+                errors.append("ace not reproducible")
+        except Exception as e:   # noqa: BLE001
+            errors.append("ace: %r" % (e,))
+
+    threads = [threading.Thread(target=work, args=(n,)) for n in refs] + [threading.Thread(target=work_ace)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+
+
 def test_pil_images_round_trip(gpu, oracle):
     from PIL import Image
     page = synthetic_page(90, 70, 12)
