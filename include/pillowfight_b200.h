@@ -95,6 +95,46 @@ void pf_sobel(const struct pf_bitmap *in, struct pf_bitmap *out);
 void pf_canny(const struct pf_bitmap *in, struct pf_bitmap *out);
 
 /* ------------------------------------------------------------------------ */
+/* The pf_dbl_matrix level of the same path (upstream util.c / _gaussian.c / */
+/* _sobel.c): host matrices in, newly allocated host matrices out, as in the */
+/* reference -- the caller releases them with pf_dbl_matrix_free().  On a    */
+/* CUDA failure the returned matrices have values == NULL and size 0 x 0.    */
+/* ------------------------------------------------------------------------ */
+
+struct pf_gradient_matrixes {
+	struct pf_dbl_matrix g_x;
+	struct pf_dbl_matrix g_y;
+	struct pf_dbl_matrix intensity;   /* hypot(g_x, g_y) */
+	struct pf_dbl_matrix direction;   /* atan2(g_y, g_x) */
+};
+
+/* replaces upstream util.c: pf_dbl_matrix_new / pf_dbl_matrix_free (host
+ * memory, zero-initialised). */
+struct pf_dbl_matrix pf_dbl_matrix_new(int x, int y);
+void pf_dbl_matrix_free(struct pf_dbl_matrix *matrix);
+
+/* The reference's 3x3 Sobel kernels (upstream _sobel.c). */
+extern const struct pf_dbl_matrix g_pf_kernel_sobel_x;
+extern const struct pf_dbl_matrix g_pf_kernel_sobel_y;
+
+/* replaces upstream util.c: pf_dbl_matrix_convolution().  Kernels of up to
+ * 64 taps. */
+struct pf_dbl_matrix pf_dbl_matrix_convolution(const struct pf_dbl_matrix *img,
+		const struct pf_dbl_matrix *kernel);
+
+/* replaces upstream _gaussian.c: pf_gaussian_on_matrix(): horizontal then
+ * vertical 1-D convolution with nb_stddev taps. */
+struct pf_dbl_matrix pf_gaussian_on_matrix(const struct pf_dbl_matrix *in,
+		double sigma, int nb_stddev);
+
+/* replaces upstream _sobel.c: pf_sobel_on_matrix(): g_x, g_y by convolution
+ * with the given kernels, optionally blurred (gaussian_stddev > 0), then
+ * intensity and direction. */
+struct pf_gradient_matrixes pf_sobel_on_matrix(const struct pf_dbl_matrix *in,
+		const struct pf_dbl_matrix *kernel_x, const struct pf_dbl_matrix *kernel_y,
+		double gaussian_sigma, int gaussian_stddev);
+
+/* ------------------------------------------------------------------------ */
 /* Status-returning variants of the same calls (0 = success, else PF_B200_E*) */
 /* ------------------------------------------------------------------------ */
 

@@ -32,6 +32,17 @@ class PfBitmap(ctypes.Structure):
     _fields_ = [("size", _Size), ("pixels", ctypes.c_void_p)]
 
 
+class PfMatrix(ctypes.Structure):
+    """struct pf_dbl_matrix"""
+    _fields_ = [("size", _Size), ("values", ctypes.POINTER(ctypes.c_double))]
+
+
+class PfGradients(ctypes.Structure):
+    """struct pf_gradient_matrixes"""
+    _fields_ = [("g_x", PfMatrix), ("g_y", PfMatrix), ("intensity", PfMatrix),
+                ("direction", PfMatrix)]
+
+
 if not os.path.exists(SO_PATH):
     raise ImportError(
         "libpillowfight_b200.so is not built (expected at %s). Build it with "
@@ -54,6 +65,12 @@ SIGNATURES = {
     "pf_gaussian": (None, [_bp, _bp, ctypes.c_double, ctypes.c_int]),
     "pf_sobel": (None, [_bp, _bp]),
     "pf_canny": (None, [_bp, _bp]),
+    "pf_dbl_matrix_new": (PfMatrix, [ctypes.c_int, ctypes.c_int]),
+    "pf_dbl_matrix_free": (None, [ctypes.POINTER(PfMatrix)]),
+    "pf_dbl_matrix_convolution": (PfMatrix, [ctypes.POINTER(PfMatrix), ctypes.POINTER(PfMatrix)]),
+    "pf_gaussian_on_matrix": (PfMatrix, [ctypes.POINTER(PfMatrix), ctypes.c_double, ctypes.c_int]),
+    "pf_sobel_on_matrix": (PfGradients, [ctypes.POINTER(PfMatrix), ctypes.POINTER(PfMatrix),
+                                         ctypes.POINTER(PfMatrix), ctypes.c_double, ctypes.c_int]),
     "pf_b200_last_error": (ctypes.c_int, []),
     "pf_b200_last_error_string": (ctypes.c_char_p, []),
     "pf_b200_device_count": (ctypes.c_int, []),

@@ -15,7 +15,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libpillowfight_b200.so")
-SOURCES = ["pf_capi.cu", "pf_gaussian.cu", "pf_edges.cu", "pf_ace.cu"]
+SOURCES = ["pf_capi.cu", "pf_gaussian.cu", "pf_edges.cu", "pf_ace.cu", "pf_matrix.cu"]
 HEADERS = [os.path.join(CSRC, "pf_common.cuh"),
            os.path.join(HERE, "..", "include", "pillowfight_b200.h")]
 

@@ -252,7 +252,7 @@ static int check_bitmaps(const struct pf_bitmap *in, const struct pf_bitmap *out
 // upstream _gaussian.c: generate_gaussian_1d_kernel -- the taps are made on
 // the host with glibc's exp/sqrt, in the reference's operation order, so the
 // device only ever multiplies and adds.
-static int make_taps(double sigma, int nb_stddev, Taps &t)
+int make_taps(double sigma, int nb_stddev, Taps &t)
 {
 	if (nb_stddev < 1 || nb_stddev > kMaxTaps)
 		return fail(PF_B200_EINVAL, "gaussian: nb_stddev %d outside 1..%d", nb_stddev, kMaxTaps);

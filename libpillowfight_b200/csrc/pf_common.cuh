@@ -33,6 +33,9 @@ struct Taps {
 	double t[kMaxTaps];
 };
 
+// upstream _gaussian.c generate_gaussian_1d_kernel, on the host (pf_capi.cu)
+int make_taps(double sigma, int nb_stddev, Taps &t);
+
 // ---- stencil launchers (pf_gaussian.cu, pf_edges.cu); asynchronous on `st` --
 // [y_begin, y_end) restricts the OUTPUT rows (y_end < 0: the whole page);
 // input rows up to the stencil's reach outside that range are read, so they
@@ -52,6 +55,12 @@ size_t canny_scratch_bytes(int w, int h);
 int launch_canny(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 		CannyThresholds thr, void *scratch, size_t scratch_bytes,
 		cudaStream_t st);
+
+// ---- pf_dbl_matrix launchers (pf_matrix.cu) ------------------------------
+int launch_matrix_convolution(const double *img, double *out, int w, int h,
+		const double *kernel, int nx, int ny, cudaStream_t st);
+int launch_gradient_polar(const double *gx, const double *gy, double *intensity,
+		double *direction, size_t n, cudaStream_t st);
 
 // ---- ACE launchers (pf_ace.cu) -------------------------------------------
 struct AceParams {

@@ -28,6 +28,10 @@ class Matrix(ctypes.Structure):
     _fields_ = [("size", _Size), ("values", ctypes.POINTER(ctypes.c_double))]
 
 
+class Gradients(ctypes.Structure):
+    _fields_ = [("g_x", Matrix), ("g_y", Matrix), ("intensity", Matrix), ("direction", Matrix)]
+
+
 def build(force=False):
     """Compile libpf_oracle.so with oracle/Makefile (gcc)."""
     src = os.path.join(_HERE, "pf_oracle.c")
@@ -70,6 +74,10 @@ def lib():
                                                 ctypes.c_double, ctypes.c_int]
         _lib.pfo_gaussian_on_matrix.restype = Matrix
         _lib.pfo_matrix_free.argtypes = [ctypes.POINTER(Matrix)]
+        _lib.pfo_convolution.argtypes = [ctypes.POINTER(Matrix), ctypes.POINTER(Matrix)]
+        _lib.pfo_convolution.restype = Matrix
+        _lib.pfo_sobel_on_matrix.argtypes = [ctypes.POINTER(Matrix)]
+        _lib.pfo_sobel_on_matrix.restype = Gradients
     return _lib
 
 
@@ -122,6 +130,31 @@ def gaussian_on_matrix(mat, sigma=2.0, nb_stddev=5):
     out = np.ctypeslib.as_array(r.values, shape=mat.shape).copy()
     lib().pfo_matrix_free(ctypes.byref(r))
     return out
+
+
+def _matrix(mat):
+    mat = np.ascontiguousarray(mat, dtype=np.float64)
+    return mat, Matrix(_Size(mat.shape[1], mat.shape[0]),
+                       mat.ctypes.data_as(ctypes.POINTER(ctypes.c_double)))
+
+
+def _take(r):
+    out = np.ctypeslib.as_array(r.values, shape=(r.size.y, r.size.x)).copy()
+    lib().pfo_matrix_free(ctypes.byref(r))
+    return out
+
+
+def convolution(mat, kernel):
+    a, ma = _matrix(mat)
+    k, mk = _matrix(kernel)
+    return _take(lib().pfo_convolution(ctypes.byref(ma), ctypes.byref(mk)))
+
+
+def sobel_on_matrix(mat):
+    """-> (g_x, g_y, intensity, direction) with the reference's 3x3 kernels"""
+    a, ma = _matrix(mat)
+    g = lib().pfo_sobel_on_matrix(ctypes.byref(ma))
+    return tuple(_take(m) for m in (g.g_x, g.g_y, g.intensity, g.direction))
 
 
 def sobel(img):
