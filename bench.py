@@ -399,7 +399,14 @@ def run_b200(args):
                 "peak_source": "pf_b200_fp64_peak_tflops(): DFMA probe run in this process "
                                "(MEASURED_PEAKS.json has no FP64 figure)",
                 "algorithmic_flops_per_launch": ace_flops, "kernel_ms": ms_ace_scores,
-                "pairs_not_skipped": kept, "pairs_skipped": skipped}
+                "pairs_not_skipped": kept, "pairs_skipped": skipped,
+                # what the kernel itself issues: 1 DADD + 4 DFMA per pair it processes
+                "kernel_fp64_flops_per_launch": kept * 9.0,
+                "fp64_pipe_frac": (kept * 9.0 / (ms_ace_scores * 1e-3) / 1e12) / fp64_peak
+                if fp64_peak > 0 else None,
+                "note": "achieved/frac count the REFERENCE's 22 FP64 operations per pair (DESIGN.md 3); "
+                        "the kernel retires them with 5 FP64 instructions per pair, so frac can exceed "
+                        "the pipe's utilisation (fp64_pipe_frac) and 1.0"}
     stencils = {}
     for k in (Stage.GAUSS, Stage.SOBEL, Stage.CANNY):
         gbs = 8.0 * npix / (ms_cold[k] * 1e-3) / 1e9

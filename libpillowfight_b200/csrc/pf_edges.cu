@@ -140,28 +140,44 @@ sobel_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
 // One gradient row for the lane's 4 columns plus the two neighbouring columns.
 struct GRow {
 	int m[6];          // g_x^2 + g_y^2 at columns x0-1 .. x0+4, 0 outside the page
-	int sector[4];     // 0: E-W, 1: SE-NW, 2: N-S, 3: SW-NE neighbours
+	int sector[4];     // 0: E-W, 1: SE-NW, 2: N-S, 3: SW-NE neighbours (valid when `any`)
+	bool any;          // some pixel of the warp's row segment reaches the low threshold
 };
 
 // `row_inside`: the gradient row is inside the page; for FAST launches it
-// already includes "this lane's columns are inside the page".
+// already includes "this lane's columns are inside the page".  The direction
+// sectors are only needed where a pixel can survive the low threshold, and on
+// a document most 120-pixel row segments hold no such pixel: the warp votes
+// and skips them.
 template <bool FAST>
 __device__ __forceinline__ void grow_from_hrows(const HRow &a, const HRow &b,
-		const HRow &c, bool row_inside, int x0, int w, GRow &o)
+		const HRow &c, bool row_inside, int x0, int w, int weak_min, GRow &o)
 {
+	int gxv[4], gyv[4], gx2[4], gy2[4];
+	bool cand = false;
 #pragma unroll
 	for (int i = 0; i < 4; i++) {
-		const int gx = c.hd[i] + 2 * b.hd[i] + a.hd[i];
-		const int gy = a.hs[i] - c.hs[i];
-		const int gx2 = gx * gx, gy2 = gy * gy;
+		gxv[i] = c.hd[i] + 2 * b.hd[i] + a.hd[i];
+		gyv[i] = a.hs[i] - c.hs[i];
+		gx2[i] = gxv[i] * gxv[i];
+		gy2[i] = gyv[i] * gyv[i];
 		const int x = x0 + i;
 		const bool inside = FAST ? row_inside : (row_inside && x >= 0 && x < w);
-		o.m[i + 1] = inside ? gx2 + gy2 : 0;
-		// |angle| < 22.5 deg  <=>  (|gx|+|gy|)^2 < 2 gx^2  <=>  2|gx gy| < gx^2 - gy^2
-		const int q = gx * gy;
-		const int p2 = 2 * abs(q);
-		const int d = gx2 - gy2;
-		o.sector[i] = (p2 < d) ? 0 : ((p2 < -d) ? 2 : ((q >= 0) ? 1 : 3));
+		o.m[i + 1] = inside ? gx2[i] + gy2[i] : 0;
+		cand |= o.m[i + 1] >= weak_min;
+	}
+	o.any = __any_sync(kFull, cand);
+	if (o.any) {
+#pragma unroll
+		for (int i = 0; i < 4; i++) {
+			// |angle| < 22.5 deg  <=>  (|gx|+|gy|)^2 < 2 gx^2  <=>  2|gx gy| < gx^2 - gy^2
+			const int q = gxv[i] * gyv[i];
+			const int p2 = 2 * abs(q);
+			const int d = gx2[i] - gy2[i];
+			// bit 1: the neighbours are not on this row's E-W line / the main
+			// diagonal; bit 0 picks within each half
+			o.sector[i] = (p2 < d) ? 0 : ((p2 < -d) ? 2 : ((q >= 0) ? 1 : 3));
+		}
 	}
 	o.m[0] = __shfl_up_sync(kFull, o.m[4], 1);
 	o.m[5] = __shfl_down_sync(kFull, o.m[1], 1);
@@ -190,35 +206,38 @@ __device__ __forceinline__ void canny_step(const StripGeom &g, const WarpPlace &
 	const int r = wp.ys - 2 + s;
 	const int grow = r - 1;
 	grow_from_hrows<FAST>(hr[(J + 1) % 3], hr[(J + 2) % 3], hr[J],
-			grow >= 0 && grow < g.h && (!FAST || rd.lane_in), wp.x0, g.w, gr[J]);
+			grow >= 0 && grow < g.h && (!FAST || rd.lane_in), wp.x0, g.w, thr.weak_min, gr[J]);
 	if (s < 4)
 		return;
 	const int y = r - 2;
 	const GRow &up = gr[(J + 1) % 3], &mid = gr[(J + 2) % 3], &dn = gr[J];
 	const bool owns = wr.lane_out && y < wp.ye;
-	uint32_t res[4];
+	uint32_t res[4] = { kBlack, kBlack, kBlack, kBlack };
 	int nweak = 0;
+	if (mid.any) {
 #pragma unroll
-	for (int i = 0; i < 4; i++) {
-		const int m = mid.m[i + 1];
-		const int sc = mid.sector[i];
-		const int ew = max(mid.m[i], mid.m[i + 2]);
-		const int ns = max(up.m[i + 1], dn.m[i + 1]);
-		const int d1 = max(dn.m[i + 2], up.m[i]);       // (x+1,y+1), (x-1,y-1)
-		const int d3 = max(dn.m[i], up.m[i + 2]);       // (x-1,y+1), (x+1,y-1)
-		const int nb = (sc == 0) ? ew : ((sc == 2) ? ns : ((sc == 1) ? d1 : d3));
-		uint32_t v = kBlack;
-		if (m >= nb && m >= thr.weak_min) {
-			v = kWhite;
-			if (m < thr.strong_min && owns && (FAST || wp.x0 + i < g.w)) {
-				v = 0u;          // weak: index filled in below
-				nweak++;
+		for (int i = 0; i < 4; i++) {
+			const int m = mid.m[i + 1];
+			const int sc = mid.sector[i];
+			const int ew = max(mid.m[i], mid.m[i + 2]);
+			const int ns = max(up.m[i + 1], dn.m[i + 1]);
+			const int d1 = max(dn.m[i + 2], up.m[i]);       // (x+1,y+1), (x-1,y-1)
+			const int d3 = max(dn.m[i], up.m[i + 2]);       // (x-1,y+1), (x+1,y-1)
+			// two-level select on the sector's bits (no jump table)
+			const int lo = (sc & 1) ? d1 : ew;
+			const int hi = (sc & 1) ? d3 : ns;
+			const int nb = (sc & 2) ? hi : lo;
+			if (m >= nb && m >= thr.weak_min) {
+				res[i] = kWhite;
+				if (m < thr.strong_min && owns && (FAST || wp.x0 + i < g.w)) {
+					res[i] = 0u;          // weak: index filled in below
+					nweak++;
+				}
 			}
 		}
-		res[i] = v;
 	}
 	// warp-aggregated append of this row's weak pixels to the work list
-	if (__ballot_sync(kFull, nweak > 0)) {
+	if (mid.any && __ballot_sync(kFull, nweak > 0)) {
 		const int lane = threadIdx.x & 31;
 		int pre = nweak;
 #pragma unroll
