@@ -262,7 +262,7 @@ __device__ __forceinline__ void accumulate_sample(const AceShared &sh, int j, in
 #define PF_ACE_MINBLOCKS_P8 3
 #endif
 template <bool FAST, bool NEWTON, int P>
-__global__ void __launch_bounds__(kAceBlock, (P == 2) ? 8 : ((P == 4) ? 6 : PF_ACE_MINBLOCKS_P8))
+__global__ void __launch_bounds__(kAceBlock, (P == 2) ? 8 : ((P == 4) ? 6 : ((P == 6) ? 4 : PF_ACE_MINBLOCKS_P8)))
 ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
 		const AceConst cs, double *__restrict__ scores, double *__restrict__ minmax)
 {
@@ -533,8 +533,11 @@ int launch_ace_scores(const uint32_t *in, const int *samples_xy,
 	const bool fast = l >= 1.0 && l <= 127.0 && l == floor(l) && p.slope * l == p.limit;
 	cs.clamp_l = fast ? (int)l : 0;
 
-	static const int tile_env = getenv("PF_B200_ACE_TILE_ROWS") ? atoi(getenv("PF_B200_ACE_TILE_ROWS")) : 16;
-	cs.tile_rows = (tile_env >= 8 && tile_env % 8 == 0) ? tile_env : 16;
+	static const int tile_env = getenv("PF_B200_ACE_TILE_ROWS") ? atoi(getenv("PF_B200_ACE_TILE_ROWS")) : 0;
+	static const int rows_env0 = getenv("PF_B200_ACE_ROWS") ? atoi(getenv("PF_B200_ACE_ROWS")) : 8;
+	const int rows_p = (fast && (rows_env0 == 2 || rows_env0 == 4 || rows_env0 == 6)) ? rows_env0 : (fast ? 8 : 4);
+	// a tile is a whole number of row groups
+	cs.tile_rows = (tile_env >= rows_p && tile_env % rows_p == 0) ? tile_env : (rows_p == 6 ? 18 : 16);
 	dim3 grid((p.w + kAceBlock - 1) / kAceBlock,
 			(p.row_end - 1) / cs.tile_rows - p.row_begin / cs.tile_rows + 1);
 	const size_t smem = sizeof(AceShared);
@@ -556,7 +559,8 @@ int launch_ace_scores(const uint32_t *in, const int *samples_xy,
 			: rows_env == 8 ? ace_scores_kernel<true, true, 8> : ace_scores_kernel<true, true, 4>;
 	else
 		kern = rows_env == 2 ? ace_scores_kernel<true, false, 2>
-			: rows_env == 8 ? ace_scores_kernel<true, false, 8> : ace_scores_kernel<true, false, 4>;
+			: rows_env == 8 ? ace_scores_kernel<true, false, 8>
+			: rows_env == 6 ? ace_scores_kernel<true, false, 6> : ace_scores_kernel<true, false, 4>;
 	PFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 	kern<<<grid, kAceBlock, smem, st>>>(in, samples_xy, cs, scores, minmax);
 	PFB_CUDA(cudaGetLastError());
