@@ -236,14 +236,16 @@ gaussian_generic_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ 
 // within rounding distance of an integer (which happens for whole regions of
 // flat colour, where every value is "k * sum(taps)^2").  This kernel computes
 // the same sums with FMAs (about half the FP64 instructions; error ~1e-13),
-// truncates with one round-toward-zero add that also exposes 21 fraction
+// truncates with one round-toward-zero add that also exposes 24 fraction
 // bits, and hands a pixel to gaussian_exact_pixel only when a channel lies
 // within 2e-6 of an integer.  Results are bit-identical to the reference.
 // ---------------------------------------------------------------------------
 
-constexpr double kFracMagic = 2147483648.0;        // 2^31: ulp 2^-21 for values < 2^31
-constexpr uint32_t kFracMask = (1u << 21) - 1;
-constexpr uint32_t kFracGuard = 4;                 // 4 * 2^-21 ~ 2e-6
+// v + 2^28 rounded toward zero leaves floor(v * 2^24) in the low word for
+// 0 <= v < 256: the integer part is the top byte, 24 fraction bits below it.
+constexpr double kFracMagic = 268435456.0;         // 2^28
+constexpr uint32_t kFracMask = (1u << 24) - 1;
+constexpr uint32_t kFracGuard = 32;                // 32 * 2^-24 ~ 2e-6
 
 template <int N>
 struct GaussRing {
@@ -281,7 +283,7 @@ __device__ __forceinline__ void gauss_step(const uint32_t *__restrict__ in,
 	for (int i = 0; i < 4 + 2 * C; i++) {
 #pragma unroll
 		for (int c = 0; c < 3; c++) {
-			const uint32_t b = (px[i] >> (8 * c)) & 0xFF;
+			const uint32_t b = __byte_perm(px[i], 0u, 0x4440 + c);    // byte c, zero-extended
 			// own pixels through the conversion unit, neighbours through the
 			// FP64 pipe (2^52 trick): keeps both pipes below saturation
 			v[i][c] = (i >= C && i < C + 4) ? (double)b : u8_to_double(b);
@@ -307,7 +309,7 @@ __device__ __forceinline__ void gauss_step(const uint32_t *__restrict__ in,
 	unsigned risky = 0;           // bit o: pixel o has a channel too close to an integer
 #pragma unroll
 	for (int o = 0; o < 4; o++) {
-		uint32_t rgba = 0xFF000000u;
+		uint32_t fx[3];
 #pragma unroll
 		for (int c = 0; c < 3; c++) {
 			// tap k multiplies row y - k + C, which sits in slot (J - k) mod N
@@ -315,13 +317,15 @@ __device__ __forceinline__ void gauss_step(const uint32_t *__restrict__ in,
 #pragma unroll
 			for (int k = 1; k < N; k++)
 				a = fma(ring.h[(J - k + N) % N][o * 3 + c], t[k], a);
-			const uint32_t fx = (uint32_t)__double2loint(__dadd_rz(a, kFracMagic));
-			// (fr + guard) mod 2^21 < 2*guard  <=>  fr within guard of 0 or of 2^21
-			if (((fx + kFracGuard) & kFracMask) < 2 * kFracGuard)
-				risky |= 1u << o;
-			rgba |= min(fx >> 21, 255u) << (8 * c);
+			fx[c] = (uint32_t)__double2loint(__dadd_rz(a, kFracMagic));
 		}
-		res[o] = rgba;
+		// (fraction + guard) mod 2^24 < 2*guard  <=>  within guard of an integer
+		const uint32_t nearest = min(min((fx[0] + kFracGuard) & kFracMask,
+				(fx[1] + kFracGuard) & kFracMask), (fx[2] + kFracGuard) & kFracMask);
+		if (nearest < 2 * kFracGuard)
+			risky |= 1u << o;
+		// the three top bytes are R, G, B (the sums never reach 256)
+		res[o] = __byte_perm(__byte_perm(fx[0], fx[1], 0x4473), fx[2], 0x4710) | 0xFF000000u;
 	}
 	if (risky && wr.lane_out && y < wp.ye) {
 		// redo those pixels in the reference's exact operation order
