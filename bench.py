@@ -495,6 +495,43 @@ def run_b200(args):
             "scaling": "strong"}
         del big
 
+        # ---- extras: page batch through the stencil chain (BASELINE.json config 5:
+        # 512 pages over 8 GPUs = 64 pages per GPU; pages are independent, no collective)
+        nbp = 64
+        batch = torch.empty((nbp, h, w, 4), dtype=torch.uint8, device=dev)
+        for i in range(nbp):
+            batch[i] = pages[i % N_SETS]
+        bg, bs, bc = torch.empty_like(batch), torch.empty_like(batch), torch.empty_like(batch)
+        chain = CudaChain()
+
+        def chain_pass():
+            chain.gaussian(batch, bg)
+            chain.sobel(bg, bs)
+            chain.canny(batch, bc, pages_per_launch=8)
+
+        chain_pass()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        torch.cuda.synchronize()
+        a.record()
+        for _ in range(3):
+            chain_pass()
+        b.record()
+        torch.cuda.synchronize()
+        barrier()
+        tb = torch.tensor([a.elapsed_time(b) / 3], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tb, op=dist.ReduceOp.MAX)
+        extras["chain_batch"] = {
+            "workload": "%d A4 pages per GPU (%d in all) through pf_b200_dev_gaussian_batch -> "
+                        "sobel_batch, and pf_b200_dev_canny on the pages; device-resident, "
+                        "pages sharded over the GPUs, no collective" % (nbp, nbp * world),
+            "ms": float(tb.item()),
+            "mpx_s": world * nbp * npix / (float(tb.item()) * 1e-3) / 1e6,
+            "hbm_gbs_of_24B_per_px": world * nbp * npix * 24 / (float(tb.item()) * 1e-3) / 1e9,
+            "scaling": "weak"}
+        del batch, bg, bs, bc
+
     # ---- CPU baseline (rank 0, N = 1 only) ------------------------------------
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -284,9 +284,8 @@ __device__ __forceinline__ void gauss_step(const uint32_t *__restrict__ in,
 #pragma unroll
 		for (int c = 0; c < 3; c++) {
 			const uint32_t b = __byte_perm(px[i], 0u, 0x4440 + c);    // byte c, zero-extended
-			// own pixels through the conversion unit, neighbours through the
-			// FP64 pipe (2^52 trick): keeps both pipes below saturation
-			v[i][c] = (i >= C && i < C + 4) ? (double)b : u8_to_double(b);
+			// through the conversion unit (XU): the FP64 pipe is the busy one
+			v[i][c] = (double)b;
 		}
 	}
 	double (&hrow)[12] = ring.h[J];
@@ -312,12 +311,17 @@ __device__ __forceinline__ void gauss_step(const uint32_t *__restrict__ in,
 		uint32_t fx[3];
 #pragma unroll
 		for (int c = 0; c < 3; c++) {
-			// tap k multiplies row y - k + C, which sits in slot (J - k) mod N
-			double a = ring.h[J][o * 3 + c] * t[0];
+			// tap k multiplies row y - k + C, which sits in slot (J - k) mod N.
+			// The sum is built on top of the 2^28 offset (each partial sum is
+			// then rounded to 2^-24, N-1 times: far inside the guard band) and
+			// the last FMA rounds toward zero, which is the truncation.
+			double a = fma(ring.h[J][o * 3 + c], t[0], kFracMagic);
 #pragma unroll
-			for (int k = 1; k < N; k++)
+			for (int k = 1; k < N - 1; k++)
 				a = fma(ring.h[(J - k + N) % N][o * 3 + c], t[k], a);
-			fx[c] = (uint32_t)__double2loint(__dadd_rz(a, kFracMagic));
+			if (N > 1)
+				a = __fma_rz(ring.h[(J - (N - 1) + N) % N][o * 3 + c], t[N - 1], a);
+			fx[c] = (uint32_t)__double2loint(a);
 		}
 		// (fraction + guard) mod 2^24 < 2*guard  <=>  within guard of an integer
 		const uint32_t nearest = min(min((fx[0] + kFracGuard) & kFracMask,
