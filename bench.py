@@ -130,6 +130,25 @@ class ClockSampler:
                 "power_w_max": max(power) if power else None}
 
 
+def bind_to_gpu_cpus(index):
+    """Run this rank on the CPUs next to its GPU (and so allocate its pinned
+    pages on that NUMA node): matters for the end-to-end number when several
+    ranks stream pages over PCIe at once."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * i + b for i, wd in enumerate(words) for b in range(64) if (wd >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        cpus &= allowed
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return sorted(cpus)
+    except Exception:      # noqa: BLE001  (no NVML, containers without the call, ...)
+        return None
+
+
 def load_json(path):
     try:
         with open(path) as f:
@@ -261,6 +280,7 @@ def run_b200(args):
                          "(use --impl reference for the CPU baseline)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    bind_to_gpu_cpus(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
