@@ -28,7 +28,10 @@ def assert_fp_parity(got, ref, what):
 
 
 SIZES = [(1, 1), (2, 3), (5, 4), (7, 9), (33, 17), (64, 48), (130, 67), (257, 129),
-         (256, 200), (620, 877)]
+         (256, 200), (620, 877),
+         # widths that are multiples of 4 take the vectorised kernels: tiny and
+         # one-warp-column / many-warp-column shapes
+         (4, 1), (8, 3), (12, 2), (128, 1), (120, 7), (124, 19), (244, 5), (1000, 3)]
 
 
 @pytest.fixture(scope="module")
@@ -217,6 +220,41 @@ def test_ace_band_split_equals_whole(gpu, oracle):
     torch.cuda.synchronize()
     assert torch.equal(mm, mm2)
     assert torch.equal(whole, split)
+
+
+def test_empty_and_bad_arguments(gpu):
+    """Zero-sized bitmaps, mismatched sizes, no samples, samples outside the
+    page, tap counts out of range: an error, never a crash or a silent no-op."""
+    from libpillowfight_b200 import _capi
+    lib = _capi.lib
+    buf = np.zeros((4, 4, 4), dtype=np.uint8)
+
+    def bm(w, h, arr):
+        b = _capi.PfBitmap()
+        b.size.x, b.size.y, b.pixels = w, h, arr.ctypes.data
+        return b
+
+    for w, h in ((0, 4), (4, 0), (-1, 4)):
+        b = bm(w, h, buf)
+        assert lib.pf_b200_sobel(ctypes.byref(b), ctypes.byref(b)) == _capi.PF_B200_EINVAL
+        assert lib.pf_b200_canny(ctypes.byref(b), ctypes.byref(b)) == _capi.PF_B200_EINVAL
+        assert lib.pf_b200_gaussian(ctypes.byref(b), ctypes.byref(b), 2.0, 5) == _capi.PF_B200_EINVAL
+    a, b = bm(4, 4, buf), bm(4, 3, buf)
+    assert lib.pf_b200_sobel(ctypes.byref(a), ctypes.byref(b)) == _capi.PF_B200_EINVAL
+    for n in (0, -3, 64, 1000):
+        assert lib.pf_b200_gaussian(ctypes.byref(a), ctypes.byref(a), 2.0, n) == _capi.PF_B200_EINVAL
+    xy = np.array([1, 1, 9, 1], dtype=np.int32)      # second sample outside a 4 x 4 page
+    xyp = xy.ctypes.data_as(ctypes.POINTER(ctypes.c_int))
+    assert lib.pf_b200_ace(ctypes.byref(a), ctypes.byref(a), 2, xyp, 10.0, 1000.0) == _capi.PF_B200_EINVAL
+    assert lib.pf_b200_ace(ctypes.byref(a), ctypes.byref(a), 0, xyp, 10.0, 1000.0) == _capi.PF_B200_EINVAL
+    assert lib.pf_b200_ace(ctypes.byref(a), ctypes.byref(a), 1, xyp, -1.0, 1000.0) == _capi.PF_B200_EINVAL
+    with pytest.raises(gpu.PillowfightB200Error):
+        gpu.gaussian(buf, 2.0, 0)
+    # the void entry points report instead of crashing and leave `out` alone
+    out = np.full((4, 4, 4), 7, dtype=np.uint8)
+    bz, bo = bm(0, 0, buf), bm(0, 0, out)
+    lib.pf_apply_sobel(ctypes.byref(bz), ctypes.byref(bo))
+    assert lib.pf_b200_last_error() == _capi.PF_B200_EINVAL and (out == 7).all()
 
 
 def test_c_entry_points_and_aliases(gpu, oracle):
