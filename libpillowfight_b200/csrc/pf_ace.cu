@@ -13,12 +13,13 @@
 // so a common factor on w cancels.  The N samples are one table for the whole
 // page: a block gathers the sample pixels once into shared memory, and the
 // inner loop has no global loads at all.  Per pixel-sample pair the FP64 pipe
-// does: d^2 (1 add), one Newton step on MUFU.RSQ64H (3), three accumulating
-// FMAs and the weight sum (4).  The clamp runs on the integer pipe, two
-// pixels per instruction in 16-bit halves, and its result is spliced straight
-// into the high word of a double (4224 + c, exact), so no conversion
-// instruction is issued in the loop.  Samples whose skip circle contains the
-// whole tile are dropped per tile, those that cannot reach it skip the test.
+// does: d^2 (1 add), three accumulating FMAs and one for the denominator (4);
+// the weight is MUFU.RSQ64H's 1/sqrt (optionally one Newton step, 3 more).
+// The clamp is one integer instruction for two pixels (16-bit halves), and
+// its result is spliced straight into the high word of a double
+// (4096 + L + c, exact), so no conversion instruction is issued in the loop.
+// Samples whose skip circle contains the whole tile are dropped per tile,
+// those that cannot reach it skip the test.
 #include <cfloat>
 #include <cmath>
 #include <cstdlib>
@@ -209,7 +210,7 @@ __device__ __noinline__ void stage_samples(AceShared &sh, const AceConst &cs,
 template <bool FAST, bool NEWTON, bool TEST, int P>
 __device__ __forceinline__ void accumulate_sample(const AceShared &sh, int j, int x,
 		const uint32_t (&pix)[P], const uint32_t (&pk)[P / 2][3],
-		uint32_t lo2, uint32_t hi2, double too_close2, double top_value,
+		uint32_t hi2, double too_close2, double top_value,
 		double (&acc)[P][3], double (&top)[P])
 {
 	const SampleEntry se = sh.tbl[j];
@@ -290,7 +291,6 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 		}
 	}
 
-	const uint32_t lo2 = 0u;
 	const uint32_t hi2 = (uint32_t)(2 * cs.clamp_l) * 0x00010001u;
 	const double too_close2 = (double)cs.too_close2;
 	const double top_value = FAST ? kBase + 2.0 * (double)cs.clamp_l : cs.limit;
@@ -350,10 +350,10 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 			const int n_far = sh.n_far;
 #pragma unroll kAceUnroll
 			for (int j = 0; j < n_far; j++)
-				accumulate_sample<FAST, NEWTON, false, P>(sh, j, x, pix, pk, lo2, hi2,
+				accumulate_sample<FAST, NEWTON, false, P>(sh, j, x, pix, pk, hi2,
 						too_close2, top_value, acc, top);
 			for (int j = n_far; j < n_act; j++)
-				accumulate_sample<FAST, NEWTON, true, P>(sh, j, x, pix, pk, lo2, hi2,
+				accumulate_sample<FAST, NEWTON, true, P>(sh, j, x, pix, pk, hi2,
 						too_close2, top_value, acc, top);
 		}
 
