@@ -8,7 +8,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libpillowfight_b200.so")
+# PF_B200_LIBRARY: another build of the same library (kernel experiments)
+SO_PATH = os.environ.get("PF_B200_LIBRARY") or os.path.join(_HERE, "libpillowfight_b200.so")
 
 PF_B200_OK = 0
 PF_B200_EINVAL = 1
