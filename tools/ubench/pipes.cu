@@ -138,6 +138,32 @@ void run_mix(const char *name, K kern, int sms, double clk_ghz, int instr_per_it
 	cudaFree(sink);
 }
 
+
+// DFMA with three distinct register-pair operands per instruction (the ACE
+// pattern: fresh multiplicand, fresh accumulator), against the probe above
+// whose multiplier and addend never change.
+__global__ void k_dfma_distinct(double *sink, double a, double b)
+{
+	double v[CHAINS], x[CHAINS], y[CHAINS];
+	for (int i = 0; i < CHAINS; i++) {
+		v[i] = threadIdx.x + i;
+		x[i] = a + i * 1e-9;
+		y[i] = b + i;
+	}
+	for (int it = 0; it < ITERS; it++) {
+#pragma unroll
+		for (int i = 0; i < CHAINS; i++) {
+			asm volatile("fma.rn.f64 %0, %1, %2, %0;" : "+d"(v[i]) : "d"(x[i]), "d"(y[(i + 1) % CHAINS]));
+			asm volatile("fma.rn.f64 %0, %1, %2, %0;" : "+d"(v[i]) : "d"(x[(i + 3) % CHAINS]), "d"(y[i]));
+		}
+	}
+	double s = v[0];
+	for (int i = 1; i < CHAINS; i++)
+		s = s + v[i];
+	if (s == 123456789.0)
+		sink[0] = s;
+}
+
 template <typename T, typename K>
 void run(const char *name, K kern, T a, T b, int sms, double clk_ghz)
 {
@@ -181,6 +207,7 @@ int main()
 	run<int>("iadd", k_iadd, 3, 7, sms, ghz);
 	run<uint32_t>("lop3", k_lop3, 0x0f0f0f0fu, 0x33333333u, sms, ghz);
 	run<double>("dfma", k_dfma, 1.0000001, 1e-9, sms, ghz);
+	run<double>("dfma 3 operands", k_dfma_distinct, 1.0000001, 1e-9, sms, ghz);
 	run<double>("dadd", k_dadd, 1.5, -1.5, sms, ghz);
 	run<double>("dmul", k_dmul, 1.0000001, 0.9999999, sms, ghz);
 	run<double>("rsqrt64", k_rsq64, 0.0, 0.0, sms, ghz);
