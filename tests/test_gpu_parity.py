@@ -353,6 +353,10 @@ def test_streamed_paths_on_pinned_pages(gpu, oracle):
         src[:] = page
         _capi.check(lib.pf_b200_gaussian(ctypes.byref(b_src), ctypes.byref(b_src), 2.0, 5))
         assert np.array_equal(src, ref_g)
+        src[:] = page
+        _capi.check(lib.pf_b200_ace(ctypes.byref(b_src), ctypes.byref(b_src), 60,
+                                    xy.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), 10.0, 1000.0))
+        assert np.array_equal(src, dst)        # same as the out-of-place ACE above
     finally:
         lib.pf_b200_host_free(pin)
 
