@@ -82,13 +82,17 @@ def ace_sharded(page, xy, slope, limit, compute, group=None, src=0):
     band = compute.scale(scores, minmax)
     if world == 1:
         return band
+    out = torch.empty((h, w, 4), dtype=torch.uint8, device=page.device)
+    if h % world == 0:
+        # equal bands: gather straight into the result
+        dist.all_gather_into_tensor(out.view(-1), band.contiguous().view(-1), group=group)
+        return out
     # all-gather needs equal shapes: pad every band to the tallest
     max_rows = max(b1 - b0 for b0, b1 in bands)
     padded = torch.zeros((max_rows, w, 4), dtype=torch.uint8, device=page.device)
     padded[: band.shape[0]] = band
     gathered = torch.empty((world, max_rows, w, 4), dtype=torch.uint8, device=page.device)
     dist.all_gather_into_tensor(gathered.view(-1), padded.view(-1), group=group)
-    out = torch.empty((h, w, 4), dtype=torch.uint8, device=page.device)
     for r, (b0, b1) in enumerate(bands):
         out[b0:b1] = gathered[r, : b1 - b0]
     return out

@@ -94,8 +94,12 @@ def test_page_shards_partition_the_batch():
             assert seen == list(range(n))
 
 
-def test_ace_row_band_sharding_world2(tmp_path, oracle):
-    w, h, n = 64, 75, 12      # odd height: bands of 37 and 38 rows
+import pytest
+
+
+@pytest.mark.parametrize("h", [75, 76])     # bands of 37 + 38 rows (padded gather), and 38 + 38
+def test_ace_row_band_sharding_world2(tmp_path, oracle, h):
+    w, n = 64, 12
     port = _free_port()
     res = str(tmp_path / "out.npy")
     mp.spawn(_worker, args=(2, port, w, h, n, res), nprocs=2, join=True)
