@@ -233,21 +233,38 @@ int pf_b200_dev_gaussian_batch(const uint32_t *d_in, uint32_t *d_out,
 int pf_b200_dev_sobel_batch(const uint32_t *d_in, uint32_t *d_out,
 		int width, int height, int nb_pages, void *stream);
 
-/* ACE in two device passes so that row bands can be split across GPUs
- * (BASELINE.json config 4):
+/* ACE in device passes so that row bands can be split across GPUs
+ * (BASELINE.json config 4).  d_minmax is a block of
+ * pf_b200_ace_minmax_bytes(width, height) bytes on the device: doubles
+ * [0..2] minimum and [3..5] maximum of R, G, B over the accumulated scores,
+ * [6..8] and [9..11] the same over the scores pass 3 recomputed, then one
+ * entry per tile of the page (bookkeeping of the passes).
+ *   0. pf_b200_dev_ace_minmax_init: once per page and device.
  *   1. pf_b200_dev_ace_scores: for rows [row_begin, row_end) of the page,
  *      accumulate the per-pixel, per-channel scores into d_scores
  *      (3 doubles per pixel of the band: plane-major R, G, B, each
  *      (row_end-row_begin)*width doubles) and fold the band's per-channel
- *      minimum / maximum into d_minmax (6 doubles: min R,G,B then max R,G,B;
- *      initialise with pf_b200_dev_ace_minmax_init first).
- *   2. (multi-GPU only) all-reduce d_minmax: min over the first 3, max over
- *      the last 3.
- *   3. pf_b200_dev_ace_scale: rescale the band's scores to RGBA8 rows of
+ *      minimum / maximum into d_minmax.
+ *   2. (multi-GPU only) all-reduce d_minmax[0..5]: min over the first 3, max
+ *      over the last 3.
+ *   3. pf_b200_dev_ace_refine, same arguments as pass 1: the scores within
+ *      2^-15 of the page's range of either extreme are recomputed in the
+ *      reference's exact arithmetic (IEEE sqrt and divisions, sample order),
+ *      because the rescale turns the last bit of a score at the maximum into
+ *      the difference between 254 and 255.  Optional: without it the result
+ *      stays within +-1 of the reference's.
+ *   4. (multi-GPU only) all-reduce d_minmax[6..11] the same way.
+ *   5. pf_b200_dev_ace_scale: rescale the band's scores to RGBA8 rows of
  *      d_out_band ((row_end-row_begin)*width pixels).
  * d_samples: nb_samples * 2 ints (x, y) on the device.
- * upstream _ace.c: ace_thread_adjustment (pass 1), ace_thread_scaling (pass 3). */
-int pf_b200_dev_ace_minmax_init(double *d_minmax, void *stream);
+ * upstream _ace.c: ace_thread_adjustment (passes 1 and 3), ace_thread_scaling
+ * (pass 5). */
+size_t pf_b200_ace_minmax_bytes(int width, int height);
+int pf_b200_dev_ace_minmax_init(double *d_minmax, int width, int height, void *stream);
+int pf_b200_dev_ace_refine(const uint32_t *d_in, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, int nb_samples, double slope, double limit,
+		double *d_scores, double *d_minmax, void *stream);
 int pf_b200_dev_ace_scores(const uint32_t *d_in, int width, int height,
 		int row_begin, int row_end,
 		const int *d_samples, int nb_samples, double slope, double limit,

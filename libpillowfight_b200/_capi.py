@@ -93,8 +93,12 @@ SIGNATURES = {
                                                   ctypes.c_int, ctypes.c_double, ctypes.c_int, _vp]),
     "pf_b200_dev_sobel_batch": (ctypes.c_int, [_u32p, _u32p, ctypes.c_int, ctypes.c_int,
                                                ctypes.c_int, _vp]),
-    "pf_b200_dev_ace_minmax_init": (ctypes.c_int, [_vp, _vp]),
+    "pf_b200_ace_minmax_bytes": (ctypes.c_size_t, [ctypes.c_int, ctypes.c_int]),
+    "pf_b200_dev_ace_minmax_init": (ctypes.c_int, [_vp, ctypes.c_int, ctypes.c_int, _vp]),
     "pf_b200_dev_ace_scores": (ctypes.c_int, [_u32p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                              ctypes.c_int, _vp, ctypes.c_int, ctypes.c_double,
+                                              ctypes.c_double, _vp, _vp, _vp]),
+    "pf_b200_dev_ace_refine": (ctypes.c_int, [_u32p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                               ctypes.c_int, _vp, ctypes.c_int, ctypes.c_double,
                                               ctypes.c_double, _vp, _vp, _vp]),
     "pf_b200_dev_ace_scale": (ctypes.c_int, [_vp, _vp, ctypes.c_int, ctypes.c_int, _u32p, _vp]),

@@ -16,8 +16,10 @@
 // does: d^2 (1 add), three accumulating FMAs and one for the denominator (4);
 // the weight is MUFU.RSQ64H's 1/sqrt (optionally one Newton step, 3 more).
 // The clamp is one integer instruction for two pixels (16-bit halves), and
-// its result is spliced straight into the high word of a double
-// (4096 + L + c, exact), so no conversion instruction is issued in the loop.
+// its result u = c + L is spliced straight into the high word of a subnormal
+// double (u * 2^-1034, exact and linear in u), so no conversion instruction
+// is issued in the loop and the sums carry no bias: a pixel whose difference
+// to every sample is 0, +L or -L scores exactly 0, 1, -1 as in the reference.
 // Samples whose skip circle contains the whole tile are dropped per tile,
 // those that cannot reach it skip the test.
 #include <cfloat>
@@ -37,7 +39,21 @@ constexpr int kMaxRowsPerThread = 8; // P: pixels a thread carries (same column)
 #endif
 constexpr int kAceUnroll = PF_ACE_UNROLL;   // unroll of the sample loop
 constexpr int kChunk = 512;         // samples staged in shared memory at a time
-constexpr double kBase = 4096.0;    // 2^12: the clamp result is spliced in as kBase + (c + L)
+// The min/max block of a call: [0..2] min, [3..5] max of the scores as the
+// accumulation kernel computed them; [6..8], [9..11] the same over the scores
+// ace_refine_kernel recomputed; then 6 doubles per tile of the page-wide grid.
+constexpr int kMinmaxHead = 12;
+// A score within this fraction of the page's range of its minimum or maximum
+// is recomputed in the reference's own arithmetic.  The accumulation kernel's
+// weights are good to 2^-19, which bounds its error at 2^-18 of the range
+// (measured: 3e-7 on a range of 1.4, tests/test_gpu_parity.py).
+constexpr double kNearEps = 0x1p-15;
+// Squared distances are carried scaled by 2^-1000, so the weights come out of
+// the rsqrt unit scaled by 2^500: the clamp result u = c + L is spliced into
+// the mantissa of a SUBNORMAL double (value u * 2^-1034, linear in u with no
+// implicit leading one), and weight * value must land in the normal range.
+// The common factors cancel in the score.
+constexpr double kD2Scale = 0x1p-1000;
 
 struct SampleEntry {
 	int sx;
@@ -76,6 +92,19 @@ __device__ __forceinline__ double weight_of(double d2)
 	return y0 * q;
 }
 
+// 1/d to an ulp or two: the unit's 2^-20 estimate and two Newton steps.  The
+// quotients that must be exact (the ties) are decided by comparisons, not by
+// this; 0 gives NaN, which the caller replaces.
+__device__ __forceinline__ double reciprocal(double d)
+{
+	double y;
+	asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+	double e = fma(-d, y, 1.0);
+	y = fma(y, e, y);
+	e = fma(-d, y, 1.0);
+	return fma(y, e, y);
+}
+
 __device__ __forceinline__ void atomic_min_double(double *addr, double v)
 {
 	unsigned long long *a = reinterpret_cast<unsigned long long *>(addr);
@@ -100,6 +129,13 @@ __device__ __forceinline__ void atomic_max_double(double *addr, double v)
 			break;
 		old = seen;
 	}
+}
+
+// The exactly tied scores the reference produces (ace_scores_kernel: a pixel whose difference
+// to every sample is zero or saturates).
+__device__ __forceinline__ bool is_tie_score(double s)
+{
+	return s == 0.0 || s == 1.0 || s == -1.0;
 }
 
 struct AceConst {
@@ -215,7 +251,7 @@ __device__ __forceinline__ void accumulate_sample(const AceShared &sh, int j, in
 {
 	const SampleEntry se = sh.tbl[j];
 	const int dx = x - se.sx;
-	const double dx2 = (double)(dx * dx);
+	const double dx2 = (double)(dx * dx) * kD2Scale;
 	double wgt[P];
 #pragma unroll
 	for (int r = 0; r < P; r++) {
@@ -224,8 +260,11 @@ __device__ __forceinline__ void accumulate_sample(const AceShared &sh, int j, in
 		if (TEST && d2 < too_close2)
 			wv = 0.0;
 		wgt[r] = wv;
-		// the channel that saturates high on every sample: same FMA sequence
-		// as acc[], so a pixel that does saturate everywhere gets acc == top
+		// the channel that saturates high on every sample (u = 2L): same FMA
+		// sequence as acc[], so the ties the reference produces come out
+		// exactly: acc == top (saturated high everywhere), acc == top / 2
+		// (difference 0 everywhere: scaling every term by two commutes
+		// with every rounding) and acc == 0 (saturated low everywhere)
 		top[r] = fma(wv, top_value, top[r]);
 	}
 	if (FAST) {
@@ -236,10 +275,10 @@ __device__ __forceinline__ void accumulate_sample(const AceShared &sh, int j, in
 				// clamp(p - s, -L, L) + L for two pixels in one instruction:
 				// VIADDMNMX.S16x2.RELU = max(min(p + (L - s), 2L), 0) per half
 				const uint32_t t = __viaddmin_s16x2_relu(pk[g][c], se.bias[c], hi2);
-				const double va = __hiloint2double(
-						(int)__byte_perm(t, 0x40B00000u, 0x7604), 0);
-				const double vb = __hiloint2double(
-						(int)__byte_perm(t, 0x40B00000u, 0x7624), 0);
+				// byte -> bits 8..15 of the high word, exponent field 0:
+				// the subnormal u * 2^-1034, no conversion instruction
+				const double va = __hiloint2double((int)__byte_perm(t, 0u, 0x4404), 0);
+				const double vb = __hiloint2double((int)__byte_perm(t, 0u, 0x4424), 0);
 				acc[2 * g][c] = fma(wgt[2 * g], va, acc[2 * g][c]);
 				acc[2 * g + 1][c] = fma(wgt[2 * g + 1], vb, acc[2 * g + 1][c]);
 			}
@@ -292,9 +331,9 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 	}
 
 	const uint32_t hi2 = (uint32_t)(2 * cs.clamp_l) * 0x00010001u;
-	const double too_close2 = (double)cs.too_close2;
-	const double top_value = FAST ? kBase + 2.0 * (double)cs.clamp_l : cs.limit;
-	const double mid_value = kBase + (double)cs.clamp_l;     // the value spliced in for c = 0
+	const double too_close2 = (double)cs.too_close2 * kD2Scale;
+	// what a channel saturated high contributes per unit weight
+	const double top_value = FAST ? __hiloint2double((2 * cs.clamp_l) << 8, 0) : cs.limit;
 
 	double mn[3] = { DBL_MAX, DBL_MAX, DBL_MAX };
 	double mx[3] = { -DBL_MAX, -DBL_MAX, -DBL_MAX };
@@ -342,7 +381,7 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 #pragma unroll
 				for (int r = 0; r < P; r++) {
 					const int dy = y0 + r - sh.sy[j];
-					sh.dy2[j * P + r] = (double)(dy * dy);
+					sh.dy2[j * P + r] = (double)(dy * dy) * kD2Scale;
 				}
 			}
 			__syncthreads();
@@ -360,21 +399,28 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 		// score = sum(sat/dist) / sum(limit/dist).  `top` is the numerator of a
 		// channel saturated high on every sample, i.e. limit * sum(1/dist) up
 		// to the common factor, accumulated by the same FMA sequence as acc.
-		// The reference gets exactly 1.0 for every such pixel (numerator and
-		// denominator are the same sum); acc == top reproduces that tie.
+		// The reference gets exactly 1, 0 and -1 for a pixel whose difference
+		// to every sample saturates high, is zero, saturates low (flat page
+		// areas: large sets of tied scores, also at the extremes the rescale
+		// normalises with); the comparisons below reproduce those ties.
 #pragma unroll
 		for (int r = 0; r < P; r++) {
 			const int y = y0 + r;
 			if (y >= cs.row_begin && y < cs.row_end && y < tile_y1 && x < cs.w) {
 				const size_t o = (size_t)(y - cs.score_row0) * cs.w + x;
-				const double inv = 1.0 / top[r];
+				// FAST: acc holds sum(w (c + L)); c / L = (acc - top/2) / (top/2)
+				const bool live = top[r] > 0.0;    // else every sample skipped: 0/0
+				const double den = FAST ? 0.5 * top[r] : top[r];
+				const double inv = reciprocal(den);
 #pragma unroll
 				for (int c = 0; c < 3; c++) {
-					double s = (acc[r][c] == top[r]) ? 1.0 : acc[r][c] * inv;
-					if (!(top[r] > 0.0))    // every sample skipped: 0/0 like the reference
+					const double num = FAST ? acc[r][c] - den : acc[r][c];
+					const bool tie_hi = num == den, tie_lo = num == -den;
+					double s = num * inv;           // exactly 0 when num is
+					s = tie_hi ? 1.0 : s;
+					s = tie_lo ? -1.0 : s;
+					if (!live)              // NaN like the reference
 						s = __longlong_as_double(0x7FF8000000000000LL);
-					if (FAST)   // back from (kBase + L + c) / (kBase + 2L) to c / L
-						s = fma(top_value, s, -mid_value) * cs.ratio;
 					scores[c * plane + o] = s;
 					if (s < mn[c]) mn[c] = s;     // NaN never enters
 					if (s > mx[c]) mx[c] = s;
@@ -407,15 +453,224 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 		}
 		atomic_min_double(minmax + c, a);
 		atomic_max_double(minmax + 3 + c, b);
+		// and per tile of the page-wide grid (two bands may share a tile), for
+		// ace_refine_kernel to find the tiles that matter
+		double *tile = minmax + kMinmaxHead
+			+ 6 * ((size_t)(cs.row_begin / cs.tile_rows + blockIdx.y) * gridDim.x + blockIdx.x);
+		atomic_min_double(tile + c, a);
+		atomic_max_double(tile + 3 + c, b);
 	}
 }
 
-__global__ void ace_minmax_init_kernel(double *minmax)
+__global__ void ace_minmax_init_kernel(double *minmax, size_t n)
 {
-	if (threadIdx.x < 3)
-		minmax[threadIdx.x] = DBL_MAX;
-	else if (threadIdx.x < 6)
-		minmax[threadIdx.x] = -DBL_MAX;
+	for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+			i += (size_t)gridDim.x * blockDim.x)
+		minmax[i] = (i % 6 < 3) ? DBL_MAX : -DBL_MAX;
+}
+
+constexpr int kRefineThreads = 256;
+constexpr int kRefineSlab = 16;      // rows scanned before the candidates are worked off
+constexpr int kRefineTerms = 512;    // (candidate, sample) pairs whose terms are in flight
+constexpr int kRefineTable = 1024;   // samples kept in shared memory
+
+struct RefineShared {
+	double terms[kRefineTerms][4];
+	int sx[kRefineTable], sy[kRefineTable];
+	uint32_t spx[kRefineTable];
+	unsigned short cand[kRefineSlab * kAceBlock];
+	int wanted[kRefineThreads];
+	int n_wanted, n_cand;
+};
+
+// The terms one sample contributes to one pixel in the reference's own
+// arithmetic (upstream _ace.c, ace_thread_adjustment; oracle/pf_oracle.c
+// ace_adjust_rows): IEEE sqrt and divisions.  A skipped sample contributes
+// +0.0, which changes no sum.
+// (This code runs once or a few times per page, from a cold instruction
+// cache: one copy of it, loops not unrolled.)
+__device__ __forceinline__ void ace_exact_terms(const RefineShared &sh, bool table,
+		const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
+		const AceConst &cs, int x, int y, int k, double *t)
+{
+	int sx, sy;
+	uint32_t sp;
+	if (table) {
+		sx = sh.sx[k];
+		sy = sh.sy[k];
+		sp = sh.spx[k];
+	} else {
+		const int2 sxy = __ldg(reinterpret_cast<const int2 *>(samples_xy) + k);
+		sx = sxy.x;
+		sy = sxy.y;
+		sp = cs.sample_px ? __ldg(cs.sample_px + k) : __ldg(in + (size_t)sy * cs.w + sx);
+	}
+	const uint32_t p = __ldg(in + (size_t)y * cs.w + x);
+	const double ddx = (double)(x - sx), ddy = (double)(y - sy);
+	const double dist = __dsqrt_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)));
+	const bool skipped = dist < (double)(cs.h / 5);
+#pragma unroll 1
+	for (int c = 0; c < 4; c++) {
+		const int diff = (int)((p >> (8 * c)) & 0xFF) - (int)((sp >> (8 * c)) & 0xFF);
+		double v = __dmul_rn((double)diff, cs.slope);
+		if (v > cs.limit || c == 3)
+			v = cs.limit;
+		else if (v < -cs.limit)
+			v = -cs.limit;
+		t[c] = skipped ? 0.0 : __ddiv_rn(v, dist);
+	}
+}
+
+// Exact scores of the block's listed candidates sh.cand[0 .. n) (pixels of the
+// slab at (x_lo, ys)).  The whole block computes the terms -- one (candidate,
+// sample) pair per thread and round, that is where the time goes -- then four
+// threads per candidate add them up in sample order: that chain is the
+// reference's and cannot be split.
+__device__ __forceinline__ void ace_exact_candidates(RefineShared &sh, bool table,
+		const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
+		const AceConst &cs, int x_lo, int ys, int n,
+		double *__restrict__ scores, double *__restrict__ minmax)
+{
+	const int chunk = min(cs.nb_samples, kRefineTerms);      // samples per round
+	const int batch = kRefineTerms / chunk;                   // candidates per round
+	const size_t plane = (size_t)cs.score_plane;
+	for (int i0 = 0; i0 < n; i0 += batch) {
+		const int nb = min(batch, n - i0);
+		double acc = 0.0;
+		for (int k0 = 0; k0 < cs.nb_samples; k0 += chunk) {
+			const int kn = min(chunk, cs.nb_samples - k0);
+			for (int q = threadIdx.x; q < nb * kn; q += kRefineThreads) {
+				const int ci = q / kn, j = q - ci * kn;
+				const int cd = sh.cand[i0 + ci];
+				ace_exact_terms(sh, table, in, samples_xy, cs, x_lo + cd % kAceBlock,
+						ys + cd / kAceBlock, k0 + j, sh.terms[q]);
+			}
+			__syncthreads();
+			if (threadIdx.x < 4 * nb) {
+				const double (*tm)[4] = sh.terms + (threadIdx.x >> 2) * kn;
+				const int a = threadIdx.x & 3;
+#pragma unroll 8
+				for (int j = 0; j < kn; j++)
+					acc = __dadd_rn(acc, tm[j][a]);
+			}
+			__syncthreads();
+		}
+		// threads 4i .. 4i+3 hold candidate i's R, G, B sums and the denominator
+		const double denom = __shfl_sync(0xFFFFFFFFu, acc, (threadIdx.x & 31) | 3);
+		if (threadIdx.x < 4 * nb && (threadIdx.x & 3) < 3) {
+			const int cd = sh.cand[i0 + (threadIdx.x >> 2)], c = threadIdx.x & 3;
+			const int px = x_lo + cd % kAceBlock, y = ys + cd / kAceBlock;
+			const double r = __ddiv_rn(acc, denom);
+			scores[c * plane + (size_t)(y - cs.score_row0) * cs.w + px] = r;
+			atomic_min_double(minmax + 6 + c, r);      // NaN never enters
+			atomic_max_double(minmax + 9 + c, r);
+		}
+	}
+}
+
+// Second pass over the few tiles that reach the page's extremes.  The rescale
+// divides by (max - min) and truncates, so a score AT the maximum becomes 255
+// and one an ulp below it 254: where many pixels score the same up to rounding
+// (a flat mark on a flat page, with no sample on the mark), which of them are
+// 254 depends on the last bit of the reference's sums.  Scores within kNearEps
+// of either extreme are therefore recomputed exactly as the reference does,
+// and the extremes themselves are taken over the recomputed values, which
+// makes the rescale of those pixels bit-identical to the reference's.  Tied
+// scores (0, +-1) are exact already and are left alone.
+//
+// A few blocks per SM look through the tile table the accumulation kernel left
+// (neighbouring tiles go to different blocks); a block that finds a tile near
+// an extreme lists the tile's candidate pixels and works them off with all
+// its threads.  tiles_x * tiles_y is the accumulation grid.
+__global__ void __launch_bounds__(kRefineThreads)
+ace_refine_kernel(const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
+		const AceConst cs, double *__restrict__ scores, double *__restrict__ minmax,
+		int tiles_x, int tiles_y)
+{
+	__shared__ RefineShared sh;
+	double lo[3], hi[3];
+#pragma unroll
+	for (int c = 0; c < 3; c++) {
+		const double mn = minmax[c], mx = minmax[3 + c];
+		const double thr = (mx - mn) * kNearEps;
+		lo[c] = mn + thr;
+		hi[c] = mx - thr;
+	}
+	const int col = threadIdx.x % kAceBlock;
+	const int tile_row0 = cs.row_begin / cs.tile_rows;
+	const size_t plane = (size_t)cs.score_plane;
+	const int n_tiles = tiles_x * tiles_y;
+	const bool table = cs.nb_samples <= kRefineTable;
+	bool staged = false;
+
+	for (int base = 0; base < n_tiles; base += gridDim.x * kRefineThreads) {
+		if (threadIdx.x == 0)
+			sh.n_wanted = 0;
+		__syncthreads();
+		const int t = base + threadIdx.x * gridDim.x + blockIdx.x;
+		if (t < n_tiles) {
+			const double *tile = minmax + kMinmaxHead
+				+ 6 * ((size_t)(tile_row0 + t / tiles_x) * tiles_x + t % tiles_x);
+			bool wanted = false;
+#pragma unroll
+			for (int c = 0; c < 3; c++)
+				wanted |= (tile[c] <= lo[c]) || (tile[3 + c] >= hi[c]);
+			if (wanted)
+				sh.wanted[atomicAdd(&sh.n_wanted, 1)] = t;
+		}
+		__syncthreads();
+		const int n_wanted = sh.n_wanted;
+		if (n_wanted && table && !staged) {
+			staged = true;
+			for (int k = threadIdx.x; k < cs.nb_samples; k += kRefineThreads) {
+				const int2 sxy = __ldg(reinterpret_cast<const int2 *>(samples_xy) + k);
+				sh.sx[k] = sxy.x;
+				sh.sy[k] = sxy.y;
+				sh.spx[k] = cs.sample_px ? __ldg(cs.sample_px + k)
+				                         : __ldg(in + (size_t)sxy.y * cs.w + sxy.x);
+			}
+		}
+		for (int wi = 0; wi < n_wanted; wi++) {
+			const int tw = sh.wanted[wi];
+			const int x_lo = (tw % tiles_x) * kAceBlock;
+			const int tile_y0 = (tile_row0 + tw / tiles_x) * cs.tile_rows;
+			const int y_begin = max(tile_y0, cs.row_begin);
+			const int y_end = min(min(cs.h, tile_y0 + cs.tile_rows), cs.row_end);
+			for (int ys = y_begin; ys < y_end; ys += kRefineSlab) {
+				__syncthreads();
+				if (threadIdx.x == 0)
+					sh.n_cand = 0;
+				__syncthreads();
+				// this thread's pixels of the slab: all loads first
+				constexpr int kStep = kRefineThreads / kAceBlock;
+				double sv[kRefineSlab / kStep][3];
+#pragma unroll
+				for (int i = 0; i < kRefineSlab / kStep; i++) {
+					const int y = ys + threadIdx.x / kAceBlock + i * kStep;
+					const bool in_tile = y < y_end && x_lo + col < cs.w;
+					const size_t o = in_tile ? (size_t)(y - cs.score_row0) * cs.w + x_lo + col : 0;
+#pragma unroll
+					for (int c = 0; c < 3; c++)
+						sv[i][c] = in_tile ? scores[c * plane + o] : 0.0;   // 0.0: a tie, never listed
+				}
+#pragma unroll
+				for (int i = 0; i < kRefineSlab / kStep; i++) {
+					bool need = false;
+#pragma unroll
+					for (int c = 0; c < 3; c++)
+						need |= (sv[i][c] <= lo[c] || sv[i][c] >= hi[c])
+							&& !is_tie_score(sv[i][c]);                  // false for NaN
+					if (need)
+						sh.cand[atomicAdd(&sh.n_cand, 1)] = (unsigned short)
+							((threadIdx.x / kAceBlock + i * kStep) * kAceBlock + col);
+				}
+				__syncthreads();
+				const int n = sh.n_cand;
+				ace_exact_candidates(sh, table, in, samples_xy, cs, x_lo, ys, n, scores, minmax);
+			}
+		}
+		__syncthreads();
+	}
 }
 
 // The reference's linear scaling, operation for operation (true FP64 divide).
@@ -440,8 +695,13 @@ ace_scale_kernel(const double *__restrict__ scores, const double *__restrict__ m
 	double mn[3], span[3], inv[3];
 #pragma unroll
 	for (int c = 0; c < 3; c++) {
-		mn[c] = minmax[c];
-		span[c] = minmax[3 + c] - mn[c];
+		// the extremes over the recomputed scores where ace_refine_kernel
+		// produced some; a tied extreme (exact as it is) takes part as well
+		const double mnf = minmax[c], mxf = minmax[3 + c];
+		const double mne = minmax[6 + c], mxe = minmax[9 + c];
+		mn[c] = (is_tie_score(mnf) || mne == DBL_MAX) ? fmin(mnf, mne) : mne;
+		const double mx = (is_tie_score(mxf) || mxe == -DBL_MAX) ? fmax(mxf, mxe) : mxe;
+		span[c] = mx - mn[c];
 		inv[c] = 1.0 / span[c];
 	}
 	const bool vec = (npix % 4 == 0) && (plane % 2 == 0)
@@ -494,15 +754,39 @@ __global__ void fp64_peak_kernel(double *sink, int iters, double a, double b)
 
 }  // namespace
 
-int launch_ace_minmax_init(double *minmax, cudaStream_t st)
+int launch_ace_minmax_init(double *minmax, int w, int h, cudaStream_t st)
 {
-	ace_minmax_init_kernel<<<1, 32, 0, st>>>(minmax);
+	const size_t n = ace_minmax_doubles(w, h);
+	ace_minmax_init_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(minmax, n);
 	PFB_CUDA(cudaGetLastError());
 	return PF_B200_OK;
 }
 
-int launch_ace_scores(const uint32_t *in, const int *samples_xy,
-		const AceParams &p, double *scores, double *minmax, cudaStream_t st)
+namespace {
+
+// Pixels a thread carries and rows a tile holds.  Knobs (read once per
+// process; tools/ace_time.py sweeps them); the defaults are the measured best
+// on B200 (profiles/README.md):
+//   PF_B200_ACE_ROWS = 2 | 4 | 6 | 8   pixels per thread (default 8)
+//   PF_B200_ACE_TILE_ROWS = n          rows per tile (default 16)
+int ace_rows_per_thread(bool fast)
+{
+	static const int rows_env = getenv("PF_B200_ACE_ROWS") ? atoi(getenv("PF_B200_ACE_ROWS")) : 8;
+	if (!fast)
+		return 4;
+	return (rows_env == 2 || rows_env == 4 || rows_env == 6) ? rows_env : 8;
+}
+
+int ace_tile_rows(bool fast)
+{
+	static const int tile_env = getenv("PF_B200_ACE_TILE_ROWS") ? atoi(getenv("PF_B200_ACE_TILE_ROWS")) : 0;
+	const int rows_p = ace_rows_per_thread(fast);
+	// a tile is a whole number of row groups
+	return (tile_env >= rows_p && tile_env % rows_p == 0) ? tile_env : (rows_p == 6 ? 18 : 16);
+}
+
+// Checks the arguments and lays out the launch both ACE kernels share.
+int ace_setup(const AceParams &p, AceConst &cs, dim3 &grid, bool &fast)
 {
 	if (p.nb_samples < 1)
 		return fail(PF_B200_EINVAL, "ace: nb_samples must be >= 1");
@@ -514,7 +798,6 @@ int launch_ace_scores(const uint32_t *in, const int *samples_xy,
 	if (p.w > 46340 || p.h > 32767)
 		return fail(PF_B200_ETOOBIG, "ace: page of %d x %d too large", p.w, p.h);
 
-	AceConst cs;
 	cs.w = p.w;
 	cs.h = p.h;
 	cs.row_begin = p.row_begin;
@@ -530,26 +813,41 @@ int launch_ace_scores(const uint32_t *in, const int *samples_xy,
 	cs.ratio = p.slope / p.limit;
 	// fast path: saturate(slope*d) == slope*clamp(d, -L, L) with integer L <= 127
 	const double l = p.limit / p.slope;
-	const bool fast = l >= 1.0 && l <= 127.0 && l == floor(l) && p.slope * l == p.limit;
+	fast = l >= 1.0 && l <= 127.0 && l == floor(l) && p.slope * l == p.limit;
 	cs.clamp_l = fast ? (int)l : 0;
-
-	static const int tile_env = getenv("PF_B200_ACE_TILE_ROWS") ? atoi(getenv("PF_B200_ACE_TILE_ROWS")) : 0;
-	static const int rows_env0 = getenv("PF_B200_ACE_ROWS") ? atoi(getenv("PF_B200_ACE_ROWS")) : 8;
-	const int rows_p = (fast && (rows_env0 == 2 || rows_env0 == 4 || rows_env0 == 6)) ? rows_env0 : (fast ? 8 : 4);
-	// a tile is a whole number of row groups
-	cs.tile_rows = (tile_env >= rows_p && tile_env % rows_p == 0) ? tile_env : (rows_p == 6 ? 18 : 16);
-	dim3 grid((p.w + kAceBlock - 1) / kAceBlock,
+	cs.tile_rows = ace_tile_rows(fast);
+	grid = dim3((p.w + kAceBlock - 1) / kAceBlock,
 			(p.row_end - 1) / cs.tile_rows - p.row_begin / cs.tile_rows + 1);
+	return PF_B200_OK;
+}
+
+}  // namespace
+
+size_t ace_minmax_doubles(int w, int h)
+{
+	// a band of the page never has more tile rows than the page has, plus one
+	const int tile_rows = ace_tile_rows(true) < ace_tile_rows(false) ? ace_tile_rows(true)
+	                                                                 : ace_tile_rows(false);
+	const size_t tiles = (size_t)((w + kAceBlock - 1) / kAceBlock) * ((h + tile_rows - 1) / tile_rows + 1);
+	return kMinmaxHead + 6 * tiles;
+}
+
+int launch_ace_scores(const uint32_t *in, const int *samples_xy,
+		const AceParams &p, double *scores, double *minmax, cudaStream_t st)
+{
+	AceConst cs;
+	dim3 grid;
+	bool fast;
+	const int rc = ace_setup(p, cs, grid, fast);
+	if (rc)
+		return rc;
 	const size_t smem = sizeof(AceShared);
-	// Knobs (read once per process; tools/ace_time.py sweeps them).  Defaults
-	// are the measured best on B200 (profiles/README.md):
-	//   PF_B200_ACE_ROWS = 2 | 4 | 8   pixels per thread (default 8)
 	//   PF_B200_ACE_NEWTON = 1         one Newton step on MUFU.RSQ64H's 1/dist:
 	//       weights good to ~2^-43 instead of ~2^-22.  Off by default: both
 	//       settings sit three orders of magnitude inside the +-1 LSB / 0.1 %
 	//       bar (1.1e-4 % vs 3e-5 % of channel values differ on the test page)
 	//       and the step costs 3 of 8 FP64 instructions per pair.
-	static const int rows_env = getenv("PF_B200_ACE_ROWS") ? atoi(getenv("PF_B200_ACE_ROWS")) : 8;
+	const int rows_env = ace_rows_per_thread(fast);
 	static const int newton_env = getenv("PF_B200_ACE_NEWTON") ? atoi(getenv("PF_B200_ACE_NEWTON")) : 0;
 	void (*kern)(const uint32_t *, const int *, const AceConst, double *, double *) = nullptr;
 	if (!fast)
@@ -563,6 +861,22 @@ int launch_ace_scores(const uint32_t *in, const int *samples_xy,
 			: rows_env == 6 ? ace_scores_kernel<true, false, 6> : ace_scores_kernel<true, false, 4>;
 	PFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
 	kern<<<grid, kAceBlock, smem, st>>>(in, samples_xy, cs, scores, minmax);
+	PFB_CUDA(cudaGetLastError());
+	return PF_B200_OK;
+}
+
+
+int launch_ace_refine(const uint32_t *in, const int *samples_xy,
+		const AceParams &p, double *scores, double *minmax, cudaStream_t st)
+{
+	AceConst cs;
+	dim3 grid;
+	bool fast;
+	const int rc = ace_setup(p, cs, grid, fast);
+	if (rc)
+		return rc;
+	ace_refine_kernel<<<sm_count() * 4, kRefineThreads, 0, st>>>(in, samples_xy, cs, scores,
+			minmax, (int)grid.x, (int)grid.y);
 	PFB_CUDA(cudaGetLastError());
 	return PF_B200_OK;
 }

@@ -488,13 +488,14 @@ static int run_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
 		return rc;
 	const size_t npix = (size_t)w * h;
 	const size_t bytes = npix * sizeof(uint32_t);
-	const size_t small = 64 + sizeof(int) * 3 * (size_t)nb_samples;
+	const size_t mm_bytes = (ace_minmax_doubles(w, h) * sizeof(double) + 63) / 64 * 64;
+	const size_t small = mm_bytes + sizeof(int) * 3 * (size_t)nb_samples;
 	if ((rc = grow(c.d_in, bytes, false)) || (rc = grow(c.d_out, bytes, false))
 			|| (rc = grow(c.d_scores, 3 * npix * sizeof(double), false))
 			|| (rc = grow(c.d_small, small, false)))
 		return rc;
 	double *minmax = static_cast<double *>(c.d_small.p);
-	int *d_xy = reinterpret_cast<int *>(static_cast<char *>(c.d_small.p) + 64);
+	int *d_xy = reinterpret_cast<int *>(static_cast<char *>(c.d_small.p) + mm_bytes);
 	uint32_t *d_spx = reinterpret_cast<uint32_t *>(d_xy + 2 * (size_t)nb_samples);
 	const uint32_t *din = static_cast<const uint32_t *>(c.d_in.p);
 	uint32_t *dout = static_cast<uint32_t *>(c.d_out.p);
@@ -504,7 +505,7 @@ static int run_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
 	PFB_CUDA(cudaMemcpyAsync(d_xy, sample_xy, sizeof(int) * 2 * (size_t)nb_samples,
 			cudaMemcpyHostToDevice, c.st));
 	AceParams p = { w, h, 0, h, nb_samples, slope, limit };
-	if ((rc = launch_ace_minmax_init(minmax, c.st)))
+	if ((rc = launch_ace_minmax_init(minmax, w, h, c.st)))
 		return rc;
 
 	if (h >= 512 && nb_samples <= 4096 && is_pinned(in->pixels) && is_pinned(out->pixels)) {
@@ -538,6 +539,10 @@ static int run_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
 			if ((rc = launch_ace_scores(din, d_xy, p, scores, minmax, c.st)))
 				return rc;
 		}
+		p.row_begin = 0;
+		p.row_end = h;
+		if ((rc = launch_ace_refine(din, d_xy, p, scores, minmax, c.st)))
+			return rc;
 		for (int b = 0; b < nb; b++) {
 			const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
 			if ((rc = launch_ace_scale(scores + (size_t)y0 * w, minmax, w, y1 - y0,
@@ -555,6 +560,8 @@ static int run_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
 	if ((rc = upload(c, c.d_in.p, in->pixels, bytes)))
 		return rc;
 	if ((rc = launch_ace_scores(din, d_xy, p, scores, minmax, c.st)))
+		return rc;
+	if ((rc = launch_ace_refine(din, d_xy, p, scores, minmax, c.st)))
 		return rc;
 	if ((rc = launch_ace_scale(scores, minmax, w, h, dout, c.st)))
 		return rc;
@@ -779,12 +786,39 @@ int pf_b200_dev_canny(const uint32_t *d_in, uint32_t *d_out,
 			d_scratch, scratch_bytes, static_cast<cudaStream_t>(stream));
 }
 
-int pf_b200_dev_ace_minmax_init(double *d_minmax, void *stream)
+size_t pf_b200_ace_minmax_bytes(int width, int height)
+{
+	clear_error();
+	if (width <= 0 || height <= 0) {
+		fail(PF_B200_EINVAL, "size %d x %d", width, height);
+		return 0;
+	}
+	return ace_minmax_doubles(width, height) * sizeof(double);
+}
+
+int pf_b200_dev_ace_minmax_init(double *d_minmax, int width, int height, void *stream)
 {
 	clear_error();
 	if (!d_minmax)
 		return fail(PF_B200_EINVAL, "NULL device pointer");
-	return launch_ace_minmax_init(d_minmax, static_cast<cudaStream_t>(stream));
+	if (width <= 0 || height <= 0)
+		return fail(PF_B200_EINVAL, "size %d x %d", width, height);
+	return launch_ace_minmax_init(d_minmax, width, height, static_cast<cudaStream_t>(stream));
+}
+
+int pf_b200_dev_ace_refine(const uint32_t *d_in, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, int nb_samples, double slope, double limit,
+		double *d_scores, double *d_minmax, void *stream)
+{
+	clear_error();
+	if (!d_in || !d_samples || !d_scores || !d_minmax)
+		return fail(PF_B200_EINVAL, "NULL device pointer");
+	if (width <= 0 || height <= 0)
+		return fail(PF_B200_EINVAL, "size %d x %d", width, height);
+	AceParams p = { width, height, row_begin, row_end, nb_samples, slope, limit };
+	return launch_ace_refine(d_in, d_samples, p, d_scores, d_minmax,
+			static_cast<cudaStream_t>(stream));
 }
 
 int pf_b200_dev_ace_scores(const uint32_t *d_in, int width, int height,

@@ -78,8 +78,16 @@ struct AceParams {
 	int score_row0 = -1;
 	long score_plane = -1;
 };
-int launch_ace_minmax_init(double *minmax, cudaStream_t st);
+// `minmax` is a block of ace_minmax_doubles(w, h) doubles: the page-wide
+// extremes first, then one entry per tile (pf_ace.cu, kMinmaxHead).
+size_t ace_minmax_doubles(int w, int h);
+int launch_ace_minmax_init(double *minmax, int w, int h, cudaStream_t st);
 int launch_ace_scores(const uint32_t *in, const int *samples_xy,
+		const AceParams &p, double *scores, double *minmax, cudaStream_t st);
+// After launch_ace_scores of every band (and, across GPUs, the min/max
+// exchange), same parameters: recomputes the scores at the page's extremes in
+// the reference's arithmetic.
+int launch_ace_refine(const uint32_t *in, const int *samples_xy,
 		const AceParams &p, double *scores, double *minmax, cudaStream_t st);
 // plane < 0: planes of rows*w doubles (a band-local buffer)
 int launch_ace_scale(const double *scores, const double *minmax, int w,

@@ -4,8 +4,9 @@ for the plumbing (NCCL on GPUs, gloo in the CPU tests).
 Only the two splits BASELINE.json names:
   * ACE: the page is broadcast, each rank accumulates the scores of one band
     of rows, the per-channel min/max are all-reduced (6 doubles -- the one
-    real exchange the algorithm has), each rank rescales its band, and the
-    bands are all-gathered.
+    real exchange the algorithm has; a second time for the scores at the
+    extremes once they have been recomputed exactly), each rank rescales its
+    band, and the bands are all-gathered.
   * Gaussian/Sobel/Canny: pages are independent; page i goes to rank
     i mod world and nothing is exchanged.
 
@@ -37,10 +38,13 @@ class CudaAceCompute:
         self._capi = _capi
         self._lib = _capi.lib
 
-    def new_minmax(self, device):
-        mm = torch.empty(6, dtype=torch.float64, device=device)
+    def new_minmax(self, device, width, height):
+        """The min/max block of one page (include/pillowfight_b200.h): [0:3]
+        min, [3:6] max of the scores, [6:9], [9:12] of the refined ones."""
+        n = self._lib.pf_b200_ace_minmax_bytes(width, height) // 8
+        mm = torch.empty(n, dtype=torch.float64, device=device)
         st = torch.cuda.current_stream().cuda_stream
-        self._capi.check(self._lib.pf_b200_dev_ace_minmax_init(mm.data_ptr(), st))
+        self._capi.check(self._lib.pf_b200_dev_ace_minmax_init(mm.data_ptr(), width, height, st))
         return mm
 
     def scores(self, page, xy, slope, limit, band, minmax):
@@ -54,6 +58,16 @@ class CudaAceCompute:
             page.data_ptr(), w, h, b0, b1, xy.data_ptr(), xy.numel() // 2,
             float(slope), float(limit), out.data_ptr(), minmax.data_ptr(), st))
         return out
+
+    def refine(self, page, xy, slope, limit, band, scores, minmax):
+        """Recomputes the band's scores at the page's extremes exactly; their
+        min/max go to minmax[6:12].  True: those need the exchange too."""
+        h, w = page.shape[0], page.shape[1]
+        st = torch.cuda.current_stream().cuda_stream
+        self._capi.check(self._lib.pf_b200_dev_ace_refine(
+            page.data_ptr(), w, h, band[0], band[1], xy.data_ptr(), xy.numel() // 2,
+            float(slope), float(limit), scores.data_ptr(), minmax.data_ptr(), st))
+        return True
 
     def scale(self, scores, minmax):
         rows, w = scores.shape[1], scores.shape[2]
@@ -74,11 +88,14 @@ def ace_sharded(page, xy, slope, limit, compute, group=None, src=0):
         dist.broadcast(page, src=src, group=group)
         dist.broadcast(xy, src=src, group=group)
     bands = row_bands(h, world)
-    minmax = compute.new_minmax(page.device)
+    minmax = compute.new_minmax(page.device, w, h)
     scores = compute.scores(page, xy, slope, limit, bands[rank], minmax)
     if world > 1:
-        dist.all_reduce(minmax[:3], op=dist.ReduceOp.MIN, group=group)
-        dist.all_reduce(minmax[3:], op=dist.ReduceOp.MAX, group=group)
+        dist.all_reduce(minmax[0:3], op=dist.ReduceOp.MIN, group=group)
+        dist.all_reduce(minmax[3:6], op=dist.ReduceOp.MAX, group=group)
+    if compute.refine(page, xy, slope, limit, bands[rank], scores, minmax) and world > 1:
+        dist.all_reduce(minmax[6:9], op=dist.ReduceOp.MIN, group=group)
+        dist.all_reduce(minmax[9:12], op=dist.ReduceOp.MAX, group=group)
     band = compute.scale(scores, minmax)
     if world == 1:
         return band

@@ -170,6 +170,50 @@ def test_ace_pixels_without_any_sample(gpu, oracle):
             assert (near == 0).all() and (out[22:29, 27:34, :3] == 0).all()
 
 
+def test_ace_flat_and_tied_pages(gpu, oracle):
+    """Pages where many pixels score exactly the same in the reference: a
+    difference of 0, +limit or -limit to every sample gives exactly 0, 1, -1.
+    The rescale divides by (max - min): a flat channel is 0/0 -> 0 everywhere,
+    and a tie AT the maximum must come out as 255 for every tied pixel."""
+    w, h, n = 150, 90, 20
+    xy = oracle.ace_draw_samples(n, w, h, 4)
+    sample_px = set(zip(xy[0::2].tolist(), xy[1::2].tolist()))
+    flat = np.full((h, w, 4), 255, dtype=np.uint8)
+    flat[..., :3] = (200, 17, 255)
+    mark = flat.copy()                     # a darker mark no sample lands on: page pixels tie at the maximum
+    free = next((x, y) for y in range(30, 60) for x in range(40, 110)
+                if all(abs(x - sx) > 6 or abs(y - sy) > 6 for sx, sy in sample_px))
+    mark[free[1] - 3:free[1] + 3, free[0] - 3:free[0] + 3, :3] = (90, 5, 100)
+    faint = flat.copy()                    # a brighter, faint one: ITS pixels are the maximum, tied up to rounding
+    faint[..., :3] = (100, 100, 100)
+    faint[free[1] - 3:free[1] + 3, free[0] - 3:free[0] + 3, :3] = (130, 186, 199)
+    halves = flat.copy()                   # two tones, samples on both
+    halves[:, w // 2:, :3] = (10, 10, 10)
+    for name, page in (("flat", flat), ("mark", mark), ("faint", faint), ("halves", halves)):
+        for slope, limit in ((10.0, 1000.0), (7.5, 1000.0)):       # integer-clamp and table kernels
+            ref = oracle.ace_with_samples(page, xy, slope, limit, nb_threads=4)
+            got = gpu.ace(page, slope, limit, n, seed=4)
+            if name == "halves":           # no ties: scores vary with the position, the usual bar
+                assert_fp_parity(got, ref, "ace halves")
+                continue
+            assert np.array_equal(got, ref), "%s slope %g: %d differ, max %d" % (
+                name, slope, (got != ref).sum(), np.abs(got.astype(int) - ref.astype(int)).max())
+    assert (gpu.ace(flat, 10, 1000, n, seed=4)[..., :3] == 0).all()
+    assert (gpu.ace(mark, 10, 1000, n, seed=4)[0, 0, :3] == 255).all()
+
+
+def test_randomised_sweep(gpu, oracle):
+    """tools/fuzz_parity.py: random shapes, contents (noise, flat pages with
+    spikes, blocks, ramps, binary textures, saturated pages) and parameters
+    through all four calls."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import fuzz_parity
+    bad = fuzz_parity.run(60, 1)
+    assert not bad, bad
+
+
 def test_ace_many_samples_chunked(gpu, oracle):
     # more samples than one shared-memory chunk holds (512)
     page = synthetic_page(96, 128, 6)
@@ -189,14 +233,24 @@ def _ace_scores_error(oracle):
     ref = oracle.ace_scores(page, xy, 10.0, 1000.0, nb_threads=4)
     dev = torch.device("cuda:0")
     comp = CudaAceCompute()
-    mm = comp.new_minmax(dev)
-    s = comp.scores(torch.from_numpy(page).to(dev), xy_tensor(xy, dev), 10.0, 1000.0, (0, h), mm)
+    mm = comp.new_minmax(dev, w, h)
+    tp, txy = torch.from_numpy(page).to(dev), xy_tensor(xy, dev)
+    s = comp.scores(tp, txy, 10.0, 1000.0, (0, h), mm)
     torch.cuda.synchronize()
     got = s.cpu().numpy()
     err = float(np.nanmax(np.abs(got - ref)))
     mmh = mm.cpu().numpy()
     mm_err = max(float(np.abs(mmh[:3] - np.nanmin(ref, axis=(1, 2))).max()),
-                 float(np.abs(mmh[3:] - np.nanmax(ref, axis=(1, 2))).max()))
+                 float(np.abs(mmh[3:6] - np.nanmax(ref, axis=(1, 2))).max()))
+    # the refinement pass: the extremes, and every score near them, exactly
+    comp.refine(tp, txy, 10.0, 1000.0, (0, h), s, mm)
+    torch.cuda.synchronize()
+    mmh, got = mm.cpu().numpy(), s.cpu().numpy()
+    assert np.array_equal(mmh[6:9], np.nanmin(ref, axis=(1, 2))), (mmh[6:9], np.nanmin(ref, axis=(1, 2)))
+    assert np.array_equal(mmh[9:12], np.nanmax(ref, axis=(1, 2))), (mmh[9:12], np.nanmax(ref, axis=(1, 2)))
+    span = (mmh[9:12] - mmh[6:9])[:, None, None]
+    near = (ref <= mmh[6:9, None, None] + span * 2.0 ** -16) | (ref >= mmh[9:12, None, None] - span * 2.0 ** -16)
+    assert near.sum() >= 6 and np.array_equal(got[near], ref[near])
     return err, mm_err
 
 
@@ -239,13 +293,18 @@ def test_ace_band_split_equals_whole(gpu, oracle):
     dev = torch.device("cuda:0")
     comp = CudaAceCompute()
     tp, txy = torch.from_numpy(page).to(dev), xy_tensor(xy, dev)
-    mm = comp.new_minmax(dev)
-    whole = comp.scale(comp.scores(tp, txy, 10.0, 1000.0, (0, h), mm), mm)
-    mm2 = comp.new_minmax(dev)
-    parts = [comp.scores(tp, txy, 10.0, 1000.0, b, mm2) for b in row_bands(h, 3)]
+    mm = comp.new_minmax(dev, w, h)
+    sc = comp.scores(tp, txy, 10.0, 1000.0, (0, h), mm)
+    comp.refine(tp, txy, 10.0, 1000.0, (0, h), sc, mm)
+    whole = comp.scale(sc, mm)
+    mm2 = comp.new_minmax(dev, w, h)
+    bands = row_bands(h, 3)
+    parts = [comp.scores(tp, txy, 10.0, 1000.0, b, mm2) for b in bands]
+    for b, p in zip(bands, parts):
+        comp.refine(tp, txy, 10.0, 1000.0, b, p, mm2)
     split = torch.cat([comp.scale(p, mm2) for p in parts], dim=0)
     torch.cuda.synchronize()
-    assert torch.equal(mm, mm2)
+    assert torch.equal(mm[:12], mm2[:12])
     assert torch.equal(whole, split)
 
 
@@ -452,9 +511,12 @@ def test_no_writes_outside_the_output_page(gpu, oracle, w, h):
             from libpillowfight_b200.distributed import xy_tensor
             txy = xy_tensor(xy, dev)
             sc_buf, sc = guarded(3 * w * h * 8)
-            mm = torch.empty(6, dtype=torch.float64, device=dev)
-            chk(lib.pf_b200_dev_ace_minmax_init(mm.data_ptr(), st))
+            mm_bytes = lib.pf_b200_ace_minmax_bytes(w, h)
+            mm_buf, mm = guarded(mm_bytes)
+            chk(lib.pf_b200_dev_ace_minmax_init(mm.data_ptr(), w, h, st))
             chk(lib.pf_b200_dev_ace_scores(tin.data_ptr(), w, h, 0, h, txy.data_ptr(), 10,
+                                           10.0, 1000.0, sc.data_ptr(), mm.data_ptr(), st))
+            chk(lib.pf_b200_dev_ace_refine(tin.data_ptr(), w, h, 0, h, txy.data_ptr(), 10,
                                            10.0, 1000.0, sc.data_ptr(), mm.data_ptr(), st))
             chk(lib.pf_b200_dev_ace_scale(sc.data_ptr(), mm.data_ptr(), w, h, out.data_ptr(), st))
             ref = oracle.ace_with_samples(page, xy, 10.0, 1000.0)
@@ -464,6 +526,7 @@ def test_no_writes_outside_the_output_page(gpu, oracle, w, h):
             assert intact(sbuf, sbytes), "canny wrote outside its scratch"
         if name == "ace":
             assert intact(sc_buf, 3 * w * h * 8), "ace wrote outside its score planes"
+            assert intact(mm_buf, mm_bytes), "ace wrote outside its min/max block"
             assert_fp_parity(out.cpu().numpy().reshape(h, w, 4), ref, "ace guarded")
         else:
             assert np.array_equal(out.cpu().numpy().reshape(h, w, 4), ref), name

@@ -20,9 +20,12 @@ class OracleAceCompute:
         from oracle import pf_oracle
         self.o = pf_oracle
 
-    def new_minmax(self, device):
+    def new_minmax(self, device, width, height):
         big = np.finfo(np.float64).max
-        return torch.tensor([big] * 3 + [-big] * 3, dtype=torch.float64)
+        return torch.tensor(([big] * 3 + [-big] * 3) * 2, dtype=torch.float64)
+
+    def refine(self, page, xy, slope, limit, band, scores, minmax):
+        return False        # the oracle's scores are the reference's already
 
     def scores(self, page, xy, slope, limit, band, minmax):
         b0, b1 = band
@@ -35,7 +38,7 @@ class OracleAceCompute:
     def scale(self, scores, minmax):
         s = scores.numpy()
         mn = minmax[:3].numpy()[:, None, None]
-        mx = minmax[3:].numpy()[:, None, None]
+        mx = minmax[3:6].numpy()[:, None, None]
         with np.errstate(invalid="ignore"):
             v = 255.0 * (s - mn) / (mx - mn)
         v = np.where(v > 0.0, np.minimum(v, 255.0), 0.0)

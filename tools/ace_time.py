@@ -21,7 +21,7 @@ lib, chk = _capi.lib, _capi.check
 page = torch.from_numpy(synthetic_page(w, h, 0)).to(dev)
 xy = xy_tensor(pf.ace_samples(n, w, h, 12345), dev)
 scores = torch.empty((3, h, w), dtype=torch.float64, device=dev)
-mm = torch.empty(6, dtype=torch.float64, device=dev)
+mm = torch.empty(lib.pf_b200_ace_minmax_bytes(w, h) // 8, dtype=torch.float64, device=dev)
 st = torch.cuda.current_stream().cuda_stream
 
 
@@ -30,7 +30,7 @@ def run():
                                    scores.data_ptr(), mm.data_ptr(), st))
 
 
-chk(lib.pf_b200_dev_ace_minmax_init(mm.data_ptr(), st))
+chk(lib.pf_b200_dev_ace_minmax_init(mm.data_ptr(), w, h, st))
 for _ in range(3):
     run()
 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -48,5 +48,5 @@ ref = o.ace_with_samples(small, o.ace_draw_samples(n, 1240, 1754, 7), 10.0, 1000
 got = pf.ace(small, 10, 1000, n, seed=7)
 d = np.abs(got.astype(np.int16) - ref.astype(np.int16))[..., :3]
 print("rows=%s newton=%s samples=%d: %.4f ms  (%.0f Mpx/s)  mismatch %.6f %% max %d" % (
-    os.environ.get("PF_B200_ACE_ROWS", "4"), os.environ.get("PF_B200_ACE_NEWTON", "1"), n, ms,
+    os.environ.get("PF_B200_ACE_ROWS", "8"), os.environ.get("PF_B200_ACE_NEWTON", "0"), n, ms,
     w * h / ms / 1e3, 100.0 * (d != 0).mean(), d.max()))

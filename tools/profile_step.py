@@ -20,12 +20,14 @@ out = torch.empty_like(page)
 out2 = torch.empty_like(page)
 xy = xy_tensor(pf.ace_samples(100, w, h, 12345), dev)
 scores = torch.empty((3, h, w), dtype=torch.float64, device=dev)
-mm = torch.empty(6, dtype=torch.float64, device=dev)
+mm = torch.empty(lib.pf_b200_ace_minmax_bytes(w, h) // 8, dtype=torch.float64, device=dev)
 scratch = torch.empty(lib.pf_b200_canny_scratch_bytes(w, h), dtype=torch.uint8, device=dev)
 st = torch.cuda.current_stream().cuda_stream
 for _ in range(reps):
-    chk(lib.pf_b200_dev_ace_minmax_init(mm.data_ptr(), st))
+    chk(lib.pf_b200_dev_ace_minmax_init(mm.data_ptr(), w, h, st))
     chk(lib.pf_b200_dev_ace_scores(page.data_ptr(), w, h, 0, h, xy.data_ptr(), 100, 10.0, 1000.0,
+                                   scores.data_ptr(), mm.data_ptr(), st))
+    chk(lib.pf_b200_dev_ace_refine(page.data_ptr(), w, h, 0, h, xy.data_ptr(), 100, 10.0, 1000.0,
                                    scores.data_ptr(), mm.data_ptr(), st))
     chk(lib.pf_b200_dev_ace_scale(scores.data_ptr(), mm.data_ptr(), w, h, out.data_ptr(), st))
     chk(lib.pf_b200_dev_gaussian(page.data_ptr(), out.data_ptr(), w, h, 2.0, 5, st))
