@@ -15,9 +15,9 @@
 // inner loop has no global loads at all.  Per pixel-sample pair the FP64 pipe
 // does: d^2 (1 add), three accumulating FMAs and one for the denominator (4);
 // the weight is MUFU.RSQ64H's 1/sqrt (optionally one Newton step, 3 more).
-// The clamp is one integer instruction for two pixels (16-bit halves), and
-// its result u = c + L is spliced straight into the high word of a subnormal
-// double (u * 2^-1034, exact and linear in u), so no conversion instruction
+// The clamp is one integer instruction (VIADDMNMX.RELU), and its result
+// u = c + L is used as it stands as the high word of a subnormal double
+// (u * 2^-1042, exact and linear in u), so neither a conversion nor a shuffle
 // is issued in the loop and the sums carry no bias: a pixel whose difference
 // to every sample is 0, +L or -L scores exactly 0, 1, -1 as in the reference.
 // Samples whose skip circle contains the whole tile are dropped per tile,
@@ -49,15 +49,15 @@ constexpr int kMinmaxHead = 12;
 // (measured: 3e-7 on a range of 1.4, tests/test_gpu_parity.py).
 constexpr double kNearEps = 0x1p-15;
 // Squared distances are carried scaled by 2^-1000, so the weights come out of
-// the rsqrt unit scaled by 2^500: the clamp result u = c + L is spliced into
-// the mantissa of a SUBNORMAL double (value u * 2^-1034, linear in u with no
-// implicit leading one), and weight * value must land in the normal range.
+// the rsqrt unit scaled by 2^500: the clamp result u = c + L becomes the high
+// word of a SUBNORMAL double (value u * 2^-1042, linear in u with no implicit
+// leading one), and weight * value must land in the normal range.
 // The common factors cancel in the score.
 constexpr double kD2Scale = 0x1p-1000;
 
 struct SampleEntry {
 	int sx;
-	uint32_t bias[3];   // (L - s_c) as a signed 16-bit value in both halves (fast path)
+	uint32_t bias[3];   // L - s_c (fast path) or s_c (table path) per channel
 };
 
 struct AceShared {
@@ -226,7 +226,7 @@ __device__ __noinline__ void stage_samples(AceShared &sh, const AceConst &cs,
 #pragma unroll
 			for (int c = 0; c < 3; c++) {
 				const uint32_t v = (px >> (8 * c)) & 0xFF;
-				sh.tbl[dst].bias[c] = FAST ? (((uint32_t)(cs.clamp_l - (int)v)) & 0xFFFFu) * 0x00010001u : v;
+				sh.tbl[dst].bias[c] = FAST ? (uint32_t)(cs.clamp_l - (int)v) : v;
 			}
 		}
 		for (int wv = warp; wv < kWarps; wv++) {
@@ -245,8 +245,8 @@ __device__ __noinline__ void stage_samples(AceShared &sh, const AceConst &cs,
 // skip circle on this tile, so each pair is tested (weight forced to 0).
 template <bool FAST, bool NEWTON, bool TEST, int P>
 __device__ __forceinline__ void accumulate_sample(const AceShared &sh, int j, int x,
-		const uint32_t (&pix)[P], const uint32_t (&pk)[P / 2][3],
-		uint32_t hi2, double too_close2, double top_value,
+		const uint32_t (&pix)[P], const uint32_t (&pv)[P][3],
+		int two_l, double too_close2, double top_value,
 		double (&acc)[P][3], double (&top)[P])
 {
 	const SampleEntry se = sh.tbl[j];
@@ -269,18 +269,14 @@ __device__ __forceinline__ void accumulate_sample(const AceShared &sh, int j, in
 	}
 	if (FAST) {
 #pragma unroll
-		for (int g = 0; g < P / 2; g++) {
+		for (int r = 0; r < P; r++) {
 #pragma unroll
 			for (int c = 0; c < 3; c++) {
-				// clamp(p - s, -L, L) + L for two pixels in one instruction:
-				// VIADDMNMX.S16x2.RELU = max(min(p + (L - s), 2L), 0) per half
-				const uint32_t t = __viaddmin_s16x2_relu(pk[g][c], se.bias[c], hi2);
-				// byte -> bits 8..15 of the high word, exponent field 0:
-				// the subnormal u * 2^-1034, no conversion instruction
-				const double va = __hiloint2double((int)__byte_perm(t, 0u, 0x4404), 0);
-				const double vb = __hiloint2double((int)__byte_perm(t, 0u, 0x4424), 0);
-				acc[2 * g][c] = fma(wgt[2 * g], va, acc[2 * g][c]);
-				acc[2 * g + 1][c] = fma(wgt[2 * g + 1], vb, acc[2 * g + 1][c]);
+				// clamp(p - s, -L, L) + L = max(min(p + (L - s), 2L), 0) is ONE
+				// instruction, VIADDMNMX.RELU, and its result IS the high word
+				// of the subnormal double u * 2^-1042: no conversion, no shuffle
+				const int u = __viaddmin_s32_relu((int)pv[r][c], (int)se.bias[c], two_l);
+				acc[r][c] = fma(wgt[r], __hiloint2double(u, 0), acc[r][c]);
 			}
 		}
 	} else {
@@ -330,10 +326,10 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 		}
 	}
 
-	const uint32_t hi2 = (uint32_t)(2 * cs.clamp_l) * 0x00010001u;
+	const int two_l = 2 * cs.clamp_l;
 	const double too_close2 = (double)cs.too_close2 * kD2Scale;
 	// what a channel saturated high contributes per unit weight
-	const double top_value = FAST ? __hiloint2double((2 * cs.clamp_l) << 8, 0) : cs.limit;
+	const double top_value = FAST ? __hiloint2double(two_l, 0) : cs.limit;
 
 	double mn[3] = { DBL_MAX, DBL_MAX, DBL_MAX };
 	double mx[3] = { -DBL_MAX, -DBL_MAX, -DBL_MAX };
@@ -347,14 +343,13 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 #pragma unroll
 		for (int r = 0; r < P; r++)
 			pix[r] = __ldg(in + (size_t)min(y0 + r, cs.h - 1) * cs.w + xc);
-		// packed channel values: rows (0,1) and (2,3) share a register
-		uint32_t pk[P / 2][3];
+		// one channel value per register (the clamp instruction wants them so)
+		uint32_t pv[P][3];
 #pragma unroll
-		for (int g = 0; g < P / 2; g++)
+		for (int r = 0; r < P; r++)
 #pragma unroll
 			for (int c = 0; c < 3; c++)
-				pk[g][c] = ((pix[2 * g] >> (8 * c)) & 0xFF)
-					| (((pix[2 * g + 1] >> (8 * c)) & 0xFF) << 16);
+				pv[r][c] = (pix[r] >> (8 * c)) & 0xFF;
 
 		double acc[P][3], top[P];
 #pragma unroll
@@ -389,10 +384,10 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 			const int n_far = sh.n_far;
 #pragma unroll kAceUnroll
 			for (int j = 0; j < n_far; j++)
-				accumulate_sample<FAST, NEWTON, false, P>(sh, j, x, pix, pk, hi2,
+				accumulate_sample<FAST, NEWTON, false, P>(sh, j, x, pix, pv, two_l,
 						too_close2, top_value, acc, top);
 			for (int j = n_far; j < n_act; j++)
-				accumulate_sample<FAST, NEWTON, true, P>(sh, j, x, pix, pk, hi2,
+				accumulate_sample<FAST, NEWTON, true, P>(sh, j, x, pix, pv, two_l,
 						too_close2, top_value, acc, top);
 		}
 
