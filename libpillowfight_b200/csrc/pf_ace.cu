@@ -671,6 +671,10 @@ ace_refine_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 // The reference's linear scaling, operation for operation (true FP64 divide).
 __device__ __noinline__ uint32_t ace_scale_exact(double s, double mn, double span)
 {
+	// a flat channel (0/0 = NaN for every pixel) and the pixels at the minimum
+	// (areas of a page can be tied there) need no division
+	if (!(span > 0.0) || s == mn)
+		return 0u;
 	const double v = __ddiv_rn(__dmul_rn(255.0, __dadd_rn(s, -mn)), span);
 	if (!(v > 0.0))         // also NaN
 		return 0u;

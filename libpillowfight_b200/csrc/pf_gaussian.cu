@@ -237,8 +237,12 @@ gaussian_generic_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ 
 // flat colour, where every value is "k * sum(taps)^2").  This kernel computes
 // the same sums with FMAs (about half the FP64 instructions; error ~1e-13),
 // truncates with one round-toward-zero add that also exposes 24 fraction
-// bits, and hands a pixel to gaussian_exact_pixel only when a channel lies
-// within 2e-6 of an integer.  Results are bit-identical to the reference.
+// bits, and only when a channel lies within 2e-6 of an integer does it ask
+// for the reference's own rounding: from a 256-entry table if the pixel's
+// whole N x N window holds one colour (flat areas: most of a document page,
+// and every pixel of them is such a case), from gaussian_exact_pixel_n
+// otherwise (a few pixels per million).  Results are bit-identical to the
+// reference and the run time does not depend on the page's content.
 // ---------------------------------------------------------------------------
 
 // v + 2^28 rounded toward zero leaves floor(v * 2^24) in the low word for
@@ -250,6 +254,24 @@ constexpr uint32_t kFracGuard = 32;                // 32 * 2^-24 ~ 2e-6
 template <int N>
 struct GaussRing {
 	double h[N][12];       // horizontal sums of the last N rows: 4 columns x 3 channels
+	// bit 24 + o: the N pixels under output column o of that row share one
+	// colour; bits 0..23: that colour (windows of two columns overlap, so
+	// there is only one), 0 if no column is flat
+	uint32_t flat[N];
+};
+
+// Taps plus the reference's result for a window of N x N equal values v, in
+// its own operation order (computed on the host, launch_gaussian_fast).  On a
+// flat area every value is v * sum(taps)^2, within rounding of the integer v,
+// so every pixel is "risky": this table answers for it without the N*N loads
+// and ~7 N*N strict operations of the exact path.  Flat areas are most of a
+// document page.
+template <int N>
+struct FastTaps {
+	double t[N];        // the taps (exact path)
+	double th[N];       // * 2^1000: horizontal pass over subnormal pixel values
+	double tv[N];       // * 2^34: vertical pass, back to the true scale
+	unsigned char flat[256];
 };
 
 // Step J of N (s = steps since the top of the strip): the row at the head of
@@ -258,10 +280,12 @@ struct GaussRing {
 // leaves.  The first N-1 steps of a strip only fill the ring.
 template <int N, int J>
 __device__ __forceinline__ void gauss_step(const uint32_t *__restrict__ in,
-		const StripGeom &g, const WarpPlace &wp, int s, const double (&t)[N],
+		const StripGeom &g, const WarpPlace &wp, int s, const FastTaps<N> &tp,
+		const unsigned char *__restrict__ flat_lut,
 		RowReader<true> &rd, RowWriter<true> &wr, uint4 (&q)[N], GaussRing<N> &ring)
 {
 	constexpr int C = N / 2;
+	const double (&t)[N] = tp.t, (&th)[N] = tp.th, (&tv)[N] = tp.tv;
 	const uint4 cur = q[J];
 	q[J] = rd.next(g);
 	// pixels x0-C .. x0+3+C: own four plus C from each neighbouring lane
@@ -283,10 +307,35 @@ __device__ __forceinline__ void gauss_step(const uint32_t *__restrict__ in,
 	for (int i = 0; i < 4 + 2 * C; i++) {
 #pragma unroll
 		for (int c = 0; c < 3; c++) {
-			const uint32_t b = __byte_perm(px[i], 0u, 0x4440 + c);    // byte c, zero-extended
-			// through the conversion unit (XU): the FP64 pipe is the busy one
-			v[i][c] = (double)b;
+			// byte c as bits 8..15 of the high word of a double whose exponent
+			// field is 0: the subnormal b * 2^-1034, exactly, by one PRMT
+			// instead of a trip through the conversion unit (16 lanes/clk).
+			// The horizontal taps carry 2^1000 and the vertical ones 2^34, so
+			// the sums are the unscaled ones times a power of two throughout.
+			v[i][c] = __hiloint2double((int)__byte_perm(px[i], 0u, 0x4404 + (c << 4)), 0);
 		}
+	}
+	{
+		// which of the four N-pixel row segments hold one colour (alpha ignored)
+		uint32_t d[3 + 2 * C];
+#pragma unroll
+		for (int i = 0; i < 3 + 2 * C; i++)
+			d[i] = px[i] ^ px[i + 1];
+		uint32_t word = 0;
+#pragma unroll
+		for (int o = 0; o < 4; o++) {
+			uint32_t any = 0;
+#pragma unroll
+			for (int i = 0; i < 2 * C; i++)
+				any |= d[o + i];
+			if (!(any & 0x00FFFFFFu)) {
+				const uint32_t colour = px[o + C] & 0x00FFFFFFu;
+				if ((word & 0x00FFFFFFu) != colour)
+					word = 0;          // (3 taps: columns 0 and 3 do not overlap)
+				word |= colour | (0x01000000u << o);
+			}
+		}
+		ring.flat[J] = word;
 	}
 	double (&hrow)[12] = ring.h[J];
 #pragma unroll
@@ -294,10 +343,10 @@ __device__ __forceinline__ void gauss_step(const uint32_t *__restrict__ in,
 #pragma unroll
 		for (int c = 0; c < 3; c++) {
 			// tap k multiplies pixel x - k + C, i.e. px index o + 2C - k
-			double a = v[o + 2 * C][c] * t[0];
+			double a = v[o + 2 * C][c] * th[0];
 #pragma unroll
 			for (int k = 1; k < N; k++)
-				a = fma(v[o + 2 * C - k][c], t[k], a);
+				a = fma(v[o + 2 * C - k][c], th[k], a);
 			hrow[o * 3 + c] = a;
 		}
 	}
@@ -315,12 +364,12 @@ __device__ __forceinline__ void gauss_step(const uint32_t *__restrict__ in,
 			// The sum is built on top of the 2^28 offset (each partial sum is
 			// then rounded to 2^-24, N-1 times: far inside the guard band) and
 			// the last FMA rounds toward zero, which is the truncation.
-			double a = fma(ring.h[J][o * 3 + c], t[0], kFracMagic);
+			double a = fma(ring.h[J][o * 3 + c], tv[0], kFracMagic);
 #pragma unroll
 			for (int k = 1; k < N - 1; k++)
-				a = fma(ring.h[(J - k + N) % N][o * 3 + c], t[k], a);
+				a = fma(ring.h[(J - k + N) % N][o * 3 + c], tv[k], a);
 			if (N > 1)
-				a = __fma_rz(ring.h[(J - (N - 1) + N) % N][o * 3 + c], t[N - 1], a);
+				a = __fma_rz(ring.h[(J - (N - 1) + N) % N][o * 3 + c], tv[N - 1], a);
 			fx[c] = (uint32_t)__double2loint(a);
 		}
 		// (fraction + guard) mod 2^24 < 2*guard  <=>  within guard of an integer
@@ -330,6 +379,27 @@ __device__ __forceinline__ void gauss_step(const uint32_t *__restrict__ in,
 			risky |= 1u << o;
 		// the three top bytes are R, G, B (the sums never reach 256)
 		res[o] = __byte_perm(__byte_perm(fx[0], fx[1], 0x4473), fx[2], 0x4710) | 0xFF000000u;
+	}
+	if (risky) {
+		// columns whose N x N window holds one colour: the tabulated result
+		uint32_t cols = ring.flat[0];
+		bool same = true;
+#pragma unroll
+		for (int k = 1; k < N; k++) {
+			cols &= ring.flat[k];
+			same = same && ((ring.flat[k] ^ ring.flat[0]) & 0x00FFFFFFu) == 0;
+		}
+		cols = same ? (cols >> 24) & risky : 0u;
+		if (cols) {
+			const uint32_t v = ring.flat[0];
+			const uint32_t px_flat = 0xFF000000u | flat_lut[v & 0xFF]
+				| (flat_lut[(v >> 8) & 0xFF] << 8) | (flat_lut[(v >> 16) & 0xFF] << 16);
+#pragma unroll
+			for (int o = 0; o < 4; o++)
+				if (cols & (1u << o))
+					res[o] = px_flat;
+			risky &= ~cols;
+		}
 	}
 	if (risky && wr.lane_out && y < wp.ye) {
 		// redo those pixels in the reference's exact operation order
@@ -348,18 +418,20 @@ __device__ __forceinline__ void gauss_step(const uint32_t *__restrict__ in,
 template <int N, int J>
 struct GaussSteps {
 	static __device__ __forceinline__ void run(const uint32_t *__restrict__ in,
-			const StripGeom &g, const WarpPlace &wp, int s, const double (&t)[N],
+			const StripGeom &g, const WarpPlace &wp, int s, const FastTaps<N> &tp,
+			const unsigned char *__restrict__ flat_lut,
 			RowReader<true> &rd, RowWriter<true> &wr, uint4 (&q)[N], GaussRing<N> &ring)
 	{
-		gauss_step<N, J>(in, g, wp, s + J, t, rd, wr, q, ring);
-		GaussSteps<N, J + 1>::run(in, g, wp, s, t, rd, wr, q, ring);
+		gauss_step<N, J>(in, g, wp, s + J, tp, flat_lut, rd, wr, q, ring);
+		GaussSteps<N, J + 1>::run(in, g, wp, s, tp, flat_lut, rd, wr, q, ring);
 	}
 };
 
 template <int N>
 struct GaussSteps<N, N> {
 	static __device__ __forceinline__ void run(const uint32_t *__restrict__,
-			const StripGeom &, const WarpPlace &, int, const double (&)[N],
+			const StripGeom &, const WarpPlace &, int, const FastTaps<N> &,
+			const unsigned char *__restrict__,
 			RowReader<true> &, RowWriter<true> &, uint4 (&)[N], GaussRing<N> &)
 	{
 	}
@@ -370,8 +442,12 @@ struct GaussSteps<N, N> {
 template <int N>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 gaussian_fast_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
-		const StripGeom g, const TapsN<N> tp)
+		const StripGeom g, const FastTaps<N> tp)
 {
+	__shared__ unsigned char flat_lut[256];
+	for (int i = threadIdx.x; i < 256; i += blockDim.x)
+		flat_lut[i] = tp.flat[i];
+	__syncthreads();
 	constexpr int C = N / 2;
 	const WarpPlace wp = place_warp(g);
 	if (!wp.valid)
@@ -379,10 +455,6 @@ gaussian_fast_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out
 	const size_t page = (size_t)blockIdx.y * g.w * g.h;
 	in += page;
 	out += page;
-	double t[N];
-#pragma unroll
-	for (int k = 0; k < N; k++)
-		t[k] = tp.t[k];
 	RowReader<true> rd;
 	RowWriter<true> wr;
 	rd.init(in, g, wp.ys - (N - 1 - C), wp.x0);
@@ -395,7 +467,7 @@ gaussian_fast_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out
 	// rows_per_strip + N - 1 steps per strip, a multiple of N
 	const int steps = g.rows_per_strip + N - 1;
 	for (int s = 0; s < steps; s += N)
-		GaussSteps<N, 0>::run(in, g, wp, s, t, rd, wr, q, ring);
+		GaussSteps<N, 0>::run(in, g, wp, s, tp, flat_lut, rd, wr, q, ring);
 }
 
 int strips_for(int w_threads_blocks, int h, int pages, int blocks_per_sm, int min_rows)
@@ -421,9 +493,29 @@ template <int N>
 static void launch_gaussian_fast(const uint32_t *in, uint32_t *out, int w, int h,
 		int pages, const Taps &taps, cudaStream_t st, int y_begin, int y_end)
 {
-	TapsN<N> tp;
-	for (int k = 0; k < N; k++)
+	FastTaps<N> tp;
+	for (int k = 0; k < N; k++) {
 		tp.t[k] = taps.t[k];
+		tp.th[k] = taps.t[k] * 0x1p+1000;
+		tp.tv[k] = taps.t[k] * 0x1p+34;
+	}
+	for (int v = 0; v < 256; v++) {
+		// the reference's loops on a window of equal values (upstream util.c
+		// pf_dbl_matrix_convolution, twice; oracle/pf_oracle.c): every product
+		// and every sum rounded, horizontal pass first
+		volatile double acc = 0.0;
+		for (int ky = 0; ky < N; ky++) {
+			volatile double hv = 0.0;
+			for (int kx = 0; kx < N; kx++) {
+				volatile double prod = (double)v * taps.t[kx];
+				hv = hv + prod;
+			}
+			volatile double prod = hv * taps.t[ky];
+			acc = acc + prod;
+		}
+		const int r = (int)acc;
+		tp.flat[v] = (unsigned char)(r > 255 ? 255 : r);
+	}
 	const StripGeom g = make_geom(gaussian_fast_kernel<N>, in, out, w, h, pages, N - 1,
 			y_begin, y_end, N);
 	const int warps = g.warp_cols * g.strips;
