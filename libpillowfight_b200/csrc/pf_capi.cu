@@ -159,6 +159,18 @@ static bool is_pinned(const void *p)
 	return a.type == cudaMemoryTypeHost;
 }
 
+// The address the kernels can use for a pinned (page-locked, mapped) host
+// buffer, or NULL: pageable memory, or pinned memory the device cannot map.
+static void *device_alias(const void *p)
+{
+	cudaPointerAttributes a;
+	if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+		cudaGetLastError();
+		return nullptr;
+	}
+	return a.type == cudaMemoryTypeHost ? a.devicePointer : nullptr;
+}
+
 // Large pageable buffers: the staging copy is the slow part (one core moves
 // ~10 GB/s, PCIe 5 takes ~55), so it is split over a few host threads.  Each
 // thread copies its slice into the pinned staging buffer and queues that
@@ -378,7 +390,9 @@ enum Op { OP_GAUSSIAN, OP_SOBEL, OP_CANNY };
 // Row bands of a streamed call: at least 256 rows each, at most kMaxBands.
 static int band_rows_for(int h)
 {
-	int rows = (h + 7) / 8;
+	static const int want = getenv("PF_B200_BANDS") ? atoi(getenv("PF_B200_BANDS")) : 8;
+	const int nbands = want < 1 ? 1 : want;
+	int rows = (h + nbands - 1) / nbands;
 	if (rows < 256)
 		rows = 256;
 	if ((h + rows - 1) / rows > kMaxBands)
@@ -401,6 +415,11 @@ static int run_stencil_streamed(Context &c, Op op, const struct pf_bitmap *in,
 	uint32_t *dst = reinterpret_cast<uint32_t *>(out->pixels);
 	const uint32_t *din = static_cast<const uint32_t *>(c.d_in.p);
 	uint32_t *dout = static_cast<uint32_t *>(c.d_out.p);
+	// The result rows go straight from the kernel into the caller's page
+	// (posted writes over PCIe, full 16-byte row segments per lane): the way
+	// back needs no copy engine, no staging in HBM and no per-band hand-over.
+	static const bool direct_env = !getenv("PF_B200_DIRECT_OUT") || atoi(getenv("PF_B200_DIRECT_OUT"));
+	uint32_t *direct = direct_env ? static_cast<uint32_t *>(device_alias(out->pixels)) : nullptr;
 	for (int b = 0; b < nb; b++) {
 		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
 		PFB_CUDA(cudaMemcpyAsync(const_cast<uint32_t *>(din) + (size_t)y0 * w, src + (size_t)y0 * w,
@@ -410,16 +429,79 @@ static int run_stencil_streamed(Context &c, Op op, const struct pf_bitmap *in,
 	for (int b = 0; b < nb; b++) {
 		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
 		PFB_CUDA(cudaStreamWaitEvent(c.st, c.ev_up[b + 1 < nb ? b + 1 : b], 0));
-		int rc = (op == OP_GAUSSIAN) ? launch_gaussian(din, dout, w, h, 1, taps, c.st, y0, y1)
-		                             : launch_sobel(din, dout, w, h, 1, c.st, y0, y1);
+		uint32_t *to = direct ? direct : dout;
+		int rc = (op == OP_GAUSSIAN) ? launch_gaussian(din, to, w, h, 1, taps, c.st, y0, y1)
+		                             : launch_sobel(din, to, w, h, 1, c.st, y0, y1);
 		if (rc)
+			return rc;
+		if (direct)
+			continue;
+		PFB_CUDA(cudaEventRecord(c.ev_done[b], c.st));
+		PFB_CUDA(cudaStreamWaitEvent(c.st_down, c.ev_done[b], 0));
+		PFB_CUDA(cudaMemcpyAsync(dst + (size_t)y0 * w, dout + (size_t)y0 * w,
+				(size_t)(y1 - y0) * w * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.st_down));
+	}
+	PFB_CUDA(cudaStreamSynchronize(direct ? c.st : c.st_down));
+	return PF_B200_OK;
+}
+
+// Canny on pinned caller memory.  Classification is row-local, so bands are
+// classified as they arrive and their rows go back at once; hysteresis, which
+// needs the whole page, then changes only the weak pixels (a few thousand on a
+// document page), and those alone are written into the caller's page again by
+// a small kernel.  PCIe carries both directions at once and nothing waits for
+// a second pass over the page.  A page with very many weak pixels takes a
+// second full download instead.
+static int run_canny_streamed(Context &c, const struct pf_bitmap *in, struct pf_bitmap *out,
+		uint32_t *mirror)
+{
+	const int w = in->size.x, h = in->size.y;
+	const size_t bytes = (size_t)w * h * sizeof(uint32_t);
+	const int rows = band_rows_for(h);
+	const int nb = (h + rows - 1) / rows;
+	int rc;
+	if ((rc = grow(c.d_scratch, canny_scratch_bytes(w, h), false)) || (rc = grow(c.h_stage, 64, true)))
+		return rc;
+	const uint32_t *src = reinterpret_cast<const uint32_t *>(in->pixels);
+	uint32_t *dst = reinterpret_cast<uint32_t *>(out->pixels);
+	const uint32_t *din = static_cast<const uint32_t *>(c.d_in.p);
+	uint32_t *dout = static_cast<uint32_t *>(c.d_out.p);
+	int *weak_count = static_cast<int *>(c.h_stage.p);
+	if ((rc = launch_canny_begin(w, h, c.d_scratch.p, c.d_scratch.cap, c.st)))
+		return rc;
+	for (int b = 0; b < nb; b++) {
+		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
+		PFB_CUDA(cudaMemcpyAsync(const_cast<uint32_t *>(din) + (size_t)y0 * w, src + (size_t)y0 * w,
+				(size_t)(y1 - y0) * w * sizeof(uint32_t), cudaMemcpyHostToDevice, c.st_up));
+		PFB_CUDA(cudaEventRecord(c.ev_up[b], c.st_up));
+	}
+	for (int b = 0; b < nb; b++) {
+		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
+		PFB_CUDA(cudaStreamWaitEvent(c.st, c.ev_up[b + 1 < nb ? b + 1 : b], 0));
+		if ((rc = launch_canny_classify_rows(din, dout, w, h, y0, y1, canny_thresholds(),
+				c.d_scratch.p, c.st)))
 			return rc;
 		PFB_CUDA(cudaEventRecord(c.ev_done[b], c.st));
 		PFB_CUDA(cudaStreamWaitEvent(c.st_down, c.ev_done[b], 0));
 		PFB_CUDA(cudaMemcpyAsync(dst + (size_t)y0 * w, dout + (size_t)y0 * w,
 				(size_t)(y1 - y0) * w * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.st_down));
 	}
-	PFB_CUDA(cudaStreamSynchronize(c.st_down));
+	if ((rc = launch_canny_resolve(dout, w, h, c.d_scratch.p, c.st)))
+		return rc;
+	PFB_CUDA(cudaMemcpyAsync(weak_count, c.d_scratch.p, sizeof(int), cudaMemcpyDeviceToHost, c.st));
+	// what follows on the kernel stream comes after the last band's download
+	PFB_CUDA(cudaEventRecord(c.ev_up[0], c.st_down));
+	PFB_CUDA(cudaStreamWaitEvent(c.st, c.ev_up[0], 0));
+	PFB_CUDA(cudaStreamSynchronize(c.st));
+	if (*weak_count == 0)
+		return PF_B200_OK;
+	if ((size_t)*weak_count <= (size_t)w * h / 64) {
+		if ((rc = launch_canny_patch(dout, mirror, c.d_scratch.p, c.st)))
+			return rc;
+	} else {
+		PFB_CUDA(cudaMemcpyAsync(dst, dout, bytes, cudaMemcpyDeviceToHost, c.st));
+	}
+	PFB_CUDA(cudaStreamSynchronize(c.st));
 	return PF_B200_OK;
 }
 
@@ -441,8 +523,13 @@ static int run_stencil(Op op, const struct pf_bitmap *in, struct pf_bitmap *out,
 	if ((rc = grow(c.d_in, bytes, false)) || (rc = grow(c.d_out, bytes, false)))
 		return rc;
 	// (bands are >= 256 rows, further than any stencil here reaches: <= 31 rows)
-	if (op != OP_CANNY && h >= 512 && is_pinned(in->pixels) && is_pinned(out->pixels))
-		return run_stencil_streamed(c, op, in, out, taps);
+	if (h >= 512 && is_pinned(in->pixels) && is_pinned(out->pixels)) {
+		if (op != OP_CANNY)
+			return run_stencil_streamed(c, op, in, out, taps);
+		// the weak pixels are written into the caller's page by a kernel
+		if (uint32_t *mirror = static_cast<uint32_t *>(device_alias(out->pixels)))
+			return run_canny_streamed(c, in, out, mirror);
+	}
 	if ((rc = upload(c, c.d_in.p, in->pixels, bytes)))
 		return rc;
 	const uint32_t *din = static_cast<const uint32_t *>(c.d_in.p);

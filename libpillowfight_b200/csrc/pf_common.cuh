@@ -55,6 +55,14 @@ size_t canny_scratch_bytes(int w, int h);
 int launch_canny(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 		CannyThresholds thr, void *scratch, size_t scratch_bytes,
 		cudaStream_t st);
+// One page in steps (row bands classified as they arrive): begin, classify
+// every band (each needs two rows above and below it in `in`), resolve; patch
+// copies the weak pixels' final values into a second image.
+int launch_canny_begin(int w, int h, void *scratch, size_t scratch_bytes, cudaStream_t st);
+int launch_canny_classify_rows(const uint32_t *in, uint32_t *out, int w, int h,
+		int y_begin, int y_end, CannyThresholds thr, void *scratch, cudaStream_t st);
+int launch_canny_resolve(uint32_t *out, int w, int h, void *scratch, cudaStream_t st);
+int launch_canny_patch(const uint32_t *out, uint32_t *mirror, void *scratch, cudaStream_t st);
 
 // ---- pf_dbl_matrix launchers (pf_matrix.cu) ------------------------------
 int launch_matrix_convolution(const double *img, double *out, int w, int h,

@@ -503,6 +503,18 @@ canny_hysteresis_kernel(uint32_t *out, PageGeom pg, int *list, int *parent,
 	}
 }
 
+// The final values of the weak pixels, copied to a second image (the caller's
+// pinned page, which already holds everything else: see pf_capi.cu).
+__global__ void canny_patch_kernel(const uint32_t *__restrict__ out, uint32_t *__restrict__ mirror,
+		const int *__restrict__ list, const int *__restrict__ hdr)
+{
+	const int count = hdr[0];
+	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+		const int idx = list[i] & ~kStrongBit;
+		mirror[idx] = out[idx];
+	}
+}
+
 }  // namespace
 
 int launch_sobel(const uint32_t *in, uint32_t *out, int w, int h, int pages,
@@ -576,6 +588,67 @@ int launch_canny(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 				reinterpret_cast<void *>(canny_hysteresis_kernel),
 				dim3(coop_blocks), dim3(kHystThreads), args, 0, st));
 	}
+	return PF_B200_OK;
+}
+
+// One page in three steps, for the host-pointer path that classifies row bands
+// as they arrive: canny_begin, canny_classify_rows for every band (in any
+// order, each needs its rows plus two above and below in `in`), canny_resolve.
+static int canny_check(int w, int h, void *scratch, size_t scratch_bytes)
+{
+	if ((size_t)w * h >= 0x7F000000ull)
+		return fail(PF_B200_ETOOBIG, "canny: page of %d x %d is too large", w, h);
+	if (scratch == nullptr || scratch_bytes < canny_scratch_bytes(w, h) || ((uintptr_t)scratch & 255) != 0)
+		return fail(PF_B200_EINVAL, "canny: scratch of %zu bytes, need %zu, 256-byte aligned",
+				scratch_bytes, canny_scratch_bytes(w, h));
+	return PF_B200_OK;
+}
+
+int launch_canny_begin(int w, int h, void *scratch, size_t scratch_bytes, cudaStream_t st)
+{
+	const int rc = canny_check(w, h, scratch, scratch_bytes);
+	if (rc)
+		return rc;
+	PFB_CUDA(cudaMemsetAsync(scratch, 0, 256, st));
+	return PF_B200_OK;
+}
+
+int launch_canny_classify_rows(const uint32_t *in, uint32_t *out, int w, int h,
+		int y_begin, int y_end, CannyThresholds thr, void *scratch, cudaStream_t st)
+{
+	if (y_begin < 0 || y_begin >= y_end || y_end > h)
+		return fail(PF_B200_EINVAL, "canny: bad row range [%d, %d) of %d", y_begin, y_end, h);
+	int *hdr = static_cast<int *>(scratch);
+	int *list = hdr + 64;
+	int *parent = list + (size_t)w * h;
+	const StripGeom g = make_geom(canny_classify_kernel, in, out, w, h, 1, 4, y_begin, y_end, 3);
+	const int warps = g.warp_cols * g.strips;
+	dim3 grid((warps + kWarpsPerBlock - 1) / kWarpsPerBlock, 1);
+	canny_classify_kernel<<<grid, kWarpsPerBlock * 32, 0, st>>>(in, out, g, thr, hdr, list, parent);
+	PFB_CUDA(cudaGetLastError());
+	return PF_B200_OK;
+}
+
+int launch_canny_resolve(uint32_t *out, int w, int h, void *scratch, cudaStream_t st)
+{
+	int *hdr = static_cast<int *>(scratch);
+	int *list = hdr + 64;
+	int *parent = list + (size_t)w * h;
+	PageGeom pg = { w, h, w * h };
+	const int *chdr = hdr;
+	void *args[] = { &out, &pg, &list, &parent, &chdr };
+	PFB_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(canny_hysteresis_kernel),
+			dim3(sm_count()), dim3(kHystThreads), args, 0, st));
+	return PF_B200_OK;
+}
+
+// After canny_resolve: the weak pixels' final values into `mirror` (a second
+// copy of the page that holds the classified rows).
+int launch_canny_patch(const uint32_t *out, uint32_t *mirror, void *scratch, cudaStream_t st)
+{
+	const int *hdr = static_cast<const int *>(scratch);
+	canny_patch_kernel<<<sm_count(), 256, 0, st>>>(out, mirror, hdr + 64, hdr);
+	PFB_CUDA(cudaGetLastError());
 	return PF_B200_OK;
 }
 

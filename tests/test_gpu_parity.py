@@ -426,6 +426,27 @@ def test_streamed_paths_on_pinned_pages(gpu, oracle):
         assert np.array_equal(dst, oracle.gaussian(page, 3.0, 9))
         _capi.check(lib.pf_b200_sobel(ctypes.byref(b_src), ctypes.byref(b_dst)))
         assert np.array_equal(dst, oracle.sobel(page))
+        # Canny: bands are classified and returned as they arrive, the weak
+        # pixels are written into the caller's page again after hysteresis
+        ref_c = oracle.canny(page)
+        dst[:] = 0x5A
+        _capi.check(lib.pf_b200_canny(ctypes.byref(b_src), ctypes.byref(b_dst)))
+        assert np.array_equal(dst, ref_c)
+        # ... and a page where most pixels are weak or strong (second full download)
+        noisy = uniform_random_page(w, h, seed=3)
+        src[:] = noisy
+        _capi.check(lib.pf_b200_canny(ctypes.byref(b_src), ctypes.byref(b_dst)))
+        assert np.array_equal(dst, oracle.canny(noisy))
+        # ... and long weak chains that only a far-away strong pixel keeps
+        chain = np.zeros((h, w, 4), dtype=np.uint8)
+        chain[..., 3] = 255
+        chain[:, 300:, :3] = 44                 # a weak vertical edge down the whole page
+        chain[700:703, 290:310, :3] = 255       # one strong spot touching it
+        src[:] = chain
+        _capi.check(lib.pf_b200_canny(ctypes.byref(b_src), ctypes.byref(b_src)))       # in place
+        assert np.array_equal(src, oracle.canny(chain))
+        assert (src[..., 0] == 255).sum() > h   # the edge was kept
+        src[:] = page
         xy = oracle.ace_draw_samples(60, w, h, 31)
         _capi.check(lib.pf_b200_ace(ctypes.byref(b_src), ctypes.byref(b_dst), 60,
                                     xy.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), 10.0, 1000.0))
