@@ -363,20 +363,26 @@ __device__ void canny_resolve_small(uint32_t *out, PageGeom pg, const int *list,
 		const int idx = s_pix[i];
 		const int p = idx % pg.npix;
 		const int y = p / pg.w, x = p - y * pg.w;
+		// all eight neighbours first: one memory round trip, not eight
+		uint32_t nv[8];
+		int n = 0;
 #pragma unroll
 		for (int dy = -1; dy <= 1; dy++) {
 #pragma unroll
 			for (int dx = -1; dx <= 1; dx++) {
 				if (dx == 0 && dy == 0)
 					continue;
-				if (x + dx < 0 || x + dx >= pg.w || y + dy < 0 || y + dy >= pg.h)
-					continue;
-				const uint32_t v = __ldcg(out + idx + dy * pg.w + dx);
-				if (v == kWhite)
-					strong_mask |= 1u << k;
-				else if (v < kBlack && (int)v > i)
-					sm_union(s_parent, i, (int)v);
+				const bool inside = x + dx >= 0 && x + dx < pg.w && y + dy >= 0 && y + dy < pg.h;
+				nv[n++] = inside ? __ldcg(out + idx + dy * pg.w + dx) : kBlack;
 			}
+		}
+#pragma unroll
+		for (n = 0; n < 8; n++) {
+			const uint32_t v = nv[n];
+			if (v == kWhite)
+				strong_mask |= 1u << k;
+			else if (v < kBlack && (int)v > i)
+				sm_union(s_parent, i, (int)v);
 		}
 	}
 	__syncthreads();
