@@ -464,42 +464,69 @@ canny_hysteresis_kernel(uint32_t *out, PageGeom pg, int *list, int *parent,
 	const int first = blockIdx.x * blockDim.x + threadIdx.x;
 	const int step = gridDim.x * blockDim.x;
 
-	for (int i = first; i < count; i += step) {
-		const int idx = list[i];
-		const int p = idx % pg.npix;
-		const int y = p / pg.w, x = p - y * pg.w;
-		const bool has_e = x + 1 < pg.w, has_w = x > 0, has_s = y + 1 < pg.h;
-		uint32_t v;
-		if (has_e && (v = __ldcg(out + idx + 1)) < kBlack)
-			uf_union(parent, i, (int)v);
-		if (has_s) {
-			if (has_w && (v = __ldcg(out + idx + pg.w - 1)) < kBlack)
-				uf_union(parent, i, (int)v);
-			if ((v = __ldcg(out + idx + pg.w)) < kBlack)
-				uf_union(parent, i, (int)v);
-			if (has_e && (v = __ldcg(out + idx + pg.w + 1)) < kBlack)
-				uf_union(parent, i, (int)v);
+	// Two entries per thread and round, all their neighbour loads issued before
+	// any is used: these loops are bound by memory latency, not by work.  The
+	// image is only read until the last loop of this kernel writes the
+	// verdicts, so the reads may go through L1 (entries that follow one
+	// another in the list are neighbours in the page and share sectors).
+	for (int i0 = first; i0 < count; i0 += 2 * step) {
+		uint32_t nv[2][4];
+#pragma unroll
+		for (int u = 0; u < 2; u++) {
+			const int i = i0 + u * step;
+#pragma unroll
+			for (int n = 0; n < 4; n++)
+				nv[u][n] = kBlack;
+			if (i >= count)
+				continue;
+			const int idx = list[i];
+			const int p = idx % pg.npix;
+			const int y = p / pg.w, x = p - y * pg.w;
+			const bool has_e = x + 1 < pg.w, has_w = x > 0, has_s = y + 1 < pg.h;
+			// each undirected edge once, from the pixel with the smaller address
+			if (has_e)
+				nv[u][0] = __ldg(out + idx + 1);
+			if (has_s && has_w)
+				nv[u][1] = __ldg(out + idx + pg.w - 1);
+			if (has_s)
+				nv[u][2] = __ldg(out + idx + pg.w);
+			if (has_s && has_e)
+				nv[u][3] = __ldg(out + idx + pg.w + 1);
 		}
+#pragma unroll
+		for (int u = 0; u < 2; u++)
+#pragma unroll
+			for (int n = 0; n < 4; n++)
+				if (nv[u][n] < kBlack)
+					uf_union(parent, i0 + u * step, (int)nv[u][n]);
 	}
 	grid.sync();
-	for (int i = first; i < count; i += step) {
-		const int idx = __ldcg(list + i) & ~kStrongBit;
-		const int p = idx % pg.npix;
-		const int y = p / pg.w, x = p - y * pg.w;
-		bool strong = false;
+	for (int i0 = first; i0 < count; i0 += 2 * step) {
+		bool strong[2] = { false, false };
 #pragma unroll
-		for (int dy = -1; dy <= 1; dy++) {
+		for (int u = 0; u < 2; u++) {
+			const int i = i0 + u * step;
+			if (i >= count)
+				continue;
+			const int idx = __ldcg(list + i) & ~kStrongBit;
+			const int p = idx % pg.npix;
+			const int y = p / pg.w, x = p - y * pg.w;
 #pragma unroll
-			for (int dx = -1; dx <= 1; dx++) {
-				if (dx == 0 && dy == 0)
-					continue;
-				if (x + dx < 0 || x + dx >= pg.w || y + dy < 0 || y + dy >= pg.h)
-					continue;
-				strong |= __ldcg(out + idx + dy * pg.w + dx) == kWhite;
+			for (int dy = -1; dy <= 1; dy++) {
+#pragma unroll
+				for (int dx = -1; dx <= 1; dx++) {
+					if (dx == 0 && dy == 0)
+						continue;
+					if (x + dx < 0 || x + dx >= pg.w || y + dy < 0 || y + dy >= pg.h)
+						continue;
+					strong[u] |= __ldg(out + idx + dy * pg.w + dx) == kWhite;
+				}
 			}
 		}
-		if (strong)
-			atomicOr(&list[uf_find(parent, i)], kStrongBit);
+#pragma unroll
+		for (int u = 0; u < 2; u++)
+			if (strong[u])
+				atomicOr(&list[uf_find(parent, i0 + u * step)], kStrongBit);
 	}
 	grid.sync();
 	for (int i = first; i < count; i += step) {
@@ -574,7 +601,8 @@ int launch_canny(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 		cudaGetLastError();
 		coop_per_sm = 1;
 	}
-	const int coop_blocks = sm_count();
+	static const int coop_env = getenv("PF_B200_HYST_BLOCKS") ? atoi(getenv("PF_B200_HYST_BLOCKS")) : 2;
+	const int coop_blocks = sm_count() * (coop_env < coop_per_sm ? coop_env : coop_per_sm);
 
 	for (int p0 = 0; p0 < pages; p0 += (int)cap_pages) {
 		const int np = (pages - p0 < (int)cap_pages) ? pages - p0 : (int)cap_pages;

@@ -212,6 +212,9 @@ def test_randomised_sweep(gpu, oracle):
     import fuzz_parity
     bad = fuzz_parity.run(60, 1)
     assert not bad, bad
+    # the same through the pinned-memory (band-pipelined) entry points
+    bad = fuzz_parity.run(20, 2, pinned=True)
+    assert not bad, bad
 
 
 def test_ace_many_samples_chunked(gpu, oracle):
@@ -221,6 +224,17 @@ def test_ace_many_samples_chunked(gpu, oracle):
     ref = oracle.ace_with_samples(page, xy, 10.0, 1000.0, nb_threads=8)
     got = gpu.ace(page, 10, 1000, 700, seed=21)
     assert_fp_parity(got, ref, "ace 700 samples")
+    # more than the refinement pass keeps in shared memory (1024), on a page
+    # whose maximum is a near-tied set (a faint mark no sample may land on is
+    # not guaranteed with this many samples: a two-tone page instead)
+    page2 = np.full((64, 80, 4), 255, dtype=np.uint8)
+    page2[..., :3] = 100
+    page2[20:30, 30:50, :3] = (130, 186, 199)
+    xy2 = oracle.ace_draw_samples(1300, 80, 64, 5)
+    for slope, limit in ((10.0, 1000.0), (7.5, 1000.0)):
+        ref2 = oracle.ace_with_samples(page2, xy2, slope, limit, nb_threads=8)
+        got2 = gpu.ace(page2, slope, limit, 1300, seed=5)
+        assert_fp_parity(got2, ref2, "ace 1300 samples")
 
 
 def _ace_scores_error(oracle):

@@ -24,7 +24,14 @@ for _ in range(28000):
     text[y:y + 12, x:x + 3, :3] = 0
 gray = np.full((h, w, 4), 255, dtype=np.uint8)
 gray[..., :3] = 137
-contents = {"synthetic": synthetic_page(w, h, 0), "noise": uniform_random_page(w, h, seed=1),
+# a smooth texture (blurred noise, stretched): many weak edges, like a photograph
+tex = rng.normal(size=(h // 4 + 2, w // 4 + 2))
+tex = np.kron(tex, np.ones((4, 4)))[:h, :w]
+for _ in range(3):
+    tex = (tex + np.roll(tex, 1, 0) + np.roll(tex, -1, 0) + np.roll(tex, 1, 1) + np.roll(tex, -1, 1)) / 5
+tex = np.clip(128 + tex * 160, 0, 255).astype(np.uint8)
+texture = np.stack([tex, tex, tex, np.full_like(tex, 255)], -1)
+contents = {"texture": np.ascontiguousarray(texture), "synthetic": synthetic_page(w, h, 0), "noise": uniform_random_page(w, h, seed=1),
             "white": white, "flat gray": gray, "text on white": text}
 out = torch.empty((h, w, 4), dtype=torch.uint8, device=dev)
 scratch = torch.empty(lib.pf_b200_canny_scratch_bytes(w, h), dtype=torch.uint8, device=dev)
@@ -63,4 +70,7 @@ for name, arr in contents.items():
          timed(ace_all),
          timed(lambda: chk(lib.pf_b200_dev_ace_refine(*ace_args))),
          timed(lambda: chk(lib.pf_b200_dev_ace_scale(scores.data_ptr(), mm.data_ptr(), w, h, out.data_ptr(), st)))]
-    print("%-14s %9.1f %9.1f %9.1f %9.1f %9.1f %9.1f" % ((name,) + tuple(t)))
+    import ctypes
+    hdr = torch.zeros(2, dtype=torch.int32)
+    hdr.copy_(scratch[:8].view(torch.int32))
+    print("%-14s %9.1f %9.1f %9.1f %9.1f %9.1f %9.1f   weak pixels %d" % ((name,) + tuple(t) + (int(hdr[0]),)))

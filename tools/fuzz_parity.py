@@ -1,5 +1,6 @@
 """Randomised parity sweep on the GPU: random shapes, contents and parameters
-through every entry point against the CPU oracle.  Usage: fuzz_parity.py [cases] [seed]"""
+through every entry point against the CPU oracle.
+Usage: fuzz_parity.py [cases] [seed] [pinned]"""
 import os
 import sys
 
@@ -57,20 +58,68 @@ def gen_cases(cases, seed):
         yield case, img, (sigma, n), ace
 
 
-def run(cases, seed):
-    """-> list of mismatch descriptions (empty: parity on every case)"""
+class _Pinned:
+    """The same four calls on pinned caller memory (the band-pipelined paths),
+    straight through the C-ABI; tall cases only (>= 512 rows stream)."""
+
+    def __init__(self):
+        import ctypes
+        from libpillowfight_b200 import _capi
+        self.ct, self.capi, self.lib = ctypes, _capi, _capi.lib
+        self.cap, self.ptr = 0, None
+
+    def call(self, fn, img, *args):
+        ct, n = self.ct, img.nbytes
+        if 2 * n > self.cap:
+            if self.ptr:
+                self.lib.pf_b200_host_free(self.ptr)
+            self.cap = 2 * n
+            self.ptr = self.lib.pf_b200_host_alloc(self.cap)
+        src = np.ctypeslib.as_array((ct.c_uint8 * n).from_address(self.ptr)).reshape(img.shape)
+        dst = np.ctypeslib.as_array((ct.c_uint8 * n).from_address(self.ptr + n)).reshape(img.shape)
+        src[:] = img
+        dst[:] = 0x5A
+        bi, bo = self.capi.PfBitmap(), self.capi.PfBitmap()
+        bi.size.x = bo.size.x = img.shape[1]
+        bi.size.y = bo.size.y = img.shape[0]
+        bi.pixels, bo.pixels = self.ptr, self.ptr + n
+        self.capi.check(fn(ct.byref(bi), ct.byref(bo), *args))
+        return dst.copy()
+
+
+def run(cases, seed, pinned=False):
+    """-> list of mismatch descriptions (empty: parity on every case).
+    pinned: tall cases go through the pinned-memory entry points instead."""
+    import ctypes
     import libpillowfight_b200 as pf
     bad = []
+    pin = _Pinned() if pinned else None
     for case, img, (sigma, n), ace in gen_cases(cases, seed):
+        if pinned:
+            reps = -(-600 // img.shape[0])             # tile the page to >= 600 rows
+            img = np.ascontiguousarray(np.tile(img, (reps, 1, 1)))
         h, w = img.shape[:2]
-        checks = [("gaussian(%g,%d)" % (sigma, n), lambda: pf.gaussian(img, sigma, n), lambda: o.gaussian(img, sigma, n), 0),
-                  ("sobel", lambda: pf.sobel(img), lambda: o.sobel(img), 0),
-                  ("canny", lambda: pf.canny(img), lambda: o.canny(img), 0)]
+        if pinned:
+            lib = pin.lib
+            checks = [("gaussian(%g,%d)" % (sigma, n), lambda: pin.call(lib.pf_b200_gaussian, img, sigma, n),
+                       lambda: o.gaussian(img, sigma, n), 0),
+                      ("sobel", lambda: pin.call(lib.pf_b200_sobel, img), lambda: o.sobel(img), 0),
+                      ("canny", lambda: pin.call(lib.pf_b200_canny, img), lambda: o.canny(img), 0)]
+        else:
+            checks = [("gaussian(%g,%d)" % (sigma, n), lambda: pf.gaussian(img, sigma, n), lambda: o.gaussian(img, sigma, n), 0),
+                      ("sobel", lambda: pf.sobel(img), lambda: o.sobel(img), 0),
+                      ("canny", lambda: pf.canny(img), lambda: o.canny(img), 0)]
         if ace:
             slope, limit, ns, seed = ace
             xy = o.ace_draw_samples(ns, w, h, seed)
-            checks.append(("ace(%g,%g,%d)" % (slope, limit, ns), lambda: pf.ace(img, slope, limit, ns, seed=seed),
-                           lambda: o.ace_with_samples(img, xy, slope, limit, nb_threads=4), 1))
+            if pinned:
+                xyp = xy.ctypes.data_as(ctypes.POINTER(ctypes.c_int))
+                checks.append(("ace(%g,%g,%d)" % (slope, limit, ns),
+                               lambda: pin.call(pin.lib.pf_b200_ace, img, ns, xyp, slope, limit),
+                               lambda: o.ace_with_samples(img, xy, slope, limit, nb_threads=8), 1))
+            else:
+                checks.append(("ace(%g,%g,%d)" % (slope, limit, ns), lambda: pf.ace(img, slope, limit, ns, seed=seed),
+                               lambda: o.ace_with_samples(img, xy, slope, limit, nb_threads=4), 1))
         for name, fg, fr, tol in checks:
             got, ref = fg(), fr()
             d = np.abs(got.astype(np.int16) - ref.astype(np.int16))
@@ -83,7 +132,7 @@ def run(cases, seed):
 
 def main():
     cases = int(sys.argv[1]) if len(sys.argv) > 1 else 100
-    bad = run(cases, int(sys.argv[2]) if len(sys.argv) > 2 else 0)
+    bad = run(cases, int(sys.argv[2]) if len(sys.argv) > 2 else 0, pinned="pinned" in sys.argv[3:])
     for line in bad:
         print("MISMATCH", line)
     print("fuzz: %d cases, %d mismatches" % (cases, len(bad)))
