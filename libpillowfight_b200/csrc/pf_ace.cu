@@ -304,6 +304,7 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	AceShared &sh = *reinterpret_cast<AceShared *>(smem_raw);
+	pdl_wait();
 	const int x = blockIdx.x * kAceBlock + threadIdx.x;
 	const int xc = min(x, cs.w - 1);
 	// Tiles sit on a page-wide grid of tile_rows rows whatever the band is, so
@@ -459,6 +460,7 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 
 __global__ void ace_minmax_init_kernel(double *minmax, size_t n)
 {
+	pdl_wait();
 	for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
 			i += (size_t)gridDim.x * blockDim.x)
 		minmax[i] = (i % 6 < 3) ? DBL_MAX : -DBL_MAX;
@@ -583,6 +585,7 @@ ace_refine_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 		int tiles_x, int tiles_y)
 {
 	__shared__ RefineShared sh;
+	pdl_wait();
 	double lo[3], hi[3];
 #pragma unroll
 	for (int c = 0; c < 3; c++) {
@@ -691,6 +694,7 @@ __global__ void __launch_bounds__(256)
 ace_scale_kernel(const double *__restrict__ scores, const double *__restrict__ minmax,
 		size_t npix, size_t plane, uint32_t *__restrict__ out)
 {
+	pdl_wait();
 	double mn[3], span[3], inv[3];
 #pragma unroll
 	for (int c = 0; c < 3; c++) {
@@ -756,8 +760,8 @@ __global__ void fp64_peak_kernel(double *sink, int iters, double a, double b)
 int launch_ace_minmax_init(double *minmax, int w, int h, cudaStream_t st)
 {
 	const size_t n = ace_minmax_doubles(w, h);
-	ace_minmax_init_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(minmax, n);
-	PFB_CUDA(cudaGetLastError());
+	PFB_CUDA(launch_pdl(ace_minmax_init_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st,
+			minmax, n));
 	return PF_B200_OK;
 }
 
@@ -859,8 +863,7 @@ int launch_ace_scores(const uint32_t *in, const int *samples_xy,
 			: rows_env == 8 ? ace_scores_kernel<true, false, 8>
 			: rows_env == 6 ? ace_scores_kernel<true, false, 6> : ace_scores_kernel<true, false, 4>;
 	PFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-	kern<<<grid, kAceBlock, smem, st>>>(in, samples_xy, cs, scores, minmax);
-	PFB_CUDA(cudaGetLastError());
+	PFB_CUDA(launch_pdl(kern, grid, dim3(kAceBlock), smem, st, in, samples_xy, cs, scores, minmax));
 	return PF_B200_OK;
 }
 
@@ -874,9 +877,8 @@ int launch_ace_refine(const uint32_t *in, const int *samples_xy,
 	const int rc = ace_setup(p, cs, grid, fast);
 	if (rc)
 		return rc;
-	ace_refine_kernel<<<sm_count() * 4, kRefineThreads, 0, st>>>(in, samples_xy, cs, scores,
-			minmax, (int)grid.x, (int)grid.y);
-	PFB_CUDA(cudaGetLastError());
+	PFB_CUDA(launch_pdl(ace_refine_kernel, dim3(sm_count() * 4), dim3(kRefineThreads), 0, st,
+			in, samples_xy, cs, scores, minmax, (int)grid.x, (int)grid.y));
 	return PF_B200_OK;
 }
 
@@ -887,9 +889,8 @@ int launch_ace_scale(const double *scores, const double *minmax, int w,
 	const size_t work = (npix + 3) / 4;       // 4 pixels per thread
 	const int blocks = (int)((work + 255) / 256 < (size_t)sm_count() * 8
 			? (work + 255) / 256 : (size_t)sm_count() * 8);
-	ace_scale_kernel<<<blocks, 256, 0, st>>>(scores, minmax, npix,
-			plane >= 0 ? (size_t)plane : npix, out);
-	PFB_CUDA(cudaGetLastError());
+	PFB_CUDA(launch_pdl(ace_scale_kernel, dim3(blocks), dim3(256), 0, st,
+			scores, minmax, npix, plane >= 0 ? (size_t)plane : npix, out));
 	return PF_B200_OK;
 }
 

@@ -39,6 +39,12 @@ void clear_error()
 	t_msg[0] = '\0';
 }
 
+bool pdl_enabled()
+{
+	static const bool on = !getenv("PF_B200_PDL") || atoi(getenv("PF_B200_PDL"));
+	return on;
+}
+
 int sm_count()
 {
 	static thread_local int cached_dev = -1, cached = 148;

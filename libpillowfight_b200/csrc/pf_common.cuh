@@ -70,6 +70,39 @@ int launch_matrix_convolution(const double *img, double *out, int w, int h,
 int launch_gradient_polar(const double *gx, const double *gy, double *intensity,
 		double *direction, size_t n, cudaStream_t st);
 
+// ---- programmatic dependent launch ---------------------------------------
+// Every kernel of this library begins with pdl_wait() and is launched with
+// launch_pdl(): its blocks may be scheduled while the kernel before it on the
+// stream is still draining, and wait (griddepcontrol.wait: until that kernel
+// has completed and its writes are visible) before they touch memory.  What is
+// saved is the launch latency between dependent kernels, a few microseconds
+// each -- 10 launches per page.  PF_B200_PDL=0 turns it off.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait()
+{
+	asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
+bool pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
+		cudaStream_t st, Args... args)
+{
+	cudaLaunchConfig_t cfg = {};
+	cfg.gridDim = grid;
+	cfg.blockDim = block;
+	cfg.dynamicSmemBytes = smem;
+	cfg.stream = st;
+	cudaLaunchAttribute attr[1];
+	attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+	attr[0].val.programmaticStreamSerializationAllowed = 1;
+	cfg.attrs = attr;
+	cfg.numAttrs = pdl_enabled() ? 1 : 0;
+	return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+#endif
+
 // ---- ACE launchers (pf_ace.cu) -------------------------------------------
 struct AceParams {
 	int w, h;

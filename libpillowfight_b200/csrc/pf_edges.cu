@@ -123,6 +123,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 sobel_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
 		const StripGeom g)
 {
+	pdl_wait();
 	const WarpPlace wp = place_warp(g);
 	if (!wp.valid)
 		return;
@@ -295,6 +296,7 @@ canny_classify_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ ou
 		const StripGeom g, CannyThresholds thr,
 		int *__restrict__ hdr, int *__restrict__ list, int *__restrict__ parent)
 {
+	pdl_wait();
 	const WarpPlace wp = place_warp(g);
 	if (!wp.valid)
 		return;
@@ -452,6 +454,7 @@ canny_hysteresis_kernel(uint32_t *out, PageGeom pg, int *list, int *parent,
 	__shared__ int s_pix[kSmallList];
 	__shared__ int s_parent[kSmallList];
 	__shared__ unsigned char s_keep[kSmallList];
+	pdl_wait();
 	const int count = hdr[0];
 	if (count == 0)
 		return;
@@ -541,6 +544,7 @@ canny_hysteresis_kernel(uint32_t *out, PageGeom pg, int *list, int *parent,
 __global__ void canny_patch_kernel(const uint32_t *__restrict__ out, uint32_t *__restrict__ mirror,
 		const int *__restrict__ list, const int *__restrict__ hdr)
 {
+	pdl_wait();
 	const int count = hdr[0];
 	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
 		const int idx = list[i] & ~kStrongBit;
@@ -549,6 +553,40 @@ __global__ void canny_patch_kernel(const uint32_t *__restrict__ out, uint32_t *_
 }
 
 }  // namespace
+
+// Blocks of the hysteresis kernel: its grid must be resident at once (grid
+// barriers); two blocks per SM hide the latency of the long-list path better
+// than one (PF_B200_HYST_BLOCKS).
+static int hysteresis_blocks()
+{
+	int per_sm = 0;
+	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, canny_hysteresis_kernel,
+			kHystThreads, 0) != cudaSuccess || per_sm < 1) {
+		cudaGetLastError();
+		per_sm = 1;
+	}
+	static const int want = getenv("PF_B200_HYST_BLOCKS") ? atoi(getenv("PF_B200_HYST_BLOCKS")) : 2;
+	return sm_count() * (want < per_sm ? (want < 1 ? 1 : want) : per_sm);
+}
+
+// The hysteresis kernel: a cooperative launch (its long-list path uses grid
+// barriers) that may also be scheduled early behind the classification.
+static cudaError_t launch_hysteresis(uint32_t *out, PageGeom pg, int *list, int *parent,
+		const int *hdr, int blocks, cudaStream_t st)
+{
+	cudaLaunchConfig_t cfg = {};
+	cfg.gridDim = dim3(blocks);
+	cfg.blockDim = dim3(kHystThreads);
+	cfg.stream = st;
+	cudaLaunchAttribute attr[2];
+	attr[0].id = cudaLaunchAttributeCooperative;
+	attr[0].val.cooperative = 1;
+	attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+	attr[1].val.programmaticStreamSerializationAllowed = 1;
+	cfg.attrs = attr;
+	cfg.numAttrs = pdl_enabled() ? 2 : 1;
+	return cudaLaunchKernelEx(&cfg, canny_hysteresis_kernel, out, pg, list, parent, hdr);
+}
 
 int launch_sobel(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 		cudaStream_t st, int y_begin, int y_end)
@@ -560,8 +598,7 @@ int launch_sobel(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 	const StripGeom g = make_geom(sobel_kernel, in, out, w, h, pages, 2, y_begin, y_end, 3);
 	const int warps = g.warp_cols * g.strips;
 	dim3 grid((warps + kWarpsPerBlock - 1) / kWarpsPerBlock, pages);
-	sobel_kernel<<<grid, kWarpsPerBlock * 32, 0, st>>>(in, out, g);
-	PFB_CUDA(cudaGetLastError());
+	PFB_CUDA(launch_pdl(sobel_kernel, grid, dim3(kWarpsPerBlock * 32), 0, st, in, out, g));
 	return PF_B200_OK;
 }
 
@@ -594,15 +631,7 @@ int launch_canny(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 	int *hdr = static_cast<int *>(scratch);
 	int *list = hdr + 64;
 	PageGeom pg = { w, h, (int)npix };
-	// the cooperative kernel's grid must be resident at once
-	int coop_per_sm = 0;
-	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&coop_per_sm,
-			canny_hysteresis_kernel, kHystThreads, 0) != cudaSuccess || coop_per_sm < 1) {
-		cudaGetLastError();
-		coop_per_sm = 1;
-	}
-	static const int coop_env = getenv("PF_B200_HYST_BLOCKS") ? atoi(getenv("PF_B200_HYST_BLOCKS")) : 2;
-	const int coop_blocks = sm_count() * (coop_env < coop_per_sm ? coop_env : coop_per_sm);
+	const int coop_blocks = hysteresis_blocks();
 
 	for (int p0 = 0; p0 < pages; p0 += (int)cap_pages) {
 		const int np = (pages - p0 < (int)cap_pages) ? pages - p0 : (int)cap_pages;
@@ -613,14 +642,9 @@ int launch_canny(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 		const StripGeom g = make_geom(canny_classify_kernel, pin, pout, w, h, np, 4, 0, -1, 3);
 		const int warps = g.warp_cols * g.strips;
 		dim3 grid((warps + kWarpsPerBlock - 1) / kWarpsPerBlock, np);
-		canny_classify_kernel<<<grid, kWarpsPerBlock * 32, 0, st>>>(pin, pout, g, thr,
-				hdr, list, parent);
-		PFB_CUDA(cudaGetLastError());
-		const int *chdr = hdr;
-		void *args[] = { &pout, &pg, &list, &parent, &chdr };
-		PFB_CUDA(cudaLaunchCooperativeKernel(
-				reinterpret_cast<void *>(canny_hysteresis_kernel),
-				dim3(coop_blocks), dim3(kHystThreads), args, 0, st));
+		PFB_CUDA(launch_pdl(canny_classify_kernel, grid, dim3(kWarpsPerBlock * 32), 0, st,
+				pin, pout, g, thr, hdr, list, parent));
+		PFB_CUDA(launch_hysteresis(pout, pg, list, parent, hdr, coop_blocks, st));
 	}
 	return PF_B200_OK;
 }
@@ -658,8 +682,8 @@ int launch_canny_classify_rows(const uint32_t *in, uint32_t *out, int w, int h,
 	const StripGeom g = make_geom(canny_classify_kernel, in, out, w, h, 1, 4, y_begin, y_end, 3);
 	const int warps = g.warp_cols * g.strips;
 	dim3 grid((warps + kWarpsPerBlock - 1) / kWarpsPerBlock, 1);
-	canny_classify_kernel<<<grid, kWarpsPerBlock * 32, 0, st>>>(in, out, g, thr, hdr, list, parent);
-	PFB_CUDA(cudaGetLastError());
+	PFB_CUDA(launch_pdl(canny_classify_kernel, grid, dim3(kWarpsPerBlock * 32), 0, st,
+			in, out, g, thr, hdr, list, parent));
 	return PF_B200_OK;
 }
 
@@ -669,10 +693,7 @@ int launch_canny_resolve(uint32_t *out, int w, int h, void *scratch, cudaStream_
 	int *list = hdr + 64;
 	int *parent = list + (size_t)w * h;
 	PageGeom pg = { w, h, w * h };
-	const int *chdr = hdr;
-	void *args[] = { &out, &pg, &list, &parent, &chdr };
-	PFB_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(canny_hysteresis_kernel),
-			dim3(sm_count()), dim3(kHystThreads), args, 0, st));
+	PFB_CUDA(launch_hysteresis(out, pg, list, parent, hdr, hysteresis_blocks(), st));
 	return PF_B200_OK;
 }
 
@@ -681,8 +702,8 @@ int launch_canny_resolve(uint32_t *out, int w, int h, void *scratch, cudaStream_
 int launch_canny_patch(const uint32_t *out, uint32_t *mirror, void *scratch, cudaStream_t st)
 {
 	const int *hdr = static_cast<const int *>(scratch);
-	canny_patch_kernel<<<sm_count(), 256, 0, st>>>(out, mirror, hdr + 64, hdr);
-	PFB_CUDA(cudaGetLastError());
+	PFB_CUDA(launch_pdl(canny_patch_kernel, dim3(sm_count()), dim3(256), 0, st,
+			out, mirror, hdr + 64, hdr));
 	return PF_B200_OK;
 }
 

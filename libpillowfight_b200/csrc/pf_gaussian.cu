@@ -56,6 +56,7 @@ __global__ void __launch_bounds__(kBlock)
 gaussian_march_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
 		int w, int h, int y_begin, int y_end, int rows_per_strip, const TapsN<N> tp)
 {
+	pdl_wait();
 	constexpr int C = N / 2;             // taps reach x+C ... x-(N-1-C)
 	constexpr int L = N - 1 - C;         // left / up reach
 	constexpr int NPIX = PX + N - 1;     // input pixels a thread needs per row
@@ -220,6 +221,7 @@ __global__ void __launch_bounds__(kBlock)
 gaussian_generic_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
 		int w, int h, int y_begin, const Taps tp)
 {
+	pdl_wait();
 	const int x = blockIdx.x * kBlock + threadIdx.x;
 	const int y = y_begin + blockIdx.y;
 	if (x >= w)
@@ -445,6 +447,7 @@ gaussian_fast_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out
 		const StripGeom g, const FastTaps<N> tp)
 {
 	__shared__ unsigned char flat_lut[256];
+	pdl_wait();
 	for (int i = threadIdx.x; i < 256; i += blockDim.x)
 		flat_lut[i] = tp.flat[i];
 	__syncthreads();
@@ -520,7 +523,7 @@ static void launch_gaussian_fast(const uint32_t *in, uint32_t *out, int w, int h
 			y_begin, y_end, N);
 	const int warps = g.warp_cols * g.strips;
 	dim3 grid((warps + kWarpsPerBlock - 1) / kWarpsPerBlock, pages);
-	gaussian_fast_kernel<N><<<grid, kWarpsPerBlock * 32, 0, st>>>(in, out, g, tp);
+	launch_pdl(gaussian_fast_kernel<N>, grid, dim3(kWarpsPerBlock * 32), 0, st, in, out, g, tp);
 }
 
 template <int N>
@@ -535,7 +538,8 @@ static void launch_gaussian_n(const uint32_t *in, uint32_t *out, int w, int h,
 	const int nrows = y_end - y_begin;
 	const int rows = strips_for(bx, nrows, pages, 4, 8 * N);
 	dim3 grid(bx, (nrows + rows - 1) / rows, pages);
-	gaussian_march_kernel<N, PX><<<grid, kBlock, 0, st>>>(in, out, w, h, y_begin, y_end, rows, tp);
+	launch_pdl(gaussian_march_kernel<N, PX>, grid, dim3(kBlock), 0, st, in, out, w, h, y_begin, y_end,
+			rows, tp);
 }
 
 int launch_gaussian(const uint32_t *in, uint32_t *out, int w, int h, int pages,
@@ -566,7 +570,7 @@ int launch_gaussian(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 	case 9: launch_gaussian_n<9>(in, out, w, h, pages, taps, st, y_begin, y_end); break;
 	default: {
 		dim3 grid((w + kBlock - 1) / kBlock, y_end - y_begin, pages);
-		gaussian_generic_kernel<<<grid, kBlock, 0, st>>>(in, out, w, h, y_begin, taps);
+		launch_pdl(gaussian_generic_kernel, grid, dim3(kBlock), 0, st, in, out, w, h, y_begin, taps);
 	}
 	}
 	PFB_CUDA(cudaGetLastError());
