@@ -272,6 +272,15 @@ int pf_b200_dev_ace_scores(const uint32_t *d_in, int width, int height,
 int pf_b200_dev_ace_scale(const double *d_scores, const double *d_minmax,
 		int width, int nb_rows, uint32_t *d_out_band, void *stream);
 
+/* The five passes above for one whole page on one GPU, with one caller-owned
+ * work area of pf_b200_ace_workspace_bytes(width, height) bytes (the score
+ * planes, 24 bytes per pixel, and the min/max block; 256-byte aligned).
+ * upstream _ace.c: pf_ace on a page resident in HBM. */
+size_t pf_b200_ace_workspace_bytes(int width, int height);
+int pf_b200_dev_ace(const uint32_t *d_in, uint32_t *d_out, int width, int height,
+		const int *d_samples, int nb_samples, double slope, double limit,
+		void *d_workspace, size_t workspace_bytes, void *stream);
+
 /* Measures the FP64 FMA rate of the current device (the ACE roofline
  * denominator): returns TFLOP/s (FMA = 2 flops), or a negative PF_B200_E*. */
 double pf_b200_fp64_peak_tflops(void);

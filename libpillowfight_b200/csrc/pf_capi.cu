@@ -941,6 +941,45 @@ int pf_b200_dev_ace_scale(const double *d_scores, const double *d_minmax,
 			static_cast<cudaStream_t>(stream));
 }
 
+size_t pf_b200_ace_workspace_bytes(int width, int height)
+{
+	clear_error();
+	if (width <= 0 || height <= 0) {
+		fail(PF_B200_EINVAL, "size %d x %d", width, height);
+		return 0;
+	}
+	const size_t scores = 3 * sizeof(double) * (size_t)width * height;
+	return (scores + 255) / 256 * 256 + ace_minmax_doubles(width, height) * sizeof(double);
+}
+
+int pf_b200_dev_ace(const uint32_t *d_in, uint32_t *d_out, int width, int height,
+		const int *d_samples, int nb_samples, double slope, double limit,
+		void *d_workspace, size_t workspace_bytes, void *stream)
+{
+	clear_error();
+	if (!d_in || !d_out || !d_samples || !d_workspace)
+		return fail(PF_B200_EINVAL, "NULL device pointer");
+	if (width <= 0 || height <= 0)
+		return fail(PF_B200_EINVAL, "size %d x %d", width, height);
+	if (d_in == d_out)
+		return fail(PF_B200_EINVAL, "ace: the device entry point is out of place");
+	if (workspace_bytes < pf_b200_ace_workspace_bytes(width, height) || ((uintptr_t)d_workspace & 255))
+		return fail(PF_B200_EINVAL, "ace: work area of %zu bytes, need %zu, 256-byte aligned",
+				workspace_bytes, pf_b200_ace_workspace_bytes(width, height));
+	cudaStream_t st = static_cast<cudaStream_t>(stream);
+	double *scores = static_cast<double *>(d_workspace);
+	const size_t score_bytes = (3 * sizeof(double) * (size_t)width * height + 255) / 256 * 256;
+	double *minmax = reinterpret_cast<double *>(static_cast<char *>(d_workspace) + score_bytes);
+	AceParams p = { width, height, 0, height, nb_samples, slope, limit };
+	int rc;
+	if ((rc = launch_ace_minmax_init(minmax, width, height, st))
+			|| (rc = launch_ace_scores(d_in, d_samples, p, scores, minmax, st))
+			|| (rc = launch_ace_refine(d_in, d_samples, p, scores, minmax, st))
+			|| (rc = launch_ace_scale(scores, minmax, width, height, d_out, st)))
+		return rc;
+	return PF_B200_OK;
+}
+
 double pf_b200_fp64_peak_tflops(void)
 {
 	clear_error();

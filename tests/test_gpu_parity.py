@@ -503,6 +503,36 @@ def test_device_batch_entry_points(gpu, oracle):
         assert np.array_equal(c5[i].cpu().numpy(), rc)
 
 
+def test_device_ace_whole_page(gpu, oracle):
+    """pf_b200_dev_ace: the ACE passes for a page resident in HBM, one call, one
+    caller-owned work area; same result as the host-pointer entry point."""
+    import torch
+    from libpillowfight_b200 import _capi
+    from libpillowfight_b200.distributed import xy_tensor
+    lib = _capi.lib
+    dev = torch.device("cuda:0")
+    w, h, n = 212, 160, 50
+    page = synthetic_page(w, h, 12)
+    xy = oracle.ace_draw_samples(n, w, h, 9)
+    tin, txy = torch.from_numpy(page).to(dev), xy_tensor(xy, dev)
+    out = torch.empty_like(tin)
+    need = lib.pf_b200_ace_workspace_bytes(w, h)
+    assert need >= 24 * w * h
+    work = torch.empty(need, dtype=torch.uint8, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    _capi.check(lib.pf_b200_dev_ace(tin.data_ptr(), out.data_ptr(), w, h, txy.data_ptr(), n, 10.0, 1000.0,
+                                    work.data_ptr(), need, st))
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    assert_fp_parity(got, oracle.ace_with_samples(page, xy, 10.0, 1000.0, nb_threads=4), "dev ace")
+    assert np.array_equal(got, gpu.ace(page, 10, 1000, n, seed=9))
+    # too small a work area, in place: refused
+    assert lib.pf_b200_dev_ace(tin.data_ptr(), out.data_ptr(), w, h, txy.data_ptr(), n, 10.0, 1000.0,
+                               work.data_ptr(), need - 1, st) == _capi.PF_B200_EINVAL
+    assert lib.pf_b200_dev_ace(tin.data_ptr(), tin.data_ptr(), w, h, txy.data_ptr(), n, 10.0, 1000.0,
+                               work.data_ptr(), need, st) == _capi.PF_B200_EINVAL
+
+
 @pytest.mark.parametrize("w,h", [(5, 4), (33, 17), (124, 61), (128, 40), (257, 129), (620, 300)])
 def test_no_writes_outside_the_output_page(gpu, oracle, w, h):
     """compute-sanitizer is not available on this pool, so: guard bands of a
