@@ -32,6 +32,43 @@ def device_count():
     return lib.pf_b200_device_count()
 
 
+def _pil_pixels(img):
+    """The pixels of a PIL image as an (H, W, 4) uint8 array in pinned memory.
+
+    Upstream converts with img.convert("RGBA") and hands Pillow's bytes to C.
+    Here RGBA and RGB images are packed band by band by Pillow's own raw
+    encoder (what tobytes() uses) straight into a pooled pinned buffer: no
+    35 MB bytes object per call (whose fresh pages cost more than the copy)
+    and, for RGB, no conversion pass -- Pillow stores RGB as four bytes per
+    pixel and none of the four operations reads the fourth.  Other modes are
+    converted first, as upstream does."""
+    from PIL import Image
+    if img.mode not in ("RGBA", "RGB"):
+        img = img.convert("RGBA")
+    img.load()
+    w, h = img.size
+    arr = _pool.empty((h, w, 4))
+    if w == 0 or h == 0:
+        return arr
+    rawmode = "RGBA" if img.mode == "RGBA" else "RGBX"
+    flat = arr.reshape(-1)
+    rows = max(1, (4 << 20) // (4 * w))
+    for y0 in range(0, h, rows):
+        y1 = min(h, y0 + rows)
+        enc = Image._getencoder(img.mode, "raw", rawmode)
+        enc.setimage(img.im, (0, y0, w, y1))
+        off, end = 4 * w * y0, 4 * w * y1
+        while True:
+            _, err, data = enc.encode(end - off + 64)
+            flat[off:off + len(data)] = np.frombuffer(data, dtype=np.uint8)
+            off += len(data)
+            if err:
+                break
+        if err < 0 or off != end:
+            raise RuntimeError("Pillow's raw encoder failed (%d)" % err)
+    return arr
+
+
 def _to_array(img_in):
     """-> (array (H, W, 4) uint8 C-contiguous, was_pil)"""
     if isinstance(img_in, np.ndarray):
@@ -39,18 +76,17 @@ def _to_array(img_in):
         if arr.ndim != 3 or arr.shape[2] != 4:
             raise ValueError("expected an (H, W, 4) uint8 RGBA array")
         return arr, False
-    # PIL image: same conversion as upstream (img_in.convert("RGBA"))
-    rgba = img_in.convert("RGBA")
-    arr = np.frombuffer(rgba.tobytes(), dtype=np.uint8).reshape(
-        rgba.size[1], rgba.size[0], 4)
-    return arr, True
+    return _pil_pixels(img_in), True
 
 
 def _from_array(arr, was_pil):
     if not was_pil:
         return arr
     from PIL import Image
-    return Image.frombytes("RGBA", (arr.shape[1], arr.shape[0]), arr.tobytes())
+    # The image wraps the result buffer (pinned memory the device wrote by
+    # DMA) instead of copying it twice; it keeps the buffer alive, and Pillow
+    # copies on the first in-place modification (the image is read-only).
+    return Image.frombuffer("RGBA", (arr.shape[1], arr.shape[0]), arr, "raw", "RGBA", 0, 1)
 
 
 class _PinnedPool:
@@ -63,18 +99,21 @@ class _PinnedPool:
     def __init__(self):
         self._free = {}
 
-    def empty_like(self, arr):
+    def empty(self, shape):
         import weakref
-        n = arr.nbytes
+        n = int(np.prod(shape))
         if n == 0:
-            return np.empty_like(arr)
+            return np.empty(shape, dtype=np.uint8)
         bucket = self._free.setdefault(n, [])
         ptr = bucket.pop() if bucket else lib.pf_b200_host_alloc(n)
         if not ptr:
-            return np.empty_like(arr)          # no device / no pinned memory: plain array
+            return np.empty(shape, dtype=np.uint8)     # no device / no pinned memory: plain array
         raw = (ctypes.c_uint8 * n).from_address(ptr)
         weakref.finalize(raw, self._release, n, ptr)
-        return np.frombuffer(raw, dtype=np.uint8).reshape(arr.shape)
+        return np.frombuffer(raw, dtype=np.uint8).reshape(shape)
+
+    def empty_like(self, arr):
+        return self.empty(arr.shape)
 
     def _release(self, n, ptr):
         bucket = self._free.setdefault(n, [])

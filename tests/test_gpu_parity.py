@@ -640,6 +640,31 @@ def test_pil_images_round_trip(gpu, oracle):
     out = gpu.sobel(img)
     assert out.mode == "RGBA" and out.size == (90, 70)
     assert np.array_equal(np.asarray(out), oracle.sobel(page))
+    # an RGBA image goes in as it is; the result image wraps the (pooled,
+    # pinned) result buffer: it must outlive other calls and survive edits
+    import gc
+    rgba = Image.fromarray(page, "RGBA")
+    outs = [gpu.gaussian(rgba), gpu.canny(rgba), gpu.ace(rgba, samples=20, seed=3)]
+    for _ in range(6):
+        gpu.sobel(rgba)                                   # churn the buffer pool
+    gc.collect()
+    assert np.array_equal(np.asarray(outs[0]), oracle.gaussian(page, 2.0, 5))
+    assert np.array_equal(np.asarray(outs[1]), oracle.canny(page))
+    assert_fp_parity(np.asarray(outs[2]), oracle.ace_with_samples(
+        page, oracle.ace_draw_samples(20, 90, 70, 3), 10.0, 1000.0), "ace PIL")
+    edited = outs[1].copy()
+    edited.putpixel((0, 0), (1, 2, 3, 4))
+    outs[1].putpixel((1, 1), (5, 6, 7, 8))               # Pillow copies before writing
+    assert outs[1].getpixel((1, 1)) == (5, 6, 7, 8)
+    assert np.array_equal(np.asarray(gpu.canny(rgba)), oracle.canny(page))
+    # other modes are converted to RGBA first, as upstream does
+    gray = rgba.convert("L")
+    as_rgba = np.asarray(gray.convert("RGBA"))
+    assert np.array_equal(np.asarray(gpu.sobel(gray)), oracle.sobel(as_rgba))
+    # a tall image (the pinned, band-pipelined path) from an RGB image
+    tall = synthetic_page(260, 700, 5)
+    assert np.array_equal(np.asarray(gpu.gaussian(Image.fromarray(tall[..., :3], "RGB"))),
+                          oracle.gaussian(tall, 2.0, 5))
 
 
 # ---- BASELINE.json's full sizes ----------------------------------------
