@@ -179,8 +179,9 @@ __device__ __noinline__ void stage_samples(AceShared &sh, const AceConst &cs,
 	__shared__ int counts[kPasses][kWarps][2];
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const int2 *xy = reinterpret_cast<const int2 *>(samples_xy) + k0;
+	const int passes = (kn + kAceBlock - 1) / kAceBlock;      // 1 for the usual 100 samples
 	// sweep 1: how many far / straddling samples each warp holds per pass
-	for (int p = 0; p < kPasses; p++) {
+	for (int p = 0; p < passes; p++) {
 		const int k = p * kAceBlock + threadIdx.x;
 		int cls = 0;
 		if (k < kn) {
@@ -196,12 +197,12 @@ __device__ __noinline__ void stage_samples(AceShared &sh, const AceConst &cs,
 	}
 	__syncthreads();
 	int n_far = 0;
-	for (int i = 0; i < kPasses * kWarps; i++)
+	for (int i = 0; i < passes * kWarps; i++)
 		n_far += counts[0][i][0];
 	// sweep 2: ordered compaction -- far samples first, then straddling, each
 	// class in sample order, so sums are reproducible
 	int off_far = 0, off_str = n_far;
-	for (int p = 0; p < kPasses; p++) {
+	for (int p = 0; p < passes; p++) {
 		for (int wv = 0; wv < warp; wv++) {
 			off_far += counts[p][wv][0];
 			off_str += counts[p][wv][1];
@@ -405,18 +406,19 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 			if (y >= cs.row_begin && y < cs.row_end && y < tile_y1 && x < cs.w) {
 				const size_t o = (size_t)(y - cs.score_row0) * cs.w + x;
 				// FAST: acc holds sum(w (c + L)); c / L = (acc - top/2) / (top/2)
-				const bool live = top[r] > 0.0;    // else every sample skipped: 0/0
+				// Every sample skipped (top == 0): the reference divides 0 by 0.
+				// Here reciprocal(0) is NaN and so is the product below; only
+				// the tie comparisons (0 == 0) have to be kept from firing.
+				const bool live = top[r] > 0.0;
 				const double den = FAST ? 0.5 * top[r] : top[r];
 				const double inv = reciprocal(den);
 #pragma unroll
 				for (int c = 0; c < 3; c++) {
 					const double num = FAST ? acc[r][c] - den : acc[r][c];
-					const bool tie_hi = num == den, tie_lo = num == -den;
+					const bool tie_hi = live && num == den, tie_lo = live && num == -den;
 					double s = num * inv;           // exactly 0 when num is
 					s = tie_hi ? 1.0 : s;
 					s = tie_lo ? -1.0 : s;
-					if (!live)              // NaN like the reference
-						s = __longlong_as_double(0x7FF8000000000000LL);
 					scores[c * plane + o] = s;
 					if (s < mn[c]) mn[c] = s;     // NaN never enters
 					if (s > mx[c]) mx[c] = s;
