@@ -148,7 +148,6 @@ struct AceConst {
 	int score_row0;        // score row stored first in `scores`
 	long score_plane;      // doubles between the R, G, B score planes
 	const uint32_t *sample_px;   // samples' pixel values, or NULL: read them from the page
-	double ratio;          // slope / limit
 	double slope, limit;
 };
 
@@ -815,7 +814,6 @@ int ace_setup(const AceParams &p, AceConst &cs, dim3 &grid, bool &fast)
 	cs.sample_px = p.sample_px;
 	cs.score_row0 = p.score_row0 >= 0 ? p.score_row0 : p.row_begin;
 	cs.score_plane = p.score_plane >= 0 ? p.score_plane : (long)(p.row_end - p.row_begin) * p.w;
-	cs.ratio = p.slope / p.limit;
 	// fast path: saturate(slope*d) == slope*clamp(d, -L, L) with integer L <= 127
 	const double l = p.limit / p.slope;
 	fast = l >= 1.0 && l <= 127.0 && l == floor(l) && p.slope * l == p.limit;

@@ -496,28 +496,37 @@ template <int N>
 static void launch_gaussian_fast(const uint32_t *in, uint32_t *out, int w, int h,
 		int pages, const Taps &taps, cudaStream_t st, int y_begin, int y_end)
 {
-	FastTaps<N> tp;
-	for (int k = 0; k < N; k++) {
-		tp.t[k] = taps.t[k];
-		tp.th[k] = taps.t[k] * 0x1p+1000;
-		tp.tv[k] = taps.t[k] * 0x1p+34;
-	}
-	for (int v = 0; v < 256; v++) {
-		// the reference's loops on a window of equal values (upstream util.c
-		// pf_dbl_matrix_convolution, twice; oracle/pf_oracle.c): every product
-		// and every sum rounded, horizontal pass first
-		volatile double acc = 0.0;
-		for (int ky = 0; ky < N; ky++) {
-			volatile double hv = 0.0;
-			for (int kx = 0; kx < N; kx++) {
-				volatile double prod = (double)v * taps.t[kx];
-				hv = hv + prod;
-			}
-			volatile double prod = hv * taps.t[ky];
-			acc = acc + prod;
+	// the table costs ~13k strict operations on the host: kept per thread for
+	// as long as the taps stay the same (the usual case: one sigma per run)
+	static thread_local FastTaps<N> tp;
+	static thread_local bool tp_valid = false;
+	bool same = tp_valid;
+	for (int k = 0; k < N && same; k++)
+		same = tp.t[k] == taps.t[k];
+	if (!same) {
+		for (int k = 0; k < N; k++) {
+			tp.t[k] = taps.t[k];
+			tp.th[k] = taps.t[k] * 0x1p+1000;
+			tp.tv[k] = taps.t[k] * 0x1p+34;
 		}
-		const int r = (int)acc;
-		tp.flat[v] = (unsigned char)(r > 255 ? 255 : r);
+		for (int v = 0; v < 256; v++) {
+			// the reference's loops on a window of equal values (upstream util.c
+			// pf_dbl_matrix_convolution, twice; oracle/pf_oracle.c): every product
+			// and every sum rounded, horizontal pass first
+			volatile double acc = 0.0;
+			for (int ky = 0; ky < N; ky++) {
+				volatile double hv = 0.0;
+				for (int kx = 0; kx < N; kx++) {
+					volatile double prod = (double)v * taps.t[kx];
+					hv = hv + prod;
+				}
+				volatile double prod = hv * taps.t[ky];
+				acc = acc + prod;
+			}
+			const int r = (int)acc;
+			tp.flat[v] = (unsigned char)(r > 255 ? 255 : r);
+		}
+		tp_valid = true;
 	}
 	const StripGeom g = make_geom(gaussian_fast_kernel<N>, in, out, w, h, pages, N - 1,
 			y_begin, y_end, N);
