@@ -183,15 +183,21 @@ static void *device_alias(const void *p)
 // slice's DMA itself, so the first DMA starts while the others still copy.
 constexpr size_t kParallelMin = (size_t)8 << 20;       // bytes
 constexpr size_t kParallelMax = (size_t)1 << 30;
-constexpr int kCopyThreads = 4;
+constexpr int kCopyThreadsMax = 16;
+static int copy_threads()
+{
+	static const int n = getenv("PF_B200_COPY_THREADS") ? atoi(getenv("PF_B200_COPY_THREADS")) : 4;
+	return n < 1 ? 1 : (n > kCopyThreadsMax ? kCopyThreadsMax : n);
+}
 
 static int upload_threads(Context &c, void *dst, const void *src, size_t bytes)
 {
 	int rc = grow(c.h_stage, bytes, true);
 	if (rc)
 		return rc;
+	const int kCopyThreads = copy_threads();
 	const size_t slice = ((bytes + kCopyThreads - 1) / kCopyThreads + 4095) & ~(size_t)4095;
-	cudaError_t errs[kCopyThreads] = {};
+	cudaError_t errs[kCopyThreadsMax] = {};
 	auto work = [&](int i) {
 		const size_t off = (size_t)i * slice;
 		if (off >= bytes)
@@ -203,12 +209,12 @@ static int upload_threads(Context &c, void *dst, const void *src, size_t bytes)
 		errs[i] = cudaMemcpyAsync(static_cast<char *>(dst) + off, stage, n,
 				cudaMemcpyHostToDevice, c.st);
 	};
-	std::thread th[kCopyThreads - 1];
+	std::thread th[kCopyThreadsMax - 1];
 	for (int i = 1; i < kCopyThreads; i++)
 		th[i - 1] = std::thread(work, i);
 	work(0);
-	for (auto &t : th)
-		t.join();
+	for (int i = 1; i < kCopyThreads; i++)
+		th[i - 1].join();
 	for (cudaError_t e : errs)
 		if (e != cudaSuccess)
 			return fail(PF_B200_ECUDA, "upload: %s", cudaGetErrorString(e));
@@ -220,6 +226,7 @@ static int download_threads(Context &c, void *dst, const void *src, size_t bytes
 	int rc = grow(c.h_stage, bytes, true);
 	if (rc)
 		return rc;
+	const int kCopyThreads = copy_threads();      // (ev_done[] has kMaxBands = 16 entries)
 	const size_t slice = ((bytes + kCopyThreads - 1) / kCopyThreads + 4095) & ~(size_t)4095;
 	for (int i = 0; i < kCopyThreads; i++) {
 		const size_t off = (size_t)i * slice;
@@ -230,7 +237,7 @@ static int download_threads(Context &c, void *dst, const void *src, size_t bytes
 				static_cast<const char *>(src) + off, n, cudaMemcpyDeviceToHost, c.st));
 		PFB_CUDA(cudaEventRecord(c.ev_done[i], c.st));
 	}
-	cudaError_t errs[kCopyThreads] = {};
+	cudaError_t errs[kCopyThreadsMax] = {};
 	auto work = [&](int i) {
 		const size_t off = (size_t)i * slice;
 		if (off >= bytes)
@@ -240,12 +247,12 @@ static int download_threads(Context &c, void *dst, const void *src, size_t bytes
 		errs[i] = cudaEventSynchronize(c.ev_done[i]);
 		memcpy(static_cast<char *>(dst) + off, static_cast<char *>(c.h_stage.p) + off, n);
 	};
-	std::thread th[kCopyThreads - 1];
+	std::thread th[kCopyThreadsMax - 1];
 	for (int i = 1; i < kCopyThreads; i++)
 		th[i - 1] = std::thread(work, i);
 	work(0);
-	for (auto &t : th)
-		t.join();
+	for (int i = 1; i < kCopyThreads; i++)
+		th[i - 1].join();
 	for (cudaError_t e : errs)
 		if (e != cudaSuccess)
 			return fail(PF_B200_ECUDA, "download: %s", cudaGetErrorString(e));
