@@ -507,20 +507,29 @@ def run_b200(args):
         torch.cuda.synchronize()
         a.record()
         for _ in range(n6):
-            ace_sharded(big, xy6, 10.0, 1000.0, comp)
+            out6 = ace_sharded(big, xy6, 10.0, 1000.0, comp)
         b.record()
         torch.cuda.synchronize()
         barrier()
         t6 = torch.tensor([a.elapsed_time(b) / n6], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t6, op=dist.ReduceOp.MAX)
+        # the split must not change the result: rank 0 (which holds the page)
+        # redoes it alone and compares bit for bit
+        same6 = None
+        if rank == 0:
+            mm6 = comp.new_minmax(dev, w6, h6)
+            sc6 = comp.scores(big, xy6, 10.0, 1000.0, (0, h6), mm6)
+            comp.refine(big, xy6, 10.0, 1000.0, (0, h6), sc6, mm6)
+            same6 = bool(torch.equal(comp.scale(sc6, mm6), out6))
+            del sc6
         extras["ace_600dpi_row_bands"] = {
-            "workload": "pf_apply_ace 4960x7016, 400 samples, rows split over %d GPU(s); "
-                        "NCCL broadcast + min/max all-reduce + band all-gather inside the timed region"
-                        % world,
+            "workload": "pf_apply_ace 4960x7016, 400 samples, rows split over %d GPU(s); NCCL scatter "
+                        "of the bands + broadcast of the samples' pixel values + two 6-double min/max "
+                        "all-reduces + band all-gather inside the timed region" % world,
             "ms": float(t6.item()), "mpx_s": w6 * h6 / (float(t6.item()) * 1e-3) / 1e6,
-            "scaling": "strong"}
-        del big
+            "scaling": "strong", "equals_single_gpu_result": same6}
+        del big, out6
 
         # ---- extras: page batch through the stencil chain (BASELINE.json config 5:
         # 512 pages over 8 GPUs = 64 pages per GPU; pages are independent, no collective)

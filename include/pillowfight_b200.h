@@ -272,6 +272,22 @@ int pf_b200_dev_ace_scores(const uint32_t *d_in, int width, int height,
 int pf_b200_dev_ace_scale(const double *d_scores, const double *d_minmax,
 		int width, int nb_rows, uint32_t *d_out_band, void *stream);
 
+/* The same two passes for a GPU that holds only its band of the page: d_band
+ * points at row row_begin (rows [row_begin, row_end) back to back) and
+ * d_sample_px holds the nb_samples sample pixels' values, gathered where the
+ * whole page is (page[y_k * width + x_k]).  A row-band split then moves
+ * height/N rows to each GPU instead of the whole page. */
+int pf_b200_dev_ace_scores_band(const uint32_t *d_band, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, const uint32_t *d_sample_px, int nb_samples,
+		double slope, double limit,
+		double *d_scores, double *d_minmax, void *stream);
+int pf_b200_dev_ace_refine_band(const uint32_t *d_band, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, const uint32_t *d_sample_px, int nb_samples,
+		double slope, double limit,
+		double *d_scores, double *d_minmax, void *stream);
+
 /* The five passes above for one whole page on one GPU, with one caller-owned
  * work area of pf_b200_ace_workspace_bytes(width, height) bytes (the score
  * planes, 24 bytes per pixel, and the min/max block; 256-byte aligned).

@@ -102,6 +102,12 @@ SIGNATURES = {
                                               ctypes.c_int, _vp, ctypes.c_int, ctypes.c_double,
                                               ctypes.c_double, _vp, _vp, _vp]),
     "pf_b200_dev_ace_scale": (ctypes.c_int, [_vp, _vp, ctypes.c_int, ctypes.c_int, _u32p, _vp]),
+    "pf_b200_dev_ace_scores_band": (ctypes.c_int, [_u32p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                                   ctypes.c_int, _vp, _vp, ctypes.c_int, ctypes.c_double,
+                                                   ctypes.c_double, _vp, _vp, _vp]),
+    "pf_b200_dev_ace_refine_band": (ctypes.c_int, [_u32p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                                   ctypes.c_int, _vp, _vp, ctypes.c_int, ctypes.c_double,
+                                                   ctypes.c_double, _vp, _vp, _vp]),
     "pf_b200_ace_workspace_bytes": (ctypes.c_size_t, [ctypes.c_int, ctypes.c_int]),
     "pf_b200_dev_ace": (ctypes.c_int, [_u32p, _u32p, ctypes.c_int, ctypes.c_int, _vp, ctypes.c_int,
                                        ctypes.c_double, ctypes.c_double, _vp, ctypes.c_size_t, _vp]),

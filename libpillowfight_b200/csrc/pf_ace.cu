@@ -339,11 +339,13 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 	for (int y0 = tile_y0; y0 < tile_y1; y0 += P) {
 		if (y0 + P <= cs.row_begin || y0 >= cs.row_end)
 			continue;       // row group outside this band (block-uniform)
-		// pixel values of this thread's P rows (rows past the page repeat the last)
+		// pixel values of this thread's P rows; rows of the group outside the band
+		// repeat the nearest one inside (their scores are not stored), so only
+		// the band's own rows of `in` are ever read
 		uint32_t pix[P];
 #pragma unroll
 		for (int r = 0; r < P; r++)
-			pix[r] = __ldg(in + (size_t)min(y0 + r, cs.h - 1) * cs.w + xc);
+			pix[r] = __ldg(in + (size_t)min(max(y0 + r, cs.row_begin), cs.row_end - 1) * cs.w + xc);
 		// one channel value per register (the clamp instruction wants them so)
 		uint32_t pv[P][3];
 #pragma unroll

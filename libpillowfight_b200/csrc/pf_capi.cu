@@ -948,6 +948,46 @@ int pf_b200_dev_ace_scale(const double *d_scores, const double *d_minmax,
 			static_cast<cudaStream_t>(stream));
 }
 
+static int ace_band_call(bool refine, const uint32_t *d_band, int width, int height,
+		int row_begin, int row_end, const int *d_samples, const uint32_t *d_sample_px,
+		int nb_samples, double slope, double limit, double *d_scores, double *d_minmax,
+		void *stream)
+{
+	clear_error();
+	if (!d_band || !d_samples || !d_sample_px || !d_scores || !d_minmax)
+		return fail(PF_B200_EINVAL, "NULL device pointer");
+	if (width <= 0 || height <= 0)
+		return fail(PF_B200_EINVAL, "size %d x %d", width, height);
+	if (row_begin < 0 || row_begin >= row_end || row_end > height)
+		return fail(PF_B200_EINVAL, "ace: bad row band [%d, %d) of %d rows", row_begin, row_end, height);
+	AceParams p = { width, height, row_begin, row_end, nb_samples, slope, limit };
+	p.sample_px = d_sample_px;
+	// the kernels index the page; with the samples' values given they only
+	// ever read rows [row_begin, row_end) of it
+	const uint32_t *page = d_band - (size_t)row_begin * width;
+	cudaStream_t st = static_cast<cudaStream_t>(stream);
+	return refine ? launch_ace_refine(page, d_samples, p, d_scores, d_minmax, st)
+	              : launch_ace_scores(page, d_samples, p, d_scores, d_minmax, st);
+}
+
+int pf_b200_dev_ace_scores_band(const uint32_t *d_band, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, const uint32_t *d_sample_px, int nb_samples,
+		double slope, double limit, double *d_scores, double *d_minmax, void *stream)
+{
+	return ace_band_call(false, d_band, width, height, row_begin, row_end, d_samples, d_sample_px,
+			nb_samples, slope, limit, d_scores, d_minmax, stream);
+}
+
+int pf_b200_dev_ace_refine_band(const uint32_t *d_band, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, const uint32_t *d_sample_px, int nb_samples,
+		double slope, double limit, double *d_scores, double *d_minmax, void *stream)
+{
+	return ace_band_call(true, d_band, width, height, row_begin, row_end, d_samples, d_sample_px,
+			nb_samples, slope, limit, d_scores, d_minmax, stream);
+}
+
 size_t pf_b200_ace_workspace_bytes(int width, int height)
 {
 	clear_error();

@@ -2,11 +2,13 @@
 for the plumbing (NCCL on GPUs, gloo in the CPU tests).
 
 Only the two splits BASELINE.json names:
-  * ACE: the page is broadcast, each rank accumulates the scores of one band
-    of rows, the per-channel min/max are all-reduced (6 doubles -- the one
-    real exchange the algorithm has; a second time for the scores at the
-    extremes once they have been recomputed exactly), each rank rescales its
-    band, and the bands are all-gathered.
+  * ACE: every rank gets its band of rows (scatter) and the N sample pixels'
+    values (a few hundred bytes, broadcast) -- not the page: a band's scores
+    need nothing else.  Each rank accumulates the scores of its band, the
+    per-channel min/max are all-reduced (6 doubles -- the one real exchange
+    the algorithm has; a second time for the scores at the extremes once
+    they have been recomputed exactly), each rank rescales its band, and the
+    bands are all-gathered.
   * Gaussian/Sobel/Canny: pages are independent; page i goes to rank
     i mod world and nothing is exchanged.
 
@@ -69,6 +71,31 @@ class CudaAceCompute:
             float(slope), float(limit), scores.data_ptr(), minmax.data_ptr(), st))
         return True
 
+    def sample_pixels(self, page, xy):
+        """The samples' pixel values, (N, 4) uint8, where the whole page is."""
+        px = page.view(-1, 4)
+        idx = xy[1::2].long() * page.shape[1] + xy[0::2].long()
+        return px.index_select(0, idx).contiguous()
+
+    def scores_band(self, rows, height, band, xy, spx, slope, limit, minmax):
+        """rows: (b1-b0, W, 4) uint8 CUDA tensor holding only the band."""
+        b0, b1 = band
+        w = rows.shape[1]
+        out = torch.empty((3, b1 - b0, w), dtype=torch.float64, device=rows.device)
+        st = torch.cuda.current_stream().cuda_stream
+        self._capi.check(self._lib.pf_b200_dev_ace_scores_band(
+            rows.data_ptr(), w, height, b0, b1, xy.data_ptr(), spx.data_ptr(), xy.numel() // 2,
+            float(slope), float(limit), out.data_ptr(), minmax.data_ptr(), st))
+        return out
+
+    def refine_band(self, rows, height, band, xy, spx, slope, limit, scores, minmax):
+        w = rows.shape[1]
+        st = torch.cuda.current_stream().cuda_stream
+        self._capi.check(self._lib.pf_b200_dev_ace_refine_band(
+            rows.data_ptr(), w, height, band[0], band[1], xy.data_ptr(), spx.data_ptr(),
+            xy.numel() // 2, float(slope), float(limit), scores.data_ptr(), minmax.data_ptr(), st))
+        return True
+
     def scale(self, scores, minmax):
         rows, w = scores.shape[1], scores.shape[2]
         out = torch.empty((rows, w, 4), dtype=torch.uint8, device=scores.device)
@@ -79,39 +106,62 @@ class CudaAceCompute:
 
 
 def ace_sharded(page, xy, slope, limit, compute, group=None, src=0):
-    """Row-band sharded ACE.  `page` must hold the input on rank `src` and be
-    an equally shaped buffer elsewhere; every rank returns the whole result."""
+    """Row-band sharded ACE.  `page` must hold the input on rank `src`; on the
+    other ranks only its shape and device are used.  `xy` is the sample table
+    on rank `src` and a buffer of the same size elsewhere.  Every rank returns
+    the whole result."""
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     h, w = page.shape[0], page.shape[1]
-    if world > 1:
-        dist.broadcast(page, src=src, group=group)
-        dist.broadcast(xy, src=src, group=group)
-    bands = row_bands(h, world)
     minmax = compute.new_minmax(page.device, w, h)
-    scores = compute.scores(page, xy, slope, limit, bands[rank], minmax)
-    if world > 1:
-        dist.all_reduce(minmax[0:3], op=dist.ReduceOp.MIN, group=group)
-        dist.all_reduce(minmax[3:6], op=dist.ReduceOp.MAX, group=group)
-    if compute.refine(page, xy, slope, limit, bands[rank], scores, minmax) and world > 1:
+    if world == 1:
+        scores = compute.scores(page, xy, slope, limit, (0, h), minmax)
+        compute.refine(page, xy, slope, limit, (0, h), scores, minmax)
+        return compute.scale(scores, minmax)
+
+    bands = row_bands(h, world)
+    max_rows = max(b1 - b0 for b0, b1 in bands)
+    b0, b1 = bands[rank]
+    # the sample table and the samples' pixel values go to everyone; the page
+    # goes out in bands (all of one size for the scatter: short ones padded)
+    n = xy.numel() // 2
+    spx = compute.sample_pixels(page, xy) if rank == src else \
+        torch.empty((n, 4), dtype=torch.uint8, device=page.device)
+    dist.broadcast(xy, src=src, group=group)
+    dist.broadcast(spx, src=src, group=group)
+    mine = torch.empty((max_rows, w, 4), dtype=torch.uint8, device=page.device)
+    chunks = None
+    if rank == src:
+        chunks = []
+        for r0, r1 in bands:
+            if r1 - r0 == max_rows:
+                chunks.append(page[r0:r1])
+            else:
+                pad = torch.zeros((max_rows, w, 4), dtype=torch.uint8, device=page.device)
+                pad[: r1 - r0] = page[r0:r1]
+                chunks.append(pad)
+    dist.scatter(mine, scatter_list=chunks, src=src, group=group)
+    rows = mine[: b1 - b0]
+
+    scores = compute.scores_band(rows, h, (b0, b1), xy, spx, slope, limit, minmax)
+    dist.all_reduce(minmax[0:3], op=dist.ReduceOp.MIN, group=group)
+    dist.all_reduce(minmax[3:6], op=dist.ReduceOp.MAX, group=group)
+    if compute.refine_band(rows, h, (b0, b1), xy, spx, slope, limit, scores, minmax):
         dist.all_reduce(minmax[6:9], op=dist.ReduceOp.MIN, group=group)
         dist.all_reduce(minmax[9:12], op=dist.ReduceOp.MAX, group=group)
     band = compute.scale(scores, minmax)
-    if world == 1:
-        return band
     out = torch.empty((h, w, 4), dtype=torch.uint8, device=page.device)
     if h % world == 0:
         # equal bands: gather straight into the result
         dist.all_gather_into_tensor(out.view(-1), band.contiguous().view(-1), group=group)
         return out
     # all-gather needs equal shapes: pad every band to the tallest
-    max_rows = max(b1 - b0 for b0, b1 in bands)
     padded = torch.zeros((max_rows, w, 4), dtype=torch.uint8, device=page.device)
     padded[: band.shape[0]] = band
     gathered = torch.empty((world, max_rows, w, 4), dtype=torch.uint8, device=page.device)
     dist.all_gather_into_tensor(gathered.view(-1), padded.view(-1), group=group)
-    for r, (b0, b1) in enumerate(bands):
-        out[b0:b1] = gathered[r, : b1 - b0]
+    for r, (r0, r1) in enumerate(bands):
+        out[r0:r1] = gathered[r, : r1 - r0]
     return out
 
 

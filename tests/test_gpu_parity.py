@@ -322,6 +322,43 @@ def test_ace_band_split_equals_whole(gpu, oracle):
     assert torch.equal(whole, split)
 
 
+def test_ace_bands_without_the_page(gpu, oracle):
+    """pf_b200_dev_ace_scores_band / refine_band: a GPU that holds only its
+    rows of the page and the samples' pixel values (what the multi-GPU split
+    sends it) computes the same band as one that holds the page."""
+    import torch
+    from libpillowfight_b200.distributed import CudaAceCompute, row_bands, xy_tensor
+    w, h, n = 200, 151, 32
+    page = synthetic_page(w, h, 9)
+    xy = oracle.ace_draw_samples(n, w, h, 77)
+    dev = torch.device("cuda:0")
+    comp = CudaAceCompute()
+    tp, txy = torch.from_numpy(page).to(dev), xy_tensor(xy, dev)
+    mm = comp.new_minmax(dev, w, h)
+    sc = comp.scores(tp, txy, 10.0, 1000.0, (0, h), mm)
+    comp.refine(tp, txy, 10.0, 1000.0, (0, h), sc, mm)
+    whole = comp.scale(sc, mm)
+    spx = comp.sample_pixels(tp, txy)
+    assert np.array_equal(spx.cpu().numpy(), page[xy[1::2], xy[0::2]])
+    mm2 = comp.new_minmax(dev, w, h)
+    bands = row_bands(h, 3)
+    # each band in its own buffer, surrounded by garbage that must not be read
+    held = []
+    for b0, b1 in bands:
+        buf = torch.full(((b1 - b0 + 16) * w * 4,), 0xA5, dtype=torch.uint8, device=dev)
+        rows = buf[8 * w * 4: (b1 - b0 + 8) * w * 4].view(b1 - b0, w, 4)
+        rows.copy_(tp[b0:b1])
+        held.append(rows)
+    parts = [comp.scores_band(r, h, b, txy, spx, 10.0, 1000.0, mm2) for r, b in zip(held, bands)]
+    for r, b, p in zip(held, bands, parts):
+        comp.refine_band(r, h, b, txy, spx, 10.0, 1000.0, p, mm2)
+    split = torch.cat([comp.scale(p, mm2) for p in parts], dim=0)
+    torch.cuda.synchronize()
+    assert torch.equal(mm[:12], mm2[:12])
+    assert torch.equal(whole, split)
+    assert_fp_parity(split.cpu().numpy(), oracle.ace_with_samples(page, xy, 10.0, 1000.0, nb_threads=4), "bands")
+
+
 def test_empty_and_bad_arguments(gpu):
     """Zero-sized bitmaps, mismatched sizes, no samples, samples outside the
     page, tap counts out of range: an error, never a crash or a silent no-op."""

@@ -27,6 +27,23 @@ class OracleAceCompute:
     def refine(self, page, xy, slope, limit, band, scores, minmax):
         return False        # the oracle's scores are the reference's already
 
+    def sample_pixels(self, page, xy):
+        p, c = page.numpy(), xy.numpy()
+        return torch.from_numpy(np.ascontiguousarray(p[c[1::2], c[0::2]]))
+
+    def scores_band(self, rows, height, band, xy, spx, slope, limit, minmax):
+        # the oracle wants a page: one that is right in the band's rows and at
+        # the samples' coordinates, and wrong (0x77) everywhere else
+        b0, b1 = band
+        c = xy.numpy()
+        fake = np.full((height, rows.shape[1], 4), 0x77, dtype=np.uint8)
+        fake[c[1::2], c[0::2]] = spx.numpy()
+        fake[b0:b1] = rows.numpy()
+        return self.scores(torch.from_numpy(fake), xy, slope, limit, band, minmax)
+
+    def refine_band(self, rows, height, band, xy, spx, slope, limit, scores, minmax):
+        return False
+
     def scores(self, page, xy, slope, limit, band, minmax):
         b0, b1 = band
         s = self.o.ace_scores(page.numpy(), xy.numpy(), slope, limit, b0, b1)[:, b0:b1]
@@ -69,7 +86,9 @@ def _worker(rank, world, port, w, h, n_samples, result_path):
             page = torch.zeros((h, w, 4), dtype=torch.uint8)
             xy = torch.zeros(2 * n_samples, dtype=torch.int32)
         out = ace_sharded(page, xy, 10.0, 1000.0, OracleAceCompute())
-        whole = o.ace_with_samples(page.numpy(), xy.numpy(), 10.0, 1000.0)
+        # (only rank 0 ever held the page: the others were sent their band and
+        # the samples' pixel values, nothing else)
+        whole = o.ace_with_samples(synthetic_page(w, h, 5), xy.numpy(), 10.0, 1000.0)
         assert np.array_equal(out.numpy(), whole), "rank %d: sharded != whole" % rank
         if rank == 0:
             np.save(result_path, out.numpy())
