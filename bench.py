@@ -529,6 +529,37 @@ def run_b200(args):
                         "all-reduces + band all-gather inside the timed region" % world,
             "ms": float(t6.item()), "mpx_s": w6 * h6 / (float(t6.item()) * 1e-3) / 1e6,
             "scaling": "strong", "equals_single_gpu_result": same6}
+        # the same over NVLink peer memory: no scatter, no all-gather
+        if world > 1:
+            try:
+                from libpillowfight_b200.distributed import AcePeerBands
+                peer = AcePeerBands(h6, w6, dev)
+                if rank == 0:
+                    peer.page.copy_(big)
+                for _ in range(2):
+                    outp = peer.run(xy6, 10.0, 1000.0)
+                barrier()
+                torch.cuda.synchronize()
+                a.record()
+                for _ in range(n6):
+                    outp = peer.run(xy6, 10.0, 1000.0)
+                b.record()
+                torch.cuda.synchronize()
+                barrier()
+                tp6 = torch.tensor([a.elapsed_time(b) / n6], dtype=torch.float64, device=dev)
+                dist.all_reduce(tp6, op=dist.ReduceOp.MAX)
+                okp = torch.tensor([1 if torch.equal(outp, out6) else 0], device=dev)
+                dist.all_reduce(okp, op=dist.ReduceOp.MIN)
+                extras["ace_600dpi_row_bands_peer"] = {
+                    "workload": "the same page; every GPU reads its band out of rank 0's page and the "
+                                "rescale kernel writes it into every GPU's result over NVLink peer "
+                                "memory (torch symmetric memory); NCCL only for the sample values and "
+                                "the min/max exchanges",
+                    "ms": float(tp6.item()), "mpx_s": w6 * h6 / (float(tp6.item()) * 1e-3) / 1e6,
+                    "scaling": "strong", "equals_nccl_result_on_every_rank": bool(okp.item())}
+                del peer, outp
+            except Exception as exc:      # no peer access / no symmetric memory on this box
+                extras["ace_600dpi_row_bands_peer"] = {"unavailable": repr(exc)[:300]}
         del big, out6
 
         # ---- extras: page batch through the stencil chain (BASELINE.json config 5:

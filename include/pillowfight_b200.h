@@ -288,6 +288,15 @@ int pf_b200_dev_ace_refine_band(const uint32_t *d_band, int width, int height,
 		double slope, double limit,
 		double *d_scores, double *d_minmax, void *stream);
 
+/* Pass 5 with several destinations: the band's rows are stored to nb_outs
+ * images at once (d_outs: HOST array of nb_outs device pointers, 1..16, each
+ * pointing at the band's first row in that image).  The images may live on
+ * other GPUs (peer-mapped memory): in a row-band split every GPU writes its
+ * band straight into every GPU's result over NVLink and the all-gather
+ * disappears. */
+int pf_b200_dev_ace_scale_to(const double *d_scores, const double *d_minmax,
+		int width, int nb_rows, uint32_t *const *d_outs, int nb_outs, void *stream);
+
 /* The five passes above for one whole page on one GPU, with one caller-owned
  * work area of pf_b200_ace_workspace_bytes(width, height) bytes (the score
  * planes, 24 bytes per pixel, and the min/max block; 256-byte aligned).

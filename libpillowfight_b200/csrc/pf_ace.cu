@@ -693,9 +693,20 @@ __device__ __noinline__ uint32_t ace_scale_exact(double s, double mn, double spa
 // against 2^31 that also exposes 21 fraction bits; only a value within 2e-6
 // of an integer -- which includes the page minimum and maximum, and NaN --
 // goes through the exact divide.  Four pixels per thread, 16-byte stores.
+//
+// MULTI: the same rows are also stored to further images (`more`), which may
+// live on other GPUs (peer memory over NVLink): the band exchange of a
+// row-band split rides on the rescale instead of following it.
+constexpr int kMaxScaleOuts = 16;
+struct ScaleOuts {
+	uint32_t *p[kMaxScaleOuts - 1];
+	int n;
+};
+
+template <bool MULTI>
 __global__ void __launch_bounds__(256)
 ace_scale_kernel(const double *__restrict__ scores, const double *__restrict__ minmax,
-		size_t npix, size_t plane, uint32_t *__restrict__ out)
+		size_t npix, size_t plane, uint32_t *__restrict__ out, const ScaleOuts more)
 {
 	pdl_wait();
 	double mn[3], span[3], inv[3];
@@ -710,8 +721,11 @@ ace_scale_kernel(const double *__restrict__ scores, const double *__restrict__ m
 		span[c] = mx - mn[c];
 		inv[c] = 1.0 / span[c];
 	}
-	const bool vec = (npix % 4 == 0) && (plane % 2 == 0)
+	bool vec = (npix % 4 == 0) && (plane % 2 == 0)
 		&& (((uintptr_t)scores | (uintptr_t)out) % 16 == 0);
+	if (MULTI)
+		for (int d = 0; d < more.n; d++)
+			vec = vec && ((uintptr_t)more.p[d] % 16 == 0);
 	const size_t ngroups = vec ? npix / 4 : 0;
 	for (size_t gi = (size_t)blockIdx.x * blockDim.x + threadIdx.x; gi < ngroups;
 			gi += (size_t)gridDim.x * blockDim.x) {
@@ -731,7 +745,11 @@ ace_scale_kernel(const double *__restrict__ scores, const double *__restrict__ m
 				px[k] |= q << (8 * c);
 			}
 		}
-		reinterpret_cast<uint4 *>(out)[gi] = make_uint4(px[0], px[1], px[2], px[3]);
+		const uint4 v = make_uint4(px[0], px[1], px[2], px[3]);
+		reinterpret_cast<uint4 *>(out)[gi] = v;
+		if (MULTI)
+			for (int d = 0; d < more.n; d++)
+				reinterpret_cast<uint4 *>(more.p[d])[gi] = v;
 	}
 	// shapes that cannot be vectorised: the plain loop
 	for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x + 4 * ngroups; i < npix;
@@ -741,6 +759,9 @@ ace_scale_kernel(const double *__restrict__ scores, const double *__restrict__ m
 		for (int c = 0; c < 3; c++)
 			rgba |= ace_scale_exact(__ldcs(scores + c * plane + i), mn[c], span[c]) << (8 * c);
 		out[i] = rgba;
+		if (MULTI)
+			for (int d = 0; d < more.n; d++)
+				more.p[d][i] = rgba;
 	}
 }
 
@@ -891,8 +912,27 @@ int launch_ace_scale(const double *scores, const double *minmax, int w,
 	const size_t work = (npix + 3) / 4;       // 4 pixels per thread
 	const int blocks = (int)((work + 255) / 256 < (size_t)sm_count() * 8
 			? (work + 255) / 256 : (size_t)sm_count() * 8);
-	PFB_CUDA(launch_pdl(ace_scale_kernel, dim3(blocks), dim3(256), 0, st,
-			scores, minmax, npix, plane >= 0 ? (size_t)plane : npix, out));
+	ScaleOuts more = {};
+	PFB_CUDA(launch_pdl(ace_scale_kernel<false>, dim3(blocks), dim3(256), 0, st,
+			scores, minmax, npix, plane >= 0 ? (size_t)plane : npix, out, more));
+	return PF_B200_OK;
+}
+
+int launch_ace_scale_multi(const double *scores, const double *minmax, int w, int rows,
+		uint32_t *const *outs, int nb_outs, cudaStream_t st)
+{
+	if (nb_outs < 1 || nb_outs > kMaxScaleOuts)
+		return fail(PF_B200_EINVAL, "ace: %d destinations (1..%d)", nb_outs, kMaxScaleOuts);
+	ScaleOuts more = {};
+	for (int d = 1; d < nb_outs; d++)
+		more.p[d - 1] = outs[d];
+	more.n = nb_outs - 1;
+	const size_t npix = (size_t)w * rows;
+	const size_t work = (npix + 3) / 4;
+	const int blocks = (int)((work + 255) / 256 < (size_t)sm_count() * 8
+			? (work + 255) / 256 : (size_t)sm_count() * 8);
+	PFB_CUDA(launch_pdl(ace_scale_kernel<true>, dim3(blocks), dim3(256), 0, st,
+			scores, minmax, npix, npix, outs[0], more));
 	return PF_B200_OK;
 }
 

@@ -948,6 +948,21 @@ int pf_b200_dev_ace_scale(const double *d_scores, const double *d_minmax,
 			static_cast<cudaStream_t>(stream));
 }
 
+int pf_b200_dev_ace_scale_to(const double *d_scores, const double *d_minmax,
+		int width, int nb_rows, uint32_t *const *d_outs, int nb_outs, void *stream)
+{
+	clear_error();
+	if (!d_scores || !d_minmax || !d_outs)
+		return fail(PF_B200_EINVAL, "NULL pointer");
+	if (width <= 0 || nb_rows <= 0)
+		return fail(PF_B200_EINVAL, "size %d x %d", width, nb_rows);
+	for (int i = 0; i < nb_outs && i < 16; i++)
+		if (!d_outs[i])
+			return fail(PF_B200_EINVAL, "NULL destination %d", i);
+	return launch_ace_scale_multi(d_scores, d_minmax, width, nb_rows, d_outs, nb_outs,
+			static_cast<cudaStream_t>(stream));
+}
+
 static int ace_band_call(bool refine, const uint32_t *d_band, int width, int height,
 		int row_begin, int row_end, const int *d_samples, const uint32_t *d_sample_px,
 		int nb_samples, double slope, double limit, double *d_scores, double *d_minmax,

@@ -165,6 +165,62 @@ def ace_sharded(page, xy, slope, limit, compute, group=None, src=0):
     return out
 
 
+class AcePeerBands:
+    """Row-band ACE with the page and the result in NVLink peer memory (torch
+    symmetric memory): no scatter and no all-gather.  Every GPU reads its band
+    of rows straight out of the page on the GPU that holds it (the
+    accumulation kernel loads each pixel once), and the rescale kernel stores
+    its band into every GPU's result (pf_b200_dev_ace_scale_to).  What is left
+    for NCCL is the sample table, the samples' pixel values and the two
+    6-double min/max exchanges.
+
+    One object per page size; `page` (on rank `src`) is where the caller puts
+    the input, `out` holds the whole result on every rank after run()."""
+
+    def __init__(self, height, width, device, group=None):
+        import torch.distributed._symmetric_memory as symm
+        from . import _capi
+        self._capi, self._lib = _capi, _capi.lib
+        self.h, self.w = height, width
+        self.group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        self.page = symm.empty((height, width, 4), dtype=torch.uint8, device=device)
+        self.out = symm.empty((height, width, 4), dtype=torch.uint8, device=device)
+        self._hp = symm.rendezvous(self.page, self.group)
+        self._ho = symm.rendezvous(self.out, self.group)
+        self.compute = CudaAceCompute()
+
+    def run(self, xy, slope, limit, src=0):
+        import ctypes
+        h, w, comp = self.h, self.w, self.compute
+        b0, b1 = row_bands(h, self.world)[self.rank]
+        n = xy.numel() // 2
+        dev = self.page.device
+        spx = comp.sample_pixels(self.page, xy) if self.rank == src else \
+            torch.empty((n, 4), dtype=torch.uint8, device=dev)
+        # these two also order every rank's reads of the page after the copy
+        # that put it there (same stream on `src`)
+        dist.broadcast(xy, src=src, group=self.group)
+        dist.broadcast(spx, src=src, group=self.group)
+        rows = self._hp.get_buffer(src, (h, w, 4), torch.uint8)[b0:b1]       # peer memory
+        minmax = comp.new_minmax(dev, w, h)
+        scores = comp.scores_band(rows, h, (b0, b1), xy, spx, slope, limit, minmax)
+        dist.all_reduce(minmax[0:3], op=dist.ReduceOp.MIN, group=self.group)
+        dist.all_reduce(minmax[3:6], op=dist.ReduceOp.MAX, group=self.group)
+        comp.refine_band(rows, h, (b0, b1), xy, spx, slope, limit, scores, minmax)
+        dist.all_reduce(minmax[6:9], op=dist.ReduceOp.MIN, group=self.group)
+        dist.all_reduce(minmax[9:12], op=dist.ReduceOp.MAX, group=self.group)
+        # own image first, then the peers'
+        order = [self.rank] + [r for r in range(self.world) if r != self.rank]
+        dests = [self._ho.get_buffer(r, (h, w, 4), torch.uint8)[b0:b1] for r in order]
+        ptrs = (ctypes.c_void_p * len(dests))(*[d.data_ptr() for d in dests])
+        st = torch.cuda.current_stream().cuda_stream
+        self._capi.check(self._lib.pf_b200_dev_ace_scale_to(
+            scores.data_ptr(), minmax.data_ptr(), w, b1 - b0, ptrs, len(dests), st))
+        self._ho.barrier()          # every band has landed everywhere
+        return self.out
+
+
 class CudaChain:
     """Gaussian -> Sobel -> Canny on batches of same-size pages resident in
     HBM, through the C-ABI device entry points."""

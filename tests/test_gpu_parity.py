@@ -357,6 +357,19 @@ def test_ace_bands_without_the_page(gpu, oracle):
     assert torch.equal(mm[:12], mm2[:12])
     assert torch.equal(whole, split)
     assert_fp_parity(split.cpu().numpy(), oracle.ace_with_samples(page, xy, 10.0, 1000.0, nb_threads=4), "bands")
+    # pf_b200_dev_ace_scale_to: every band stored into three whole-page images
+    # at once (across GPUs these are peer buffers; here all on one device)
+    from libpillowfight_b200 import _capi
+    images = [torch.full((h, w, 4), 0x11, dtype=torch.uint8, device=dev) for _ in range(3)]
+    st = torch.cuda.current_stream().cuda_stream
+    for (b0, b1), p in zip(bands, parts):
+        ptrs = (ctypes.c_void_p * 3)(*[im[b0:b1].data_ptr() for im in images])
+        _capi.check(_capi.lib.pf_b200_dev_ace_scale_to(p.data_ptr(), mm2.data_ptr(), w, b1 - b0, ptrs, 3, st))
+    torch.cuda.synchronize()
+    for im in images:
+        assert torch.equal(im, whole)
+    assert _capi.lib.pf_b200_dev_ace_scale_to(parts[0].data_ptr(), mm2.data_ptr(), w, 4, ptrs, 17, st) \
+        == _capi.PF_B200_EINVAL
 
 
 def test_empty_and_bad_arguments(gpu):
