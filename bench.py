@@ -556,7 +556,27 @@ def run_b200(args):
                                 "memory (torch symmetric memory); NCCL only for the sample values and "
                                 "the min/max exchanges",
                     "ms": float(tp6.item()), "mpx_s": w6 * h6 / (float(tp6.item()) * 1e-3) / 1e6,
-                    "scaling": "strong", "equals_nccl_result_on_every_rank": bool(okp.item())}
+                    "scaling": "strong", "equals_nccl_result_on_every_rank": bool(okp.item()),
+                    "result_stores": "multimem.st to an NVLS multicast address" if peer.use_multicast
+                                     else "one st.global per peer"}
+                if peer.use_multicast:      # and with plain peer stores, for comparison
+                    peer.use_multicast = False
+                    for _ in range(2):
+                        outp = peer.run(xy6, 10.0, 1000.0)
+                    barrier()
+                    torch.cuda.synchronize()
+                    a.record()
+                    for _ in range(n6):
+                        outp = peer.run(xy6, 10.0, 1000.0)
+                    b.record()
+                    torch.cuda.synchronize()
+                    barrier()
+                    tq6 = torch.tensor([a.elapsed_time(b) / n6], dtype=torch.float64, device=dev)
+                    dist.all_reduce(tq6, op=dist.ReduceOp.MAX)
+                    okq = torch.tensor([1 if torch.equal(outp, out6) else 0], device=dev)
+                    dist.all_reduce(okq, op=dist.ReduceOp.MIN)
+                    extras["ace_600dpi_row_bands_peer"]["ms_with_per_peer_stores"] = float(tq6.item())
+                    extras["ace_600dpi_row_bands_peer"]["per_peer_stores_equal"] = bool(okq.item())
                 del peer, outp
             except Exception as exc:      # no peer access / no symmetric memory on this box
                 extras["ace_600dpi_row_bands_peer"] = {"unavailable": repr(exc)[:300]}

@@ -296,6 +296,12 @@ int pf_b200_dev_ace_refine_band(const uint32_t *d_band, int width, int height,
  * disappears. */
 int pf_b200_dev_ace_scale_to(const double *d_scores, const double *d_minmax,
 		int width, int nb_rows, uint32_t *const *d_outs, int nb_outs, void *stream);
+/* The same with ONE destination that is an NVLS multicast address (a
+ * multicast object bound to the result image of every GPU): the rows are
+ * stored with multimem.st and the NVSwitch delivers them to all GPUs,
+ * the caller's included. */
+int pf_b200_dev_ace_scale_multicast(const double *d_scores, const double *d_minmax,
+		int width, int nb_rows, uint32_t *d_multicast_band, void *stream);
 
 /* The five passes above for one whole page on one GPU, with one caller-owned
  * work area of pf_b200_ace_workspace_bytes(width, height) bytes (the score

@@ -110,6 +110,7 @@ SIGNATURES = {
                                                    ctypes.c_double, _vp, _vp, _vp]),
     "pf_b200_dev_ace_scale_to": (ctypes.c_int, [_vp, _vp, ctypes.c_int, ctypes.c_int,
                                                 ctypes.POINTER(ctypes.c_void_p), ctypes.c_int, _vp]),
+    "pf_b200_dev_ace_scale_multicast": (ctypes.c_int, [_vp, _vp, ctypes.c_int, ctypes.c_int, _vp, _vp]),
     "pf_b200_ace_workspace_bytes": (ctypes.c_size_t, [ctypes.c_int, ctypes.c_int]),
     "pf_b200_dev_ace": (ctypes.c_int, [_u32p, _u32p, ctypes.c_int, ctypes.c_int, _vp, ctypes.c_int,
                                        ctypes.c_double, ctypes.c_double, _vp, ctypes.c_size_t, _vp]),

@@ -701,7 +701,23 @@ constexpr int kMaxScaleOuts = 16;
 struct ScaleOuts {
 	uint32_t *p[kMaxScaleOuts - 1];
 	int n;
+	int multicast;      // `out` is an NVLS multicast address: one store, the switch delivers it to every GPU
 };
+
+// 16 bytes to a multicast address (multimem.st: the NVSwitch replicates the
+// store into the buffer of every GPU bound to the multicast object)
+__device__ __forceinline__ void multimem_store16(void *addr, uint4 v)
+{
+	asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+			:: "l"(addr), "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)),
+			   "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w)) : "memory");
+}
+
+__device__ __forceinline__ void multimem_store4(void *addr, uint32_t v)
+{
+	asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;"
+			:: "l"(addr), "f"(__uint_as_float(v)) : "memory");
+}
 
 template <bool MULTI>
 __global__ void __launch_bounds__(256)
@@ -746,7 +762,10 @@ ace_scale_kernel(const double *__restrict__ scores, const double *__restrict__ m
 			}
 		}
 		const uint4 v = make_uint4(px[0], px[1], px[2], px[3]);
-		reinterpret_cast<uint4 *>(out)[gi] = v;
+		if (MULTI && more.multicast)
+			multimem_store16(reinterpret_cast<uint4 *>(out) + gi, v);
+		else
+			reinterpret_cast<uint4 *>(out)[gi] = v;
 		if (MULTI)
 			for (int d = 0; d < more.n; d++)
 				reinterpret_cast<uint4 *>(more.p[d])[gi] = v;
@@ -758,7 +777,10 @@ ace_scale_kernel(const double *__restrict__ scores, const double *__restrict__ m
 #pragma unroll
 		for (int c = 0; c < 3; c++)
 			rgba |= ace_scale_exact(__ldcs(scores + c * plane + i), mn[c], span[c]) << (8 * c);
-		out[i] = rgba;
+		if (MULTI && more.multicast)
+			multimem_store4(out + i, rgba);
+		else
+			out[i] = rgba;
 		if (MULTI)
 			for (int d = 0; d < more.n; d++)
 				more.p[d][i] = rgba;
@@ -919,7 +941,7 @@ int launch_ace_scale(const double *scores, const double *minmax, int w,
 }
 
 int launch_ace_scale_multi(const double *scores, const double *minmax, int w, int rows,
-		uint32_t *const *outs, int nb_outs, cudaStream_t st)
+		uint32_t *const *outs, int nb_outs, cudaStream_t st, bool multicast)
 {
 	if (nb_outs < 1 || nb_outs > kMaxScaleOuts)
 		return fail(PF_B200_EINVAL, "ace: %d destinations (1..%d)", nb_outs, kMaxScaleOuts);
@@ -927,6 +949,7 @@ int launch_ace_scale_multi(const double *scores, const double *minmax, int w, in
 	for (int d = 1; d < nb_outs; d++)
 		more.p[d - 1] = outs[d];
 	more.n = nb_outs - 1;
+	more.multicast = multicast ? 1 : 0;
 	const size_t npix = (size_t)w * rows;
 	const size_t work = (npix + 3) / 4;
 	const int blocks = (int)((work + 255) / 256 < (size_t)sm_count() * 8

@@ -963,6 +963,19 @@ int pf_b200_dev_ace_scale_to(const double *d_scores, const double *d_minmax,
 			static_cast<cudaStream_t>(stream));
 }
 
+int pf_b200_dev_ace_scale_multicast(const double *d_scores, const double *d_minmax,
+		int width, int nb_rows, uint32_t *d_multicast_band, void *stream)
+{
+	clear_error();
+	if (!d_scores || !d_minmax || !d_multicast_band)
+		return fail(PF_B200_EINVAL, "NULL pointer");
+	if (width <= 0 || nb_rows <= 0)
+		return fail(PF_B200_EINVAL, "size %d x %d", width, nb_rows);
+	uint32_t *outs[1] = { d_multicast_band };
+	return launch_ace_scale_multi(d_scores, d_minmax, width, nb_rows, outs, 1,
+			static_cast<cudaStream_t>(stream), true);
+}
+
 static int ace_band_call(bool refine, const uint32_t *d_band, int width, int height,
 		int row_begin, int row_end, const int *d_samples, const uint32_t *d_sample_px,
 		int nb_samples, double slope, double limit, double *d_scores, double *d_minmax,

@@ -135,7 +135,7 @@ int launch_ace_scale(const double *scores, const double *minmax, int w,
 		int rows, uint32_t *out, cudaStream_t st, long plane = -1);
 // the same rows to nb_outs images at once (band-local score planes)
 int launch_ace_scale_multi(const double *scores, const double *minmax, int w, int rows,
-		uint32_t *const *outs, int nb_outs, cudaStream_t st);
+		uint32_t *const *outs, int nb_outs, cudaStream_t st, bool multicast = false);
 double measure_fp64_peak_tflops();
 
 }  // namespace pfb

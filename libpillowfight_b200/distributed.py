@@ -177,7 +177,7 @@ class AcePeerBands:
     One object per page size; `page` (on rank `src`) is where the caller puts
     the input, `out` holds the whole result on every rank after run()."""
 
-    def __init__(self, height, width, device, group=None):
+    def __init__(self, height, width, device, group=None, use_multicast=True):
         import torch.distributed._symmetric_memory as symm
         from . import _capi
         self._capi, self._lib = _capi, _capi.lib
@@ -189,6 +189,8 @@ class AcePeerBands:
         self._hp = symm.rendezvous(self.page, self.group)
         self._ho = symm.rendezvous(self.out, self.group)
         self.compute = CudaAceCompute()
+        # NVLS multicast for the result stores when the fabric offers it
+        self.use_multicast = bool(use_multicast and getattr(self._ho, "multicast_ptr", 0))
 
     def run(self, xy, slope, limit, src=0):
         import ctypes
@@ -210,13 +212,19 @@ class AcePeerBands:
         comp.refine_band(rows, h, (b0, b1), xy, spx, slope, limit, scores, minmax)
         dist.all_reduce(minmax[6:9], op=dist.ReduceOp.MIN, group=self.group)
         dist.all_reduce(minmax[9:12], op=dist.ReduceOp.MAX, group=self.group)
-        # own image first, then the peers'
-        order = [self.rank] + [r for r in range(self.world) if r != self.rank]
-        dests = [self._ho.get_buffer(r, (h, w, 4), torch.uint8)[b0:b1] for r in order]
-        ptrs = (ctypes.c_void_p * len(dests))(*[d.data_ptr() for d in dests])
         st = torch.cuda.current_stream().cuda_stream
-        self._capi.check(self._lib.pf_b200_dev_ace_scale_to(
-            scores.data_ptr(), minmax.data_ptr(), w, b1 - b0, ptrs, len(dests), st))
+        mc = self._ho.multicast_ptr if self.use_multicast else 0
+        if mc:
+            # one multimem.st per 16 bytes: the NVSwitch delivers the band to all GPUs
+            self._capi.check(self._lib.pf_b200_dev_ace_scale_multicast(
+                scores.data_ptr(), minmax.data_ptr(), w, b1 - b0, mc + b0 * w * 4, st))
+        else:
+            # own image first, then the peers'
+            order = [self.rank] + [r for r in range(self.world) if r != self.rank]
+            dests = [self._ho.get_buffer(r, (h, w, 4), torch.uint8)[b0:b1] for r in order]
+            ptrs = (ctypes.c_void_p * len(dests))(*[d.data_ptr() for d in dests])
+            self._capi.check(self._lib.pf_b200_dev_ace_scale_to(
+                scores.data_ptr(), minmax.data_ptr(), w, b1 - b0, ptrs, len(dests), st))
         self._ho.barrier()          # every band has landed everywhere
         return self.out
 
