@@ -191,27 +191,41 @@ class AcePeerBands:
         self.compute = CudaAceCompute()
         # NVLS multicast for the result stores when the fabric offers it
         self.use_multicast = bool(use_multicast and getattr(self._ho, "multicast_ptr", 0))
+        self._rows = self._dests = self._tmp = None
+
+    def _exchange(self, minmax, lo):
+        """min over minmax[lo:lo+3], max over minmax[lo+3:lo+6], in ONE
+        all-reduce: -min is a max, and negation is exact."""
+        t = self._tmp
+        torch.neg(minmax[lo:lo + 3], out=t[0:3])
+        t[3:6].copy_(minmax[lo + 3:lo + 6])
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        torch.neg(t[0:3], out=minmax[lo:lo + 3])
+        minmax[lo + 3:lo + 6].copy_(t[3:6])
 
     def run(self, xy, slope, limit, src=0):
-        import ctypes
         h, w, comp = self.h, self.w, self.compute
         b0, b1 = row_bands(h, self.world)[self.rank]
         n = xy.numel() // 2
         dev = self.page.device
-        spx = comp.sample_pixels(self.page, xy) if self.rank == src else \
-            torch.empty((n, 4), dtype=torch.uint8, device=dev)
-        # these two also order every rank's reads of the page after the copy
-        # that put it there (same stream on `src`)
-        dist.broadcast(xy, src=src, group=self.group)
-        dist.broadcast(spx, src=src, group=self.group)
-        rows = self._hp.get_buffer(src, (h, w, 4), torch.uint8)[b0:b1]       # peer memory
+        # sample table and sample values in one message; it also orders every
+        # rank's reads of the page after the copy that put it there (same
+        # stream on `src`)
+        msg = torch.empty(3 * n, dtype=torch.int32, device=dev)
+        if self.rank == src:
+            msg[: 2 * n].copy_(xy)
+            msg[2 * n:].copy_(comp.sample_pixels(self.page, xy).view(torch.int32).view(-1))
+        dist.broadcast(msg, src=src, group=self.group)
+        xy, spx = msg[: 2 * n], msg[2 * n:]
+        if self._rows is None:
+            self._rows = self._hp.get_buffer(src, (h, w, 4), torch.uint8)[b0:b1]       # peer memory
+            self._tmp = torch.empty(6, dtype=torch.float64, device=dev)
+        rows = self._rows
         minmax = comp.new_minmax(dev, w, h)
         scores = comp.scores_band(rows, h, (b0, b1), xy, spx, slope, limit, minmax)
-        dist.all_reduce(minmax[0:3], op=dist.ReduceOp.MIN, group=self.group)
-        dist.all_reduce(minmax[3:6], op=dist.ReduceOp.MAX, group=self.group)
+        self._exchange(minmax, 0)
         comp.refine_band(rows, h, (b0, b1), xy, spx, slope, limit, scores, minmax)
-        dist.all_reduce(minmax[6:9], op=dist.ReduceOp.MIN, group=self.group)
-        dist.all_reduce(minmax[9:12], op=dist.ReduceOp.MAX, group=self.group)
+        self._exchange(minmax, 6)
         st = torch.cuda.current_stream().cuda_stream
         mc = self._ho.multicast_ptr if self.use_multicast else 0
         if mc:
@@ -219,12 +233,13 @@ class AcePeerBands:
             self._capi.check(self._lib.pf_b200_dev_ace_scale_multicast(
                 scores.data_ptr(), minmax.data_ptr(), w, b1 - b0, mc + b0 * w * 4, st))
         else:
-            # own image first, then the peers'
-            order = [self.rank] + [r for r in range(self.world) if r != self.rank]
-            dests = [self._ho.get_buffer(r, (h, w, 4), torch.uint8)[b0:b1] for r in order]
-            ptrs = (ctypes.c_void_p * len(dests))(*[d.data_ptr() for d in dests])
+            import ctypes
+            if self._dests is None:          # own image first, then the peers'
+                order = [self.rank] + [r for r in range(self.world) if r != self.rank]
+                self._dests = [self._ho.get_buffer(r, (h, w, 4), torch.uint8)[b0:b1] for r in order]
+            ptrs = (ctypes.c_void_p * len(self._dests))(*[d.data_ptr() for d in self._dests])
             self._capi.check(self._lib.pf_b200_dev_ace_scale_to(
-                scores.data_ptr(), minmax.data_ptr(), w, b1 - b0, ptrs, len(dests), st))
+                scores.data_ptr(), minmax.data_ptr(), w, b1 - b0, ptrs, len(self._dests), st))
         self._ho.barrier()          # every band has landed everywhere
         return self.out
 
