@@ -195,6 +195,38 @@ GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "oracle_small.npz")
 
 
 @pytest.mark.skipif(not os.path.exists(GOLDEN), reason="golden fixture not generated")
+def test_ace_exact_ties_and_flat_pages(oracle):
+    """What the CUDA kernels have to reproduce bit for bit: a
+    pixel whose difference to EVERY sample is zero, saturates high or saturates
+    low scores exactly 0, 1, -1 (numerator and denominator are the same sums);
+    a flat channel is 0/0 and comes out 0; the pixels tied AT the maximum all
+    become the same value."""
+    w, h, n = 90, 60, 12
+    xy = oracle.ace_draw_samples(n, w, h, 8)
+    free = next((x, y) for y in range(20, 40) for x in range(20, 70)
+                if all(abs(x - sx) > 4 or abs(y - sy) > 4 for sx, sy in zip(xy[0::2], xy[1::2])))
+    page = np.full((h, w, 4), 255, dtype=np.uint8)
+    page[..., :3] = (100, 100, 40)
+    page[free[1] - 2:free[1] + 2, free[0] - 2:free[0] + 2, :3] = (230, 60, 40)    # no sample on it
+    s = oracle.ace_scores(page, xy, 10.0, 1000.0)
+    mark = (slice(free[1] - 2, free[1] + 2), slice(free[0] - 2, free[0] + 2))
+    background = np.ones((h, w), dtype=bool)
+    background[mark] = False
+    assert (s[0][background] == 0.0).all() and (s[1][background] == 0.0).all()
+    assert (s[0][mark] == 1.0).all()          # 230 - 100 = 130 > limit / slope = 100: saturated high
+    assert (s[1][mark] == -0.4).any() or np.allclose(s[1][mark], -0.4, atol=1e-12)   # 60 - 100 = -40
+    assert (s[2] == 0.0).all()                # flat channel
+    out = oracle.ace_with_samples(page, xy, 10.0, 1000.0)
+    assert (out[..., 2] == 0).all()           # 0/0 -> 0
+    assert (out[..., 0][mark] == 255).all() and (out[..., 0][background] == 0).all()
+    assert (out[..., 1][background] == out[0, 0, 1]).all() and out[0, 0, 1] >= 254
+    # saturated low everywhere: exactly -1
+    dark = page.copy()
+    dark[mark[0], mark[1], :3] = (0, 0, 40)
+    s2 = oracle.ace_scores(dark, xy, 10.0, 1000.0)
+    assert (s2[0][mark] == -1.0).all() and (s2[1][mark] == -1.0).all()
+
+
 def test_oracle_matches_committed_fixtures(oracle):
     """Regression fixtures made by tests/golden/make_golden.py from this same
     oracle (not upstream goldens -- none exist in the mount)."""
