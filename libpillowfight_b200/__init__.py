@@ -52,21 +52,37 @@ def _pil_pixels(img):
         return arr
     rawmode = "RGBA" if img.mode == "RGBA" else "RGBX"
     flat = arr.reshape(-1)
-    rows = max(1, (4 << 20) // (4 * w))
-    for y0 in range(0, h, rows):
-        y1 = min(h, y0 + rows)
-        enc = Image._getencoder(img.mode, "raw", rawmode)
-        enc.setimage(img.im, (0, y0, w, y1))
-        off, end = 4 * w * y0, 4 * w * y1
-        while True:
-            _, err, data = enc.encode(end - off + 64)
-            flat[off:off + len(data)] = np.frombuffer(data, dtype=np.uint8)
-            off += len(data)
-            if err:
-                break
-        if err < 0 or off != end:
-            raise RuntimeError("Pillow's raw encoder failed (%d)" % err)
+
+    def pack(y_begin, y_end):
+        rows = max(1, (4 << 20) // (4 * w))
+        for y0 in range(y_begin, y_end, rows):
+            y1 = min(y_end, y0 + rows)
+            enc = Image._getencoder(img.mode, "raw", rawmode)
+            enc.setimage(img.im, (0, y0, w, y1))
+            off, end = 4 * w * y0, 4 * w * y1
+            while True:
+                _, err, data = enc.encode(end - off + 64)
+                flat[off:off + len(data)] = np.frombuffer(data, dtype=np.uint8)
+                off += len(data)
+                if err:
+                    break
+            if err < 0 or off != end:
+                raise RuntimeError("Pillow's raw encoder failed (%d)" % err)
+
+    if arr.nbytes < (8 << 20):
+        pack(0, h)
+    else:
+        # the copies run without the GIL: four threads roughly halve the time
+        global _pack_pool
+        if _pack_pool is None:
+            from concurrent.futures import ThreadPoolExecutor
+            _pack_pool = ThreadPoolExecutor(4, thread_name_prefix="pf_b200_pack")
+        bands = [(h * i // 4, h * (i + 1) // 4) for i in range(4)]
+        list(_pack_pool.map(lambda b: pack(*b), bands))
     return arr
+
+
+_pack_pool = None
 
 
 def _to_array(img_in):
