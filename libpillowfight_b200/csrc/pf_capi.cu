@@ -10,7 +10,12 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <thread>
+#include <vector>
 #if defined(__x86_64__)
 #include <immintrin.h>
 #endif
@@ -74,8 +79,79 @@ struct Buffer {
 
 constexpr int kMaxBands = 16;      // row bands a streamed call is cut into, at most
 
+// A few host threads that live as long as the calling thread's context: the
+// staging copies of pageable pages run on them (starting eight threads per
+// call costs more than some of the copies take, and makes the call's duration
+// erratic).  start(f) hands f(worker index) to every worker; wait() returns
+// when all have finished it.
+class CopyPool {
+public:
+	~CopyPool()
+	{
+		{
+			std::lock_guard<std::mutex> lk(m_);
+			stop_ = true;
+		}
+		cv_job_.notify_all();
+		for (std::thread &t : threads_)
+			t.join();
+	}
+	int size() const { return (int)threads_.size(); }
+	void ensure(int n)
+	{
+		while ((int)threads_.size() < n) {
+			const int idx = (int)threads_.size();
+			threads_.emplace_back([this, idx] { loop(idx); });
+		}
+	}
+	void start(std::function<void(int)> f)
+	{
+		std::lock_guard<std::mutex> lk(m_);
+		job_ = std::move(f);
+		pending_ = (int)threads_.size();
+		generation_++;
+		cv_job_.notify_all();
+	}
+	void wait()
+	{
+		std::unique_lock<std::mutex> lk(m_);
+		cv_done_.wait(lk, [this] { return pending_ == 0; });
+	}
+
+private:
+	void loop(int idx)
+	{
+		unsigned long seen = 0;
+		for (;;) {
+			std::function<void(int)> f;
+			{
+				std::unique_lock<std::mutex> lk(m_);
+				cv_job_.wait(lk, [&] { return stop_ || generation_ != seen; });
+				if (stop_)
+					return;
+				seen = generation_;
+				f = job_;
+			}
+			f(idx);
+			{
+				std::lock_guard<std::mutex> lk(m_);
+				if (--pending_ == 0)
+					cv_done_.notify_all();
+			}
+		}
+	}
+	std::vector<std::thread> threads_;
+	std::mutex m_;
+	std::condition_variable cv_job_, cv_done_;
+	std::function<void(int)> job_;
+	unsigned long generation_ = 0;
+	int pending_ = 0;
+	bool stop_ = false;
+};
+
 struct Context {
 	int dev = -1;
+	CopyPool pool;
 	cudaStream_t st = nullptr;           // kernels
 	cudaStream_t st_up = nullptr;        // host -> device copies of a streamed call
 	cudaStream_t st_down = nullptr;      // device -> host copies of a streamed call
@@ -258,12 +334,14 @@ static int upload_threads(Context &c, void *dst, const void *src, size_t bytes)
 		errs[i] = cudaMemcpyAsync(static_cast<char *>(dst) + off, stage, n,
 				cudaMemcpyHostToDevice, c.st);
 	};
-	std::thread th[kCopyThreadsMax - 1];
-	for (int i = 1; i < kCopyThreads; i++)
-		th[i - 1] = std::thread(work, i);
+	// slice 0 on the calling thread, the others on the pool
+	c.pool.ensure(kCopyThreads - 1);
+	c.pool.start([&](int i) {
+		if (i + 1 < kCopyThreads)
+			work(i + 1);
+	});
 	work(0);
-	for (int i = 1; i < kCopyThreads; i++)
-		th[i - 1].join();
+	c.pool.wait();
 	for (cudaError_t e : errs)
 		if (e != cudaSuccess)
 			return fail(PF_B200_ECUDA, "upload: %s", cudaGetErrorString(e));
@@ -296,12 +374,14 @@ static int download_threads(Context &c, void *dst, const void *src, size_t bytes
 		errs[i] = cudaEventSynchronize(c.ev_done[i]);
 		copy_slice(static_cast<char *>(dst) + off, static_cast<char *>(c.h_stage.p) + off, n);
 	};
-	std::thread th[kCopyThreadsMax - 1];
-	for (int i = 1; i < kCopyThreads; i++)
-		th[i - 1] = std::thread(work, i);
+	// slice 0 on the calling thread, the others on the pool
+	c.pool.ensure(kCopyThreads - 1);
+	c.pool.start([&](int i) {
+		if (i + 1 < kCopyThreads)
+			work(i + 1);
+	});
 	work(0);
-	for (int i = 1; i < kCopyThreads; i++)
-		th[i - 1].join();
+	c.pool.wait();
 	for (cudaError_t e : errs)
 		if (e != cudaSuccess)
 			return fail(PF_B200_ECUDA, "download: %s", cudaGetErrorString(e));
@@ -567,6 +647,115 @@ static int run_canny_streamed(Context &c, const struct pf_bitmap *in, struct pf_
 	return PF_B200_OK;
 }
 
+// Gaussian / Sobel on ordinary (pageable) caller memory, both sides -- what a
+// C program that mallocs its bitmaps gets.  The same band pipeline as on
+// pinned pages, fed and drained through two page-sized pinned staging areas:
+// host threads copy the input bands in (streaming stores), the calling thread
+// queues each band's DMA as soon as it is staged and each band's kernel as
+// soon as the band below it is on the device, the kernels write their rows
+// straight into the second staging area, and the host threads copy every band
+// out to the caller as soon as its kernel has finished.  Host copies, PCIe in
+// both directions and the kernels overlap.
+static int run_stencil_pageable(Context &c, Op op, const struct pf_bitmap *in,
+		struct pf_bitmap *out, const Taps &taps)
+{
+	const int w = in->size.x, h = in->size.y;
+	const size_t bytes = (size_t)w * h * sizeof(uint32_t);
+	int rows = (h + kMaxBands - 1) / kMaxBands;
+	if (rows < 128)
+		rows = 128;
+	const int nb = (h + rows - 1) / rows;
+	int rc = grow(c.h_stage, 2 * bytes + 256, true);
+	if (rc)
+		return rc;
+	char *stage_in = static_cast<char *>(c.h_stage.p);
+	char *stage_out = stage_in + ((bytes + 255) & ~(size_t)255);
+	uint32_t *direct = static_cast<uint32_t *>(device_alias(stage_out));
+	if (!direct)
+		return fail(PF_B200_ECUDA, "the pinned staging area is not mapped for the device");
+	const char *src = reinterpret_cast<const char *>(in->pixels);
+	char *dst = reinterpret_cast<char *>(out->pixels);
+	const uint32_t *din = static_cast<const uint32_t *>(c.d_in.p);
+
+	std::atomic<int> in_ready[kMaxBands], out_ready[kMaxBands];
+	for (int b = 0; b < nb; b++) {
+		in_ready[b].store(0);
+		out_ready[b].store(0);
+	}
+	std::atomic<bool> failed(false);
+	cudaError_t sync_err[kMaxBands] = {};
+	auto band_off = [&](int b) { return (size_t)b * rows * w * sizeof(uint32_t); };
+	auto band_len = [&](int b) {
+		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
+		return (size_t)(y1 - y0) * w * sizeof(uint32_t);
+	};
+	const int nthreads = copy_threads();
+	auto work = [&](int t) {
+		cudaSetDevice(c.dev);
+		for (int b = t; b < nb; b += nthreads) {
+			copy_slice(stage_in + band_off(b), src + band_off(b), band_len(b));
+			in_ready[b].store(1, std::memory_order_release);
+		}
+		for (int b = t; b < nb; b += nthreads) {
+			while (!out_ready[b].load(std::memory_order_acquire)) {
+				if (failed.load())
+					return;
+				std::this_thread::yield();
+			}
+			sync_err[b] = cudaEventSynchronize(c.ev_done[b]);
+			if (sync_err[b] == cudaSuccess)
+				copy_slice(dst + band_off(b), stage_out + band_off(b), band_len(b));
+		}
+	};
+	c.pool.ensure(nthreads);
+	c.pool.start([&](int t) {
+		if (t < nthreads)
+			work(t);
+	});
+
+	// the calling thread drives the device
+	auto launch_band = [&](int b) -> int {
+		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
+		cudaError_t e = cudaStreamWaitEvent(c.st, c.ev_up[b + 1 < nb ? b + 1 : b], 0);
+		if (e != cudaSuccess)
+			return fail(PF_B200_ECUDA, "%s", cudaGetErrorString(e));
+		int r = (op == OP_GAUSSIAN) ? launch_gaussian(din, direct, w, h, 1, taps, c.st, y0, y1)
+		                            : launch_sobel(din, direct, w, h, 1, c.st, y0, y1);
+		if (r)
+			return r;
+		e = cudaEventRecord(c.ev_done[b], c.st);
+		if (e != cudaSuccess)
+			return fail(PF_B200_ECUDA, "%s", cudaGetErrorString(e));
+		out_ready[b].store(1, std::memory_order_release);
+		return PF_B200_OK;
+	};
+	for (int b = 0; b < nb && !rc; b++) {
+		while (!in_ready[b].load(std::memory_order_acquire))
+			std::this_thread::yield();
+		cudaError_t e = cudaMemcpyAsync(const_cast<uint32_t *>(din) + band_off(b) / sizeof(uint32_t),
+				stage_in + band_off(b), band_len(b), cudaMemcpyHostToDevice, c.st_up);
+		if (e == cudaSuccess)
+			e = cudaEventRecord(c.ev_up[b], c.st_up);
+		if (e != cudaSuccess)
+			rc = fail(PF_B200_ECUDA, "upload: %s", cudaGetErrorString(e));
+		if (!rc && b >= 1)
+			rc = launch_band(b - 1);
+	}
+	if (!rc)
+		rc = launch_band(nb - 1);
+	if (rc)
+		failed.store(true);
+	c.pool.wait();
+	if (!rc)
+		for (int b = 0; b < nb; b++)
+			if (sync_err[b] != cudaSuccess)
+				rc = fail(PF_B200_ECUDA, "download: %s", cudaGetErrorString(sync_err[b]));
+	// nothing of this call may still be running when the staging areas are reused
+	cudaStreamSynchronize(c.st);
+	cudaStreamSynchronize(c.st_up);
+	return rc;
+}
+
 static int run_stencil(Op op, const struct pf_bitmap *in, struct pf_bitmap *out,
 		double sigma, int nb_stddev)
 {
@@ -592,6 +781,10 @@ static int run_stencil(Op op, const struct pf_bitmap *in, struct pf_bitmap *out,
 		if (uint32_t *mirror = static_cast<uint32_t *>(device_alias(out->pixels)))
 			return run_canny_streamed(c, in, out, mirror);
 	}
+	static const bool pipe_env = !getenv("PF_B200_PAGEABLE_PIPELINE") || atoi(getenv("PF_B200_PAGEABLE_PIPELINE"));
+	if (pipe_env && op != OP_CANNY && h >= 512 && bytes >= kParallelMin && bytes <= kParallelMax
+			&& !is_pinned(in->pixels) && !is_pinned(out->pixels))
+		return run_stencil_pageable(c, op, in, out, taps);
 	if ((rc = upload(c, c.d_in.p, in->pixels, bytes)))
 		return rc;
 	const uint32_t *din = static_cast<const uint32_t *>(c.d_in.p);

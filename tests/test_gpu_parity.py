@@ -532,6 +532,42 @@ def test_streamed_paths_on_pinned_pages(gpu, oracle):
         lib.pf_b200_host_free(pin)
 
 
+def test_pageable_band_pipeline(gpu, oracle):
+    """Ordinary (malloc) memory on both sides, a page of 8 MB or more: host
+    threads stage bands in and out around the band pipeline.  Also in place,
+    and with a height that leaves a short last band."""
+    from libpillowfight_b200 import _capi
+    lib = _capi.lib
+    w, h = 1704, 1237                    # 8.4 MB, 16 bands of 78 -> 128 rows: 10 bands, the last short
+    page = synthetic_page(w, h, 21)
+
+    def bm(a):
+        b = _capi.PfBitmap()
+        b.size.x, b.size.y, b.pixels = w, h, a.ctypes.data
+        return b
+
+    out = np.full_like(page, 0x5A)
+    b_in, b_out = bm(page), bm(out)
+    ref_g, ref_s = oracle.gaussian(page, 2.0, 5), oracle.sobel(page)
+    for _ in range(3):                   # repeated: staging areas are reused
+        _capi.check(lib.pf_b200_gaussian(ctypes.byref(b_in), ctypes.byref(b_out), 2.0, 5))
+        assert np.array_equal(out, ref_g)
+        _capi.check(lib.pf_b200_sobel(ctypes.byref(b_in), ctypes.byref(b_out)))
+        assert np.array_equal(out, ref_s)
+    _capi.check(lib.pf_b200_gaussian(ctypes.byref(b_in), ctypes.byref(b_out), 3.0, 9))
+    assert np.array_equal(out, oracle.gaussian(page, 3.0, 9))
+    work = page.copy()
+    b_work = bm(work)
+    _capi.check(lib.pf_b200_sobel(ctypes.byref(b_work), ctypes.byref(b_work)))        # in place
+    assert np.array_equal(work, ref_s)
+    work[:] = page
+    _capi.check(lib.pf_b200_gaussian(ctypes.byref(b_work), ctypes.byref(b_work), 2.0, 5))
+    assert np.array_equal(work, ref_g)
+    # the other two calls on the same memory (plain staging)
+    _capi.check(lib.pf_b200_canny(ctypes.byref(b_in), ctypes.byref(b_out)))
+    assert np.array_equal(out, oracle.canny(page))
+
+
 def test_device_batch_entry_points(gpu, oracle):
     import torch
     from libpillowfight_b200.distributed import CudaChain
