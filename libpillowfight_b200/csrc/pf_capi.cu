@@ -810,6 +810,125 @@ static int run_stencil(Op op, const struct pf_bitmap *in, struct pf_bitmap *out,
 	return download(c, out->pixels, dout, bytes);
 }
 
+// ACE on ordinary (pageable) memory on both sides: the same pipeline as
+// run_stencil_pageable.  Bands are staged in by the pool and accumulated as
+// they arrive (the samples' pixel values go ahead); after the page-wide
+// extremes are known the rescale writes band after band into the second
+// staging area and the pool copies each out as soon as it is there.
+static int run_ace_pageable(Context &c, const struct pf_bitmap *in, struct pf_bitmap *out,
+		AceParams p, const int *sample_xy, const int *d_xy, uint32_t *d_spx,
+		double *minmax, double *scores)
+{
+	const int w = in->size.x, h = in->size.y;
+	const size_t npix = (size_t)w * h;
+	const size_t bytes = npix * sizeof(uint32_t);
+	int rows = (h + kMaxBands - 1) / kMaxBands;
+	if (rows < 128)
+		rows = 128;
+	const int nb = (h + rows - 1) / rows;
+	int rc = grow(c.h_stage, 2 * bytes + 256, true);
+	if (rc)
+		return rc;
+	char *stage_in = static_cast<char *>(c.h_stage.p);
+	char *stage_out = stage_in + ((bytes + 255) & ~(size_t)255);
+	uint32_t *direct = static_cast<uint32_t *>(device_alias(stage_out));
+	if (!direct)
+		return fail(PF_B200_ECUDA, "the pinned staging area is not mapped for the device");
+	const uint32_t *src32 = reinterpret_cast<const uint32_t *>(in->pixels);
+	const char *src = reinterpret_cast<const char *>(in->pixels);
+	char *dst = reinterpret_cast<char *>(out->pixels);
+	const uint32_t *din = static_cast<const uint32_t *>(c.d_in.p);
+
+	uint32_t spx[4096];
+	for (int i = 0; i < p.nb_samples; i++)
+		spx[i] = src32[(size_t)sample_xy[2 * i + 1] * w + sample_xy[2 * i]];
+	// (pageable source: the runtime stages it before returning)
+	PFB_CUDA(cudaMemcpyAsync(d_spx, spx, sizeof(uint32_t) * (size_t)p.nb_samples,
+			cudaMemcpyHostToDevice, c.st));
+	p.sample_px = d_spx;
+	p.score_row0 = 0;
+	p.score_plane = (long)npix;
+
+	std::atomic<int> in_ready[kMaxBands], out_ready[kMaxBands];
+	for (int b = 0; b < nb; b++) {
+		in_ready[b].store(0);
+		out_ready[b].store(0);
+	}
+	std::atomic<bool> failed(false);
+	cudaError_t sync_err[kMaxBands] = {};
+	auto band_off = [&](int b) { return (size_t)b * rows * w * sizeof(uint32_t); };
+	auto band_len = [&](int b) {
+		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
+		return (size_t)(y1 - y0) * w * sizeof(uint32_t);
+	};
+	const int nthreads = copy_threads();
+	auto work = [&](int t) {
+		cudaSetDevice(c.dev);
+		for (int b = t; b < nb; b += nthreads) {
+			copy_slice(stage_in + band_off(b), src + band_off(b), band_len(b));
+			in_ready[b].store(1, std::memory_order_release);
+		}
+		for (int b = t; b < nb; b += nthreads) {
+			while (!out_ready[b].load(std::memory_order_acquire)) {
+				if (failed.load())
+					return;
+				std::this_thread::yield();
+			}
+			sync_err[b] = cudaEventSynchronize(c.ev_done[b]);
+			if (sync_err[b] == cudaSuccess)
+				copy_slice(dst + band_off(b), stage_out + band_off(b), band_len(b));
+		}
+	};
+	c.pool.ensure(nthreads);
+	c.pool.start([&](int t) {
+		if (t < nthreads)
+			work(t);
+	});
+
+	auto cuda_rc = [&](cudaError_t e, const char *what) {
+		return e == cudaSuccess ? PF_B200_OK : fail(PF_B200_ECUDA, "%s: %s", what, cudaGetErrorString(e));
+	};
+	for (int b = 0; b < nb && !rc; b++) {
+		while (!in_ready[b].load(std::memory_order_acquire))
+			std::this_thread::yield();
+		rc = cuda_rc(cudaMemcpyAsync(const_cast<uint32_t *>(din) + band_off(b) / sizeof(uint32_t),
+				stage_in + band_off(b), band_len(b), cudaMemcpyHostToDevice, c.st_up), "upload");
+		if (!rc)
+			rc = cuda_rc(cudaEventRecord(c.ev_up[b], c.st_up), "upload");
+		if (!rc)
+			rc = cuda_rc(cudaStreamWaitEvent(c.st, c.ev_up[b], 0), "upload");
+		if (!rc) {
+			p.row_begin = b * rows;
+			p.row_end = (p.row_begin + rows < h) ? p.row_begin + rows : h;
+			rc = launch_ace_scores(din, d_xy, p, scores, minmax, c.st);
+		}
+	}
+	if (!rc) {
+		p.row_begin = 0;
+		p.row_end = h;
+		rc = launch_ace_refine(din, d_xy, p, scores, minmax, c.st);
+	}
+	for (int b = 0; b < nb && !rc; b++) {
+		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
+		rc = launch_ace_scale(scores + (size_t)y0 * w, minmax, w, y1 - y0,
+				direct + (size_t)y0 * w, c.st, (long)npix);
+		if (!rc)
+			rc = cuda_rc(cudaEventRecord(c.ev_done[b], c.st), "rescale");
+		if (!rc)
+			out_ready[b].store(1, std::memory_order_release);
+	}
+	if (rc)
+		failed.store(true);
+	c.pool.wait();
+	if (!rc)
+		for (int b = 0; b < nb; b++)
+			if (sync_err[b] != cudaSuccess)
+				rc = fail(PF_B200_ECUDA, "download: %s", cudaGetErrorString(sync_err[b]));
+	cudaStreamSynchronize(c.st);
+	cudaStreamSynchronize(c.st_up);
+	return rc;
+}
+
 static int run_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
 		int nb_samples, const int *sample_xy, double slope, double limit)
 {
@@ -899,6 +1018,10 @@ static int run_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
 		return PF_B200_OK;
 	}
 
+	static const bool pipe_env = !getenv("PF_B200_PAGEABLE_PIPELINE") || atoi(getenv("PF_B200_PAGEABLE_PIPELINE"));
+	if (pipe_env && h >= 512 && nb_samples <= 4096 && bytes >= kParallelMin && bytes <= kParallelMax
+			&& !is_pinned(in->pixels) && !is_pinned(out->pixels))
+		return run_ace_pageable(c, in, out, p, sample_xy, d_xy, d_spx, minmax, scores);
 	if ((rc = upload(c, c.d_in.p, in->pixels, bytes)))
 		return rc;
 	if ((rc = launch_ace_scores(din, d_xy, p, scores, minmax, c.st)))

@@ -563,9 +563,21 @@ def test_pageable_band_pipeline(gpu, oracle):
     work[:] = page
     _capi.check(lib.pf_b200_gaussian(ctypes.byref(b_work), ctypes.byref(b_work), 2.0, 5))
     assert np.array_equal(work, ref_g)
-    # the other two calls on the same memory (plain staging)
+    # Canny on the same memory (plain staging)
     _capi.check(lib.pf_b200_canny(ctypes.byref(b_in), ctypes.byref(b_out)))
     assert np.array_equal(out, oracle.canny(page))
+    # ACE: bands accumulated as they are staged in, rescaled bands staged out
+    xy = oracle.ace_draw_samples(40, w, h, 17)
+    xyp = xy.ctypes.data_as(ctypes.POINTER(ctypes.c_int))
+    ref_a = oracle.ace_with_samples(page, xy, 10.0, 1000.0, nb_threads=8)
+    for _ in range(2):
+        out[:] = 0x5A
+        _capi.check(lib.pf_b200_ace(ctypes.byref(b_in), ctypes.byref(b_out), 40, xyp, 10.0, 1000.0))
+        assert_fp_parity(out, ref_a, "pageable ace")
+    assert np.array_equal(out, gpu.ace(page, 10, 1000, 40, seed=17))     # same kernels, same tiles
+    work[:] = page
+    _capi.check(lib.pf_b200_ace(ctypes.byref(b_work), ctypes.byref(b_work), 40, xyp, 10.0, 1000.0))
+    assert np.array_equal(work, out)
 
 
 def test_device_batch_entry_points(gpu, oracle):
