@@ -670,7 +670,12 @@ static int run_stencil_pageable(Context &c, Op op, const struct pf_bitmap *in,
 		return rc;
 	char *stage_in = static_cast<char *>(c.h_stage.p);
 	char *stage_out = stage_in + ((bytes + 255) & ~(size_t)255);
-	uint32_t *direct = static_cast<uint32_t *>(device_alias(stage_out));
+	// pinned caller memory on the way back (the Python layer's result arrays):
+	// the kernels write into it directly and nothing is staged out
+	uint32_t *direct = static_cast<uint32_t *>(device_alias(out->pixels));
+	const bool stage_back = direct == nullptr;
+	if (stage_back)
+		direct = static_cast<uint32_t *>(device_alias(stage_out));
 	if (!direct)
 		return fail(PF_B200_ECUDA, "the pinned staging area is not mapped for the device");
 	const char *src = reinterpret_cast<const char *>(in->pixels);
@@ -696,7 +701,7 @@ static int run_stencil_pageable(Context &c, Op op, const struct pf_bitmap *in,
 			copy_slice(stage_in + band_off(b), src + band_off(b), band_len(b));
 			in_ready[b].store(1, std::memory_order_release);
 		}
-		for (int b = t; b < nb; b += nthreads) {
+		for (int b = t; stage_back && b < nb; b += nthreads) {
 			while (!out_ready[b].load(std::memory_order_acquire)) {
 				if (failed.load())
 					return;
@@ -783,7 +788,7 @@ static int run_stencil(Op op, const struct pf_bitmap *in, struct pf_bitmap *out,
 	}
 	static const bool pipe_env = !getenv("PF_B200_PAGEABLE_PIPELINE") || atoi(getenv("PF_B200_PAGEABLE_PIPELINE"));
 	if (pipe_env && op != OP_CANNY && h >= 512 && bytes >= kParallelMin && bytes <= kParallelMax
-			&& !is_pinned(in->pixels) && !is_pinned(out->pixels))
+			&& !is_pinned(in->pixels))
 		return run_stencil_pageable(c, op, in, out, taps);
 	if ((rc = upload(c, c.d_in.p, in->pixels, bytes)))
 		return rc;
@@ -831,7 +836,12 @@ static int run_ace_pageable(Context &c, const struct pf_bitmap *in, struct pf_bi
 		return rc;
 	char *stage_in = static_cast<char *>(c.h_stage.p);
 	char *stage_out = stage_in + ((bytes + 255) & ~(size_t)255);
-	uint32_t *direct = static_cast<uint32_t *>(device_alias(stage_out));
+	// pinned caller memory on the way back (the Python layer's result arrays):
+	// the kernels write into it directly and nothing is staged out
+	uint32_t *direct = static_cast<uint32_t *>(device_alias(out->pixels));
+	const bool stage_back = direct == nullptr;
+	if (stage_back)
+		direct = static_cast<uint32_t *>(device_alias(stage_out));
 	if (!direct)
 		return fail(PF_B200_ECUDA, "the pinned staging area is not mapped for the device");
 	const uint32_t *src32 = reinterpret_cast<const uint32_t *>(in->pixels);
@@ -868,7 +878,7 @@ static int run_ace_pageable(Context &c, const struct pf_bitmap *in, struct pf_bi
 			copy_slice(stage_in + band_off(b), src + band_off(b), band_len(b));
 			in_ready[b].store(1, std::memory_order_release);
 		}
-		for (int b = t; b < nb; b += nthreads) {
+		for (int b = t; stage_back && b < nb; b += nthreads) {
 			while (!out_ready[b].load(std::memory_order_acquire)) {
 				if (failed.load())
 					return;
@@ -1020,7 +1030,7 @@ static int run_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
 
 	static const bool pipe_env = !getenv("PF_B200_PAGEABLE_PIPELINE") || atoi(getenv("PF_B200_PAGEABLE_PIPELINE"));
 	if (pipe_env && h >= 512 && nb_samples <= 4096 && bytes >= kParallelMin && bytes <= kParallelMax
-			&& !is_pinned(in->pixels) && !is_pinned(out->pixels))
+			&& !is_pinned(in->pixels))
 		return run_ace_pageable(c, in, out, p, sample_xy, d_xy, d_spx, minmax, scores);
 	if ((rc = upload(c, c.d_in.p, in->pixels, bytes)))
 		return rc;
