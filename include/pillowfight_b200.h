@@ -64,9 +64,12 @@ struct pf_dbl_matrix {
 /* Drop-in entry points: host bitmaps in, host bitmaps out.                  */
 /* `out->pixels` is caller-allocated, same size as `in`; in/out may alias.   */
 /* These are void like the reference's.  On a CUDA failure (no device, out   */
-/* of memory, launch error) they print one line to stderr, record the error  */
-/* (pf_b200_last_error) and leave `out` untouched; with the environment      */
-/* variable PF_B200_ABORT_ON_ERROR=1 they abort().  There is no CPU fallback. */
+/* of memory, launch error) they print one line to stderr and record the     */
+/* error (pf_b200_last_error); `out` is then undefined (untouched when the   */
+/* arguments were refused, possibly partly written when a copy or a kernel   */
+/* failed half way), and no work of the call is still in flight on return.   */
+/* With the environment variable PF_B200_ABORT_ON_ERROR=1 they abort().      */
+/* There is no CPU fallback.                                                 */
 /* ------------------------------------------------------------------------ */
 
 /* replaces upstream src/pillowfight/_ace.c: pf_ace().  Draws nb_samples
@@ -215,8 +218,13 @@ int pf_b200_dev_canny(const uint32_t *d_in, uint32_t *d_out,
  * The call itself performs no cudaMalloc, cudaFree or other allocating call.
  *
  * The first call on each device looks up the array's device address (once
- * per device, with that device current).  Make that first call during
- * set-up, before any stream capture is started.
+ * per device, with that device current) and keeps it for the life of the
+ * process, indexed by device ordinal.  Make that first call during set-up,
+ * before any stream capture is started; with CUDA's lazy module loading it is
+ * also the moment the array comes into being on that GPU.  The remembered
+ * address belongs to the device's primary context: after cudaDeviceReset(),
+ * or with a second (driver-API) context current on the same ordinal, it no
+ * longer points at the array, so neither is supported with this entry point.
  *
  * Every call on a device shares the one array.  Each call clears the part
  * that has to start at zero and overwrites the rest as it goes, so calls that

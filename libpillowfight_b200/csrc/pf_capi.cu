@@ -97,11 +97,19 @@ public:
 			t.join();
 	}
 	int size() const { return (int)threads_.size(); }
+	// Only between jobs (never while one is running): a new worker starts at
+	// the generation current now, so it waits for the NEXT start() and never
+	// sees the previous call's job.
 	void ensure(int n)
 	{
 		while ((int)threads_.size() < n) {
 			const int idx = (int)threads_.size();
-			threads_.emplace_back([this, idx] { loop(idx); });
+			unsigned long gen;
+			{
+				std::lock_guard<std::mutex> lk(m_);
+				gen = generation_;
+			}
+			threads_.emplace_back([this, idx, gen] { loop(idx, gen); });
 		}
 	}
 	void start(std::function<void(int)> f)
@@ -116,12 +124,12 @@ public:
 	{
 		std::unique_lock<std::mutex> lk(m_);
 		cv_done_.wait(lk, [this] { return pending_ == 0; });
+		job_ = nullptr;     // its captures die with the caller's frame
 	}
 
 private:
-	void loop(int idx)
+	void loop(int idx, unsigned long seen)
 	{
-		unsigned long seen = 0;
 		for (;;) {
 			std::function<void(int)> f;
 			{
@@ -232,6 +240,21 @@ static int grow(Buffer &b, size_t bytes, bool pinned)
 		PFB_CUDA(cudaMalloc(&b.p, bytes));
 	b.cap = bytes;
 	return PF_B200_OK;
+}
+
+// A streamed call that fails half way leaves copies and kernels queued that
+// still read the caller's input or write its output; nothing of the call may
+// be in flight when it returns (the caller may free the pages, and the next
+// call reuses the device buffers and events).
+static int drained(Context &c, int rc)
+{
+	if (rc != PF_B200_OK && c.st) {
+		cudaStreamSynchronize(c.st_up);
+		cudaStreamSynchronize(c.st);
+		cudaStreamSynchronize(c.st_down);
+		cudaGetLastError();
+	}
+	return rc;
 }
 
 static bool is_pinned(const void *p)
@@ -939,7 +962,7 @@ static int run_ace_pageable(Context &c, const struct pf_bitmap *in, struct pf_bi
 	return rc;
 }
 
-static int run_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
+static int run_ace_impl(const struct pf_bitmap *in, struct pf_bitmap *out,
 		int nb_samples, const int *sample_xy, double slope, double limit)
 {
 	clear_error();
@@ -1041,6 +1064,13 @@ static int run_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
 	if ((rc = launch_ace_scale(scores, minmax, w, h, dout, c.st)))
 		return rc;
 	return download(c, out->pixels, c.d_out.p, bytes);
+}
+
+static int run_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
+		int nb_samples, const int *sample_xy, double slope, double limit)
+{
+	const int rc = run_ace_impl(in, out, nb_samples, sample_xy, slope, limit);
+	return (rc != PF_B200_OK && t_ctx.st) ? drained(t_ctx, rc) : rc;
 }
 
 static void report(const char *who, int rc)

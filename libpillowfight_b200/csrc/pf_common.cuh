@@ -1,5 +1,6 @@
 // Shared declarations of the sm_100a build of libpillowfight's hot path.
-// Kernels live in pf_stencil.cu / pf_ace.cu, the C-ABI in pf_capi.cu.
+// Kernels live in pf_gaussian.cu, pf_edges.cu, pf_ace.cu and pf_matrix.cu, the
+// C-ABI in pf_capi.cu.
 #pragma once
 
 #include <cuda_runtime.h>
@@ -71,8 +72,9 @@ int launch_gradient_polar(const double *gx, const double *gy, double *intensity,
 		double *direction, size_t n, cudaStream_t st);
 
 // ---- programmatic dependent launch ---------------------------------------
-// Every kernel of this library begins with pdl_wait() and is launched with
-// launch_pdl(): its blocks may be scheduled while the kernel before it on the
+// Every kernel of the bitmap path (pf_gaussian.cu, pf_edges.cu, pf_ace.cu; the
+// pf_dbl_matrix kernels of pf_matrix.cu are launched the plain way) begins
+// with pdl_wait() and is launched with launch_pdl(): its blocks may be scheduled while the kernel before it on the
 // stream is still draining, and wait (griddepcontrol.wait: until that kernel
 // has completed and its writes are visible) before they touch memory.  What is
 // saved is the launch latency between dependent kernels, a few microseconds

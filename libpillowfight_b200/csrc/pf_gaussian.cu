@@ -219,15 +219,16 @@ __device__ __noinline__ uint32_t gaussian_exact_pixel_n(const uint32_t *__restri
 // Any tap count: one thread per pixel.
 __global__ void __launch_bounds__(kBlock)
 gaussian_generic_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
-		int w, int h, int y_begin, const Taps tp)
+		int w, int h, int y_begin, int y_end, const Taps tp)
 {
 	pdl_wait();
 	const int x = blockIdx.x * kBlock + threadIdx.x;
-	const int y = y_begin + blockIdx.y;
 	if (x >= w)
 		return;
 	const size_t page = (size_t)blockIdx.z * w * h;
-	out[page + (size_t)y * w + x] = gaussian_exact_pixel(in + page, w, h, x, y, tp.t, tp.n);
+	// grid.y is capped at 65535: taller row ranges wrap around
+	for (int y = y_begin + blockIdx.y; y < y_end; y += gridDim.y)
+		out[page + (size_t)y * w + x] = gaussian_exact_pixel(in + page, w, h, x, y, tp.t, tp.n);
 }
 
 // ---------------------------------------------------------------------------
@@ -578,8 +579,9 @@ int launch_gaussian(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 	case 7: launch_gaussian_n<7>(in, out, w, h, pages, taps, st, y_begin, y_end); break;
 	case 9: launch_gaussian_n<9>(in, out, w, h, pages, taps, st, y_begin, y_end); break;
 	default: {
-		dim3 grid((w + kBlock - 1) / kBlock, y_end - y_begin, pages);
-		launch_pdl(gaussian_generic_kernel, grid, dim3(kBlock), 0, st, in, out, w, h, y_begin, taps);
+		const int nrows = y_end - y_begin;
+		dim3 grid((w + kBlock - 1) / kBlock, nrows < 65535 ? nrows : 65535, pages);
+		launch_pdl(gaussian_generic_kernel, grid, dim3(kBlock), 0, st, in, out, w, h, y_begin, y_end, taps);
 	}
 	}
 	PFB_CUDA(cudaGetLastError());

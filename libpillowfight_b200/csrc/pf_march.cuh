@@ -59,9 +59,6 @@ __device__ __forceinline__ void store_px4(uint32_t *__restrict__ img,
 			row[x0 + i] = v[i];
 }
 
-// Horizontal parts of the two Sobel kernels for the lane's 4 columns:
-//   hd = g(x-1) - g(x+1)            (g_x row term, kernel flipped)
-
 // ---------------------------------------------------------------------------
 // Row access for the march.  FAST: the width is a multiple of 4 and rows are
 // 16-byte aligned, so a lane's 4 columns are inside the page or outside it

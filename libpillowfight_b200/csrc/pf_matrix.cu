@@ -31,23 +31,25 @@ matrix_convolution_kernel(const double *__restrict__ img, double *__restrict__ o
 		int w, int h, const ConvKernel k)
 {
 	const int x = blockIdx.x * blockDim.x + threadIdx.x;
-	const int y = blockIdx.y;
 	if (x >= w)
 		return;
 	const int cx = k.nx / 2, cy = k.ny / 2;
-	double val = 0.0;
-	for (int kx = 0; kx < k.nx; kx++) {
-		const int ix = x - kx + cx;
-		if (ix < 0 || ix >= w)
-			continue;
-		for (int ky = 0; ky < k.ny; ky++) {
-			const int iy = y - ky + cy;
-			if (iy < 0 || iy >= h)
+	// grid.y is capped at 65535: taller matrices wrap around
+	for (int y = blockIdx.y; y < h; y += gridDim.y) {
+		double val = 0.0;
+		for (int kx = 0; kx < k.nx; kx++) {
+			const int ix = x - kx + cx;
+			if (ix < 0 || ix >= w)
 				continue;
-			val = __dadd_rn(val, __dmul_rn(__ldg(img + (size_t)iy * w + ix), k.v[ky * k.nx + kx]));
+			for (int ky = 0; ky < k.ny; ky++) {
+				const int iy = y - ky + cy;
+				if (iy < 0 || iy >= h)
+					continue;
+				val = __dadd_rn(val, __dmul_rn(__ldg(img + (size_t)iy * w + ix), k.v[ky * k.nx + kx]));
+			}
 		}
+		out[(size_t)y * w + x] = val;
 	}
-	out[(size_t)y * w + x] = val;
 }
 
 // intensity = hypot(g_x, g_y), direction = atan2(g_y, g_x)
@@ -75,7 +77,7 @@ int launch_matrix_convolution(const double *img, double *out, int w, int h,
 	k.ny = ny;
 	for (int i = 0; i < nx * ny; i++)
 		k.v[i] = kernel[i];
-	dim3 grid((w + 255) / 256, h);
+	dim3 grid((w + 255) / 256, h < 65535 ? h : 65535);
 	matrix_convolution_kernel<<<grid, 256, 0, st>>>(img, out, w, h, k);
 	PFB_CUDA(cudaGetLastError());
 	return PF_B200_OK;

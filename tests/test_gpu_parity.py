@@ -111,8 +111,8 @@ def test_canny_long_weak_chains(gpu, oracle):
 
 
 def test_canny_snake_fills_queues(gpu, oracle):
-    # dense weak texture seeded by a few strong pixels: stresses the per-warp
-    # queues (overflow -> repeat sweep path)
+    # dense weak texture seeded by a few strong pixels: a long work list, so the
+    # grid-wide union-find path of the hysteresis kernel
     rng = np.random.default_rng(5)
     h, w = 256, 256
     g = (rng.integers(0, 2, size=(h, w)) * 45).astype(np.uint8)

@@ -58,6 +58,38 @@ def test_noalloc_canny_matches_the_ordinary_entry_point_twice(pf):
     assert (ref2[..., 0] == 255).any()
     # and it is the same answer the host-pointer entry point gives
     assert np.array_equal(got2, pf.canny(small))
+    # ... and the CPU oracle, directly (not only through the other entry point)
+    from oracle import pf_oracle
+    assert np.array_equal(got, pf_oracle.canny(big))
+    assert np.array_equal(got2, pf_oracle.canny(small))
+
+
+def test_noalloc_canny_allocates_nothing(pf):
+    """What the name promises: once the entry point has been called on the
+    device (set-up), further calls leave the amount of free device memory where
+    it was.  torch's caching allocator is kept out of the measured region (the
+    buffers exist before it starts), so any change would be the library's."""
+    import torch
+    from libpillowfight_b200 import _capi
+    if pf.device_count() <= 0:
+        pytest.fail("no CUDA device: the gpu-marked tests must run on the B200 box")
+    lib = _capi.lib
+    dev = torch.device("cuda:0")
+    page = synthetic_page(1024, 768, 3)
+    h, w = page.shape[:2]
+    tin = torch.from_numpy(page).to(dev)
+    out = torch.zeros_like(tin)
+    st = torch.cuda.current_stream().cuda_stream
+    _capi.check(lib.pf_b200_dev_canny_noalloc(tin.data_ptr(), out.data_ptr(), w, h, st))   # set-up call
+    torch.cuda.synchronize()
+    free_before, _ = torch.cuda.mem_get_info(dev)
+    for _ in range(5):
+        _capi.check(lib.pf_b200_dev_canny_noalloc(tin.data_ptr(), out.data_ptr(), w, h, st))
+    torch.cuda.synchronize()
+    free_after, _ = torch.cuda.mem_get_info(dev)
+    assert free_after == free_before
+    from oracle import pf_oracle
+    assert np.array_equal(out.cpu().numpy(), pf_oracle.canny(page))
 
 
 def test_noalloc_canny_refuses_pages_beyond_its_limit(pf):
