@@ -59,6 +59,18 @@ PROBE(k_f2f64, double, threadIdx.x + i,
 PROBE(k_vabsdiff4, uint32_t, threadIdx.x + i,
 	asm volatile("vabsdiff4.u32.u32.u32.add %0, %0, %1, %2;" : "+r"(v[i]) : "r"(a), "r"(b)); asm volatile("vabsdiff4.u32.u32.u32.add %0, %0, %2, %1;" : "+r"(v[i]) : "r"(a), "r"(b)))
 
+PROBE(k_rsq32, float, threadIdx.x + i + 1.0f,
+	asm volatile("rsqrt.approx.ftz.f32 %0, %0;" : "+f"(v[i])); asm volatile("rsqrt.approx.ftz.f32 %0, %0;" : "+f"(v[i])))
+PROBE(k_ffma2, unsigned long long, threadIdx.x + i,
+	asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(v[i]) : "l"(a), "l"(b)); asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(v[i]) : "l"(a), "l"(b)))
+PROBE(k_fadd2, unsigned long long, threadIdx.x + i,
+	asm volatile("add.rn.f32x2 %0, %0, %1;" : "+l"(v[i]) : "l"(a)); asm volatile("add.rn.f32x2 %0, %0, %1;" : "+l"(v[i]) : "l"(b)))
+PROBE(k_fadd, float, threadIdx.x + i,
+	asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(v[i]) : "f"(a)); asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(v[i]) : "f"(b)))
+PROBE(k_ffma_denorm, float, __int_as_float(threadIdx.x + i),
+	asm volatile("fma.rn.f32 %0, %1, %2, %0;" : "+f"(v[i]) : "f"(a), "f"(b)); asm volatile("fma.rn.f32 %0, %2, %1, %0;" : "+f"(v[i]) : "f"(a), "f"(b)))
+PROBE(k_viaddmnmx, int, threadIdx.x + i,
+	asm volatile("{ .reg .s32 t; add.s32 t, %0, %1; min.s32 t, t, %2; max.s32 %0, t, 0; }" : "+r"(v[i]) : "r"(a), "r"(b)); asm volatile("{ .reg .s32 t; add.s32 t, %0, %2; min.s32 t, t, %1; max.s32 %0, t, 0; }" : "+r"(v[i]) : "r"(a), "r"(b)))
 
 // ---- pairs of instruction kinds interleaved: do their pipes overlap? ------
 #define MIX(NAME, BODYA, BODYB)                                                \
@@ -218,6 +230,12 @@ int main()
 	run<double>("i2f.f64", k_i2f64, 0.0, 0.0, sms, ghz);
 	run<double>("f2f.f64.f32", k_f2f64, 0.0, 0.0, sms, ghz);
 	run<uint32_t>("vabsdiff4", k_vabsdiff4, 0x01020304u, 0x04030201u, sms, ghz);
+	run<float>("rsqrt32.ftz", k_rsq32, 0.f, 0.f, sms, ghz);
+	run<unsigned long long>("ffma2", k_ffma2, 0x3f8000013f800001ull, 0x3089705f3089705full, sms, ghz);
+	run<unsigned long long>("fadd2", k_fadd2, 0x3fc000003fc00000ull, 0xbfc00000bfc00000ull, sms, ghz);
+	run<float>("fadd", k_fadd, 1.5f, -1.5f, sms, ghz);
+	run<float>("ffma denormal op", k_ffma_denorm, 1e20f, 1.4e-43f, sms, ghz);
+	run<int>("viaddmnmx.relu", k_viaddmnmx, 3, 200, sms, ghz);
 	printf("mixed probes: 16 warps per SMSP, each iteration = 8 A + 8 B instructions per warp\n");
 	run_mix("dfma only", m_dfma_only, sms, ghz, 8);
 	run_mix("dfma+vimnmx", m_dfma_vmnmx, sms, ghz, 16);
