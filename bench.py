@@ -315,7 +315,7 @@ def run_b200(args):
     out_g = torch.empty_like(pages)
     out_s = torch.empty_like(pages)
     out_c = torch.empty_like(pages)
-    scores = torch.empty((3, h, w), dtype=torch.float64, device=dev)
+    scores = torch.empty(lib.pf_b200_ace_scores_bytes(w, h), dtype=torch.uint8, device=dev)
     minmax = torch.empty(lib.pf_b200_ace_minmax_bytes(w, h) // 8, dtype=torch.float64, device=dev)
     scratch = torch.empty(lib.pf_b200_canny_scratch_bytes(w, h), dtype=torch.uint8, device=dev)
     st = torch.cuda.current_stream().cuda_stream
@@ -327,7 +327,8 @@ def run_b200(args):
                                        10.0, 1000.0, scores.data_ptr(), minmax.data_ptr(), st))
         chk(lib.pf_b200_dev_ace_refine(pages[i].data_ptr(), w, h, 0, h, xy.data_ptr(), 100,
                                        10.0, 1000.0, scores.data_ptr(), minmax.data_ptr(), st))
-        chk(lib.pf_b200_dev_ace_scale(scores.data_ptr(), minmax.data_ptr(), w, h,
+        chk(lib.pf_b200_dev_ace_scale(pages[i].data_ptr(), w, h, 0, h, xy.data_ptr(), 100,
+                                      10.0, 1000.0, scores.data_ptr(), minmax.data_ptr(),
                                       out_ace[i].data_ptr(), st))
 
     def do_gauss(i):
@@ -398,8 +399,9 @@ def run_b200(args):
         chk(lib.pf_b200_dev_ace_refine(pages[i].data_ptr(), w, h, 0, h, xy.data_ptr(), 100,
                                        10.0, 1000.0, scores.data_ptr(), minmax.data_ptr(), st))
 
-    def ace_scale_only(i):
-        chk(lib.pf_b200_dev_ace_scale(scores.data_ptr(), minmax.data_ptr(), w, h,
+    def ace_scale_only(i):      # rescale + fix-up pass
+        chk(lib.pf_b200_dev_ace_scale(pages[i].data_ptr(), w, h, 0, h, xy.data_ptr(), 100,
+                                      10.0, 1000.0, scores.data_ptr(), minmax.data_ptr(),
                                       out_ace[i].data_ptr(), st))
 
     iters = max(10, min(K, 50))
@@ -521,7 +523,7 @@ def run_b200(args):
             mm6 = comp.new_minmax(dev, w6, h6)
             sc6 = comp.scores(big, xy6, 10.0, 1000.0, (0, h6), mm6)
             comp.refine(big, xy6, 10.0, 1000.0, (0, h6), sc6, mm6)
-            same6 = bool(torch.equal(comp.scale(sc6, mm6), out6))
+            same6 = bool(torch.equal(comp.scale(big, xy6, 10.0, 1000.0, (0, h6), sc6, mm6), out6))
             del sc6
         extras["ace_600dpi_row_bands"] = {
             "workload": "pf_apply_ace 4960x7016, 400 samples, rows split over %d GPU(s); NCCL scatter "

@@ -242,45 +242,52 @@ int pf_b200_dev_sobel_batch(const uint32_t *d_in, uint32_t *d_out,
 		int width, int height, int nb_pages, void *stream);
 
 /* ACE in device passes so that row bands can be split across GPUs
- * (BASELINE.json config 4).  d_minmax is a block of
- * pf_b200_ace_minmax_bytes(width, height) bytes on the device: doubles
- * [0..2] minimum and [3..5] maximum of R, G, B over the accumulated scores,
- * [6..8] and [9..11] the same over the scores pass 3 recomputed, then one
- * entry per tile of the page (bookkeeping of the passes).
+ * (BASELINE.json config 4).  upstream _ace.c: ace_thread_adjustment (passes
+ * 1, 3 and the second half of 5), ace_thread_scaling (pass 5).
+ *
+ * How the result is made the reference's for every pixel: pass 1 computes the
+ * scores in FP32 with a worst-case error bound; pass 3 recomputes, in the
+ * reference's own arithmetic (IEEE sqrt and divide, sample order), the scores
+ * that could be the page's extremes, so the extremes are exact; pass 5
+ * rescales with them and recomputes the same way every pixel whose rescaled
+ * value lies closer to an integer than the bound allows (a fraction of a per
+ * cent of a page).
+ *
+ * d_minmax: pf_b200_ace_minmax_bytes(width, height) bytes on the device:
+ *   doubles [0..2] minimum and [3..5] maximum of R, G, B over the pass-1
+ *   scores, [6..8] and [9..11] the exact extremes of pass 3, then one entry
+ *   per tile of the page (bookkeeping of the passes).  One per page and GPU.
+ * d_scores: a score block of pf_b200_ace_scores_bytes(width, row_end-row_begin)
+ *   bytes, 256-byte aligned, per band: three FP32 score planes plus the list
+ *   of pixels pass 5 has to recompute (16 bytes per pixel and a header).
+ * d_samples: nb_samples * 2 ints (x, y) on the device.
+ *
  *   0. pf_b200_dev_ace_minmax_init: once per page and device.
- *   1. pf_b200_dev_ace_scores: for rows [row_begin, row_end) of the page,
- *      accumulate the per-pixel, per-channel scores into d_scores
- *      (3 doubles per pixel of the band: plane-major R, G, B, each
- *      (row_end-row_begin)*width doubles) and fold the band's per-channel
- *      minimum / maximum into d_minmax.
+ *   1. pf_b200_dev_ace_scores: rows [row_begin, row_end) of the page.
  *   2. (multi-GPU only) all-reduce d_minmax[0..5]: min over the first 3, max
  *      over the last 3.
- *   3. pf_b200_dev_ace_refine, same arguments as pass 1: the scores within
- *      2^-15 of the page's range of either extreme are recomputed in the
- *      reference's exact arithmetic (IEEE sqrt and divisions, sample order),
- *      because the rescale turns the last bit of a score at the maximum into
- *      the difference between 254 and 255.  Optional: without it the result
- *      stays within +-1 of the reference's.
+ *   3. pf_b200_dev_ace_refine, same arguments as pass 1.  Not optional.
  *   4. (multi-GPU only) all-reduce d_minmax[6..11] the same way.
- *   5. pf_b200_dev_ace_scale: rescale the band's scores to RGBA8 rows of
- *      d_out_band ((row_end-row_begin)*width pixels).
- * d_samples: nb_samples * 2 ints (x, y) on the device.
- * upstream _ace.c: ace_thread_adjustment (passes 1 and 3), ace_thread_scaling
- * (pass 5). */
+ *   5. pf_b200_dev_ace_scale, same arguments plus the destination: the
+ *      band's RGBA8 rows into d_out_band ((row_end-row_begin)*width pixels).
+ */
 size_t pf_b200_ace_minmax_bytes(int width, int height);
+size_t pf_b200_ace_scores_bytes(int width, int nb_rows);
 int pf_b200_dev_ace_minmax_init(double *d_minmax, int width, int height, void *stream);
-int pf_b200_dev_ace_refine(const uint32_t *d_in, int width, int height,
-		int row_begin, int row_end,
-		const int *d_samples, int nb_samples, double slope, double limit,
-		double *d_scores, double *d_minmax, void *stream);
 int pf_b200_dev_ace_scores(const uint32_t *d_in, int width, int height,
 		int row_begin, int row_end,
 		const int *d_samples, int nb_samples, double slope, double limit,
-		double *d_scores, double *d_minmax, void *stream);
-int pf_b200_dev_ace_scale(const double *d_scores, const double *d_minmax,
-		int width, int nb_rows, uint32_t *d_out_band, void *stream);
+		void *d_scores, double *d_minmax, void *stream);
+int pf_b200_dev_ace_refine(const uint32_t *d_in, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, int nb_samples, double slope, double limit,
+		void *d_scores, double *d_minmax, void *stream);
+int pf_b200_dev_ace_scale(const uint32_t *d_in, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, int nb_samples, double slope, double limit,
+		void *d_scores, double *d_minmax, uint32_t *d_out_band, void *stream);
 
-/* The same two passes for a GPU that holds only its band of the page: d_band
+/* The same three passes for a GPU that holds only its band of the page: d_band
  * points at row row_begin (rows [row_begin, row_end) back to back) and
  * d_sample_px holds the nb_samples sample pixels' values, gathered where the
  * whole page is (page[y_k * width + x_k]).  A row-band split then moves
@@ -289,31 +296,45 @@ int pf_b200_dev_ace_scores_band(const uint32_t *d_band, int width, int height,
 		int row_begin, int row_end,
 		const int *d_samples, const uint32_t *d_sample_px, int nb_samples,
 		double slope, double limit,
-		double *d_scores, double *d_minmax, void *stream);
+		void *d_scores, double *d_minmax, void *stream);
 int pf_b200_dev_ace_refine_band(const uint32_t *d_band, int width, int height,
 		int row_begin, int row_end,
 		const int *d_samples, const uint32_t *d_sample_px, int nb_samples,
 		double slope, double limit,
-		double *d_scores, double *d_minmax, void *stream);
+		void *d_scores, double *d_minmax, void *stream);
+int pf_b200_dev_ace_scale_band(const uint32_t *d_band, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, const uint32_t *d_sample_px, int nb_samples,
+		double slope, double limit,
+		void *d_scores, double *d_minmax, uint32_t *d_out_band, void *stream);
 
 /* Pass 5 with several destinations: the band's rows are stored to nb_outs
  * images at once (d_outs: HOST array of nb_outs device pointers, 1..16, each
  * pointing at the band's first row in that image).  The images may live on
  * other GPUs (peer-mapped memory): in a row-band split every GPU writes its
  * band straight into every GPU's result over NVLink and the all-gather
- * disappears. */
-int pf_b200_dev_ace_scale_to(const double *d_scores, const double *d_minmax,
-		int width, int nb_rows, uint32_t *const *d_outs, int nb_outs, void *stream);
+ * disappears.  d_band / d_sample_px as above; with d_sample_px == NULL d_band
+ * must lie inside the whole page (the samples are then read from it). */
+int pf_b200_dev_ace_scale_to(const uint32_t *d_band, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, const uint32_t *d_sample_px, int nb_samples,
+		double slope, double limit,
+		void *d_scores, double *d_minmax,
+		uint32_t *const *d_outs, int nb_outs, void *stream);
 /* The same with ONE destination that is an NVLS multicast address (a
  * multicast object bound to the result image of every GPU): the rows are
  * stored with multimem.st and the NVSwitch delivers them to all GPUs,
  * the caller's included. */
-int pf_b200_dev_ace_scale_multicast(const double *d_scores, const double *d_minmax,
-		int width, int nb_rows, uint32_t *d_multicast_band, void *stream);
+int pf_b200_dev_ace_scale_multicast(const uint32_t *d_band, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, const uint32_t *d_sample_px, int nb_samples,
+		double slope, double limit,
+		void *d_scores, double *d_minmax,
+		uint32_t *d_multicast_band, void *stream);
 
-/* The five passes above for one whole page on one GPU, with one caller-owned
+/* The passes above for one whole page on one GPU, with one caller-owned
  * work area of pf_b200_ace_workspace_bytes(width, height) bytes (the score
- * planes, 24 bytes per pixel, and the min/max block; 256-byte aligned).
+ * block, 16 bytes per pixel, and the min/max block; 256-byte aligned).
  * upstream _ace.c: pf_ace on a page resident in HBM. */
 size_t pf_b200_ace_workspace_bytes(int width, int height);
 int pf_b200_dev_ace(const uint32_t *d_in, uint32_t *d_out, int width, int height,
@@ -323,6 +344,8 @@ int pf_b200_dev_ace(const uint32_t *d_in, uint32_t *d_out, int width, int height
 /* Measures the FP64 FMA rate of the current device (the ACE roofline
  * denominator): returns TFLOP/s (FMA = 2 flops), or a negative PF_B200_E*. */
 double pf_b200_fp64_peak_tflops(void);
+/* The same for FP32 (the pipe the ACE accumulation pass runs on). */
+double pf_b200_fp32_peak_tflops(void);
 
 #ifdef __cplusplus
 }

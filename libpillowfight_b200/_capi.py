@@ -94,27 +94,40 @@ SIGNATURES = {
     "pf_b200_dev_sobel_batch": (ctypes.c_int, [_u32p, _u32p, ctypes.c_int, ctypes.c_int,
                                                ctypes.c_int, _vp]),
     "pf_b200_ace_minmax_bytes": (ctypes.c_size_t, [ctypes.c_int, ctypes.c_int]),
+    "pf_b200_ace_scores_bytes": (ctypes.c_size_t, [ctypes.c_int, ctypes.c_int]),
     "pf_b200_dev_ace_minmax_init": (ctypes.c_int, [_vp, ctypes.c_int, ctypes.c_int, _vp]),
+    # (d_in, w, h, row_begin, row_end, d_samples, n, slope, limit, d_scores, d_minmax[, d_out], stream)
     "pf_b200_dev_ace_scores": (ctypes.c_int, [_u32p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                               ctypes.c_int, _vp, ctypes.c_int, ctypes.c_double,
                                               ctypes.c_double, _vp, _vp, _vp]),
     "pf_b200_dev_ace_refine": (ctypes.c_int, [_u32p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                               ctypes.c_int, _vp, ctypes.c_int, ctypes.c_double,
                                               ctypes.c_double, _vp, _vp, _vp]),
-    "pf_b200_dev_ace_scale": (ctypes.c_int, [_vp, _vp, ctypes.c_int, ctypes.c_int, _u32p, _vp]),
+    "pf_b200_dev_ace_scale": (ctypes.c_int, [_u32p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                             ctypes.c_int, _vp, ctypes.c_int, ctypes.c_double,
+                                             ctypes.c_double, _vp, _vp, _u32p, _vp]),
+    # (d_band, w, h, row_begin, row_end, d_samples, d_sample_px, n, slope, limit, d_scores, d_minmax, ...)
     "pf_b200_dev_ace_scores_band": (ctypes.c_int, [_u32p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                                    ctypes.c_int, _vp, _vp, ctypes.c_int, ctypes.c_double,
                                                    ctypes.c_double, _vp, _vp, _vp]),
     "pf_b200_dev_ace_refine_band": (ctypes.c_int, [_u32p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                                    ctypes.c_int, _vp, _vp, ctypes.c_int, ctypes.c_double,
                                                    ctypes.c_double, _vp, _vp, _vp]),
-    "pf_b200_dev_ace_scale_to": (ctypes.c_int, [_vp, _vp, ctypes.c_int, ctypes.c_int,
+    "pf_b200_dev_ace_scale_band": (ctypes.c_int, [_u32p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                                  ctypes.c_int, _vp, _vp, ctypes.c_int, ctypes.c_double,
+                                                  ctypes.c_double, _vp, _vp, _u32p, _vp]),
+    "pf_b200_dev_ace_scale_to": (ctypes.c_int, [_u32p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                                ctypes.c_int, _vp, _vp, ctypes.c_int, ctypes.c_double,
+                                                ctypes.c_double, _vp, _vp,
                                                 ctypes.POINTER(ctypes.c_void_p), ctypes.c_int, _vp]),
-    "pf_b200_dev_ace_scale_multicast": (ctypes.c_int, [_vp, _vp, ctypes.c_int, ctypes.c_int, _vp, _vp]),
+    "pf_b200_dev_ace_scale_multicast": (ctypes.c_int, [_u32p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                                       ctypes.c_int, _vp, _vp, ctypes.c_int, ctypes.c_double,
+                                                       ctypes.c_double, _vp, _vp, _vp, _vp]),
     "pf_b200_ace_workspace_bytes": (ctypes.c_size_t, [ctypes.c_int, ctypes.c_int]),
     "pf_b200_dev_ace": (ctypes.c_int, [_u32p, _u32p, ctypes.c_int, ctypes.c_int, _vp, ctypes.c_int,
                                        ctypes.c_double, ctypes.c_double, _vp, ctypes.c_size_t, _vp]),
     "pf_b200_fp64_peak_tflops": (ctypes.c_double, []),
+    "pf_b200_fp32_peak_tflops": (ctypes.c_double, []),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

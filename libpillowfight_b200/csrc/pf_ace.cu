@@ -6,25 +6,44 @@
 //     score[c] += saturate(slope * (p[c] - sample_k[c]), +-limit) / dist(p, k)
 //     denom    += limit / dist(p, k)
 // then score[c] /= denom, a page-wide min/max per channel, and a linear
-// rescale to 0..255.
+// rescale to 0..255 that truncates.
 //
-// B200 formulation.  With w_k = 1/dist and L = limit/slope,
-//     score[c] = (slope/limit) * sum_k w_k * clamp(p[c]-s_k[c], -L, L) / sum_k w_k
-// so a common factor on w cancels.  The N samples are one table for the whole
-// page: a block gathers the sample pixels once into shared memory, and the
-// inner loop has no global loads at all.  Per pixel-sample pair the FP64 pipe
-// does: d^2 (1 add), three accumulating FMAs and one for the denominator (4);
-// the weight is MUFU.RSQ64H's 1/sqrt (optionally one Newton step, 3 more).
-// The clamp is one integer instruction (VIADDMNMX.RELU), and its result
-// u = c + L is used as it stands as the high word of a subnormal double
-// (u * 2^-1042, exact and linear in u), so neither a conversion nor a shuffle
-// is issued in the loop and the sums carry no bias: a pixel whose difference
-// to every sample is 0, +L or -L scores exactly 0, 1, -1 as in the reference.
-// Samples whose skip circle contains the whole tile are dropped per tile,
-// those that cannot reach it skip the test.
+// B200 formulation: a fast pass whose error is BOUNDED, and an exact pass for
+// the few pixels where that error could matter.  The result is the reference's
+// for every pixel, by construction rather than by measurement.
+//
+//  1. ace_scores_kernel (all but a few per cent of the time).  With
+//     w_k = 1/dist and u_k = clamp((p - s_k) * slope / (2 limit) + 1/2, 0, 1),
+//         score = 2 * sum_k w_k u_k / sum_k w_k - 1.
+//     Everything is FP32: d^2 is one FADD2 (two rows at a time), the weight one
+//     MUFU.RSQ (2^-22.9), the clamp ONE saturating FMA per channel
+//     (FFMA.SAT: p * inv + (1/2 - s_k * inv)), the sums FFMA2 over row pairs,
+//     flushed every 16 samples into a second set of accumulators (two-level
+//     summation).  The N samples are one table for the whole page: a block
+//     stages them in shared memory per tile and the loop touches no global
+//     memory.  Samples whose skip circle contains the tile are dropped per
+//     tile, those that cannot reach it skip the test.  A worst-case bound
+//     eps on |score - reference score| follows from the operation counts
+//     (ace_score_eps below).
+//     Ties -- a pixel whose difference to every sample saturates high, is
+//     zero, or saturates low scores exactly 1, 0, -1 in the reference; flat
+//     areas of a page are millions of such pixels -- are recognised by exact
+//     integer comparisons against the tile's sample extremes, not by the sums.
+//  2. ace_refine_kernel: the page extremes exactly.  Every score within
+//     2 eps of the approximate minimum or maximum is recomputed in the
+//     reference's own arithmetic (IEEE sqrt and divide, sample order) and the
+//     extremes are taken over those values.
+//  3. ace_scale_kernel: 255 (s - min) / (max - min) in FP32 with the exact
+//     extremes.  A value farther from an integer than the bound allows is
+//     truncated as it stands; the others (a fraction of a per cent) go on a
+//     list.
+//  4. ace_fixup_kernel: the listed pixels in the reference's own arithmetic,
+//     score and rescale.
 #include <cfloat>
 #include <cmath>
 #include <cstdlib>
+
+#include <cooperative_groups.h>
 
 #include "pf_common.cuh"
 
@@ -33,76 +52,72 @@ namespace pfb {
 namespace {
 
 constexpr int kAceBlock = 128;      // threads = columns per block
-constexpr int kMaxRowsPerThread = 8; // P: pixels a thread carries (same column), 2 / 4 / 8
-#ifndef PF_ACE_UNROLL
-#define PF_ACE_UNROLL 4
-#endif
-constexpr int kAceUnroll = PF_ACE_UNROLL;   // unroll of the sample loop
+constexpr int kRows = 8;            // pixels a thread carries (same column)
+constexpr int kTileRows = 16;       // rows a block walks; tiles sit on a page-wide grid of this pitch
 constexpr int kChunk = 512;         // samples staged in shared memory at a time
+constexpr int kFlush = 16;          // samples between flushes of the first-level sums
 // The min/max block of a call: [0..2] min, [3..5] max of the scores as the
-// accumulation kernel computed them; [6..8], [9..11] the same over the scores
-// ace_refine_kernel recomputed; then 6 doubles per tile of the page-wide grid.
-constexpr int kMinmaxHead = 12;
-// A score within this fraction of the page's range of its minimum or maximum
-// is recomputed in the reference's own arithmetic.  The accumulation kernel's
-// weights are good to 2^-19, which bounds its error at 2^-18 of the range
-// (measured: 3e-7 on a range of 1.4, tests/test_gpu_parity.py).
-constexpr double kNearEps = 0x1p-15;
-// Squared distances are carried scaled by 2^-1000, so the weights come out of
-// the rsqrt unit scaled by 2^500: the clamp result u = c + L becomes the high
-// word of a SUBNORMAL double (value u * 2^-1042, linear in u with no implicit
-// leading one), and weight * value must land in the normal range.
-// The common factors cancel in the score.
-constexpr double kD2Scale = 0x1p-1000;
+// accumulation kernel computed them; [6..8], [9..11] the exact extremes
+// (ace_refine_kernel), [12..14], [15..17] the extremes of its FP64 candidate
+// scores; then 6 doubles per tile of the page-wide grid.
+constexpr int kMinmaxHead = 18;
 
 struct SampleEntry {
-	int sx;
-	uint32_t bias[3];   // L - s_c (fast path) or s_c (table path) per channel
+	float sx;
+	float b[3];         // 1/2 - s_c * inv per channel
 };
 
 struct AceShared {
-	SampleEntry tbl[kChunk];                    // reordered: far samples, then straddling
-	double dy2[kChunk * kMaxRowsPerThread];     // [sample][row of the group], stride P
-	int sy[kChunk];
-	double lut[511];                            // general path only
-	int n_far, n_str;
+	SampleEntry tbl[kChunk + 4];      // far samples, padded to a multiple of 4 with weightless entries, then straddling ones
+	float dy2[(kChunk + 4) * kRows];  // [sample][row of the group]
+	int sy[kChunk + 4];
+	int sxi[kChunk + 4];              // straddling samples are tested in integers
+	int n_far4, n_str;
+	int smin[3], smax[3];             // channel extremes over the samples staged for this tile (ties)
 };
 
-__device__ __forceinline__ double rsqrt_approx(double x)
+__device__ __forceinline__ float rsqrt_f32(float x)
 {
-	double y;
-	asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+	// every argument is a normal number or +inf, so .ftz changes no result; it
+	// only spares the subnormal-input wrapper (FSETP + 2 FMUL) per rsqrt
+	float y;
+	asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
 	return y;
 }
 
-// 2/sqrt(d2) to ~2^-43 (NEWTON) or 1/sqrt(d2) to ~2^-20 relative; a common
-// factor on the weights cancels in the score.  MUFU.RSQ64H reads and writes
-// only the high word of a double; without the Newton step the low word is
-// left as it is (d2's own low word, at most 2^-20 of the value) rather than
-// zeroed with an extra instruction -- the same order as the unit's own error,
-// and the same weight feeds numerator and denominator.
-template <bool NEWTON>
-__device__ __forceinline__ double weight_of(double d2)
+__device__ __forceinline__ float fma_sat(float a, float b, float c)
 {
-	const double y0 = rsqrt_approx(d2);
-	if (!NEWTON)
-		return __hiloint2double(__double2hiint(y0), __double2loint(d2));
-	const double t = d2 * y0;
-	const double q = fma(-t, y0, 3.0);
-	return y0 * q;
+	float d;
+	asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+	return d;
 }
 
-// 1/d to an ulp or two: the unit's 2^-20 estimate and two Newton steps.  The
-// quotients that must be exact (the ties) are decided by comparisons, not by
-// this; 0 gives NaN, which the caller replaces.
-__device__ __forceinline__ double reciprocal(double d)
+typedef unsigned long long f32x2;     // two floats in a 64-bit register pair
+
+__device__ __forceinline__ f32x2 pack2(float lo, float hi)
 {
-	double y;
-	asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
-	double e = fma(-d, y, 1.0);
-	y = fma(y, e, y);
-	e = fma(-d, y, 1.0);
-	return fma(y, e, y);
+	f32x2 r;
+	asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+	return r;
+}
+
+__device__ __forceinline__ void unpack2(f32x2 v, float &lo, float &hi)
+{
+	asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+
+__device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c)
+{
+	f32x2 d;
+	asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+	return d;
+}
+
+__device__ __forceinline__ f32x2 fadd2(f32x2 a, f32x2 b)
+{
+	f32x2 d;
+	asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+	return d;
 }
 
 __device__ __forceinline__ void atomic_min_double(double *addr, double v)
@@ -131,11 +146,11 @@ __device__ __forceinline__ void atomic_max_double(double *addr, double v)
 	}
 }
 
-// The exactly tied scores the reference produces (ace_scores_kernel: a pixel whose difference
-// to every sample is zero or saturates).
-__device__ __forceinline__ bool is_tie_score(double s)
+// In the score planes exactly 0, 1 and -1 mean "tie": the reference's score is
+// exactly that (ace_scores_kernel moves an approximate score off these values).
+__device__ __forceinline__ bool is_tie_score(float s)
 {
-	return s == 0.0 || s == 1.0 || s == -1.0;
+	return s == 0.0f || s == 1.0f || s == -1.0f;
 }
 
 struct AceConst {
@@ -143,18 +158,15 @@ struct AceConst {
 	int row_begin, row_end;
 	int nb_samples;
 	int too_close2;        // (h/5)^2: pairs with d^2 below this are skipped
-	int clamp_l;           // L = limit/slope when it is an integer <= 127 (fast path)
-	int tile_rows;         // rows a block walks; tiles sit on a page-wide grid of this pitch
-	int score_row0;        // score row stored first in `scores`
-	long score_plane;      // doubles between the R, G, B score planes
+	int dsat;              // smallest difference whose saturation reaches the limit (256: none does)
+	int score_row0;        // score row stored first in the planes
+	long score_plane;      // floats between the R, G, B score planes
 	const uint32_t *sample_px;   // samples' pixel values, or NULL: read them from the page
 	double slope, limit;
+	float inv;             // slope / (2 limit), rounded up a little (ace_setup)
+	float eps;             // bound on |approximate score - reference score| (ace_score_eps)
 };
 
-// Stages one chunk of the sample table for this block's tile.  Samples are
-// classified against the tile rectangle: "far" ones can never be skipped,
-// "inside" ones always are (dropped here), the rest straddle the skip circle.
-// Order inside each class is the sample order, so sums are reproducible.
 // 1 = far (never skipped on this tile), 2 = straddles the skip circle, 0 = inside
 __device__ __forceinline__ int classify_sample(int sx, int sy, int x_lo, int x_hi,
 		int y_lo, int y_hi, int too_close2)
@@ -168,7 +180,12 @@ __device__ __forceinline__ int classify_sample(int sx, int sy, int x_lo, int x_h
 	return (dxM * dxM + dyM * dyM >= too_close2) ? 2 : 0;
 }
 
-template <bool FAST>
+constexpr int kNoSample = 1 << 30;     // sy of a padding entry: its dy^2 is +inf, its weight 0
+
+// Stages one chunk of the sample table for this block's tile.  Samples are
+// classified against the tile rectangle: "far" ones can never be skipped,
+// "inside" ones always are (dropped here), the rest straddle the skip circle.
+// Also folds the staged samples' channel extremes into sh.smin / sh.smax.
 __device__ __noinline__ void stage_samples(AceShared &sh, const AceConst &cs,
 		const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
 		int k0, int kn, int x_lo, int x_hi, int y_lo, int y_hi)
@@ -198,9 +215,10 @@ __device__ __noinline__ void stage_samples(AceShared &sh, const AceConst &cs,
 	int n_far = 0;
 	for (int i = 0; i < passes * kWarps; i++)
 		n_far += counts[0][i][0];
-	// sweep 2: ordered compaction -- far samples first, then straddling, each
-	// class in sample order, so sums are reproducible
-	int off_far = 0, off_str = n_far;
+	const int n_far4 = (n_far + 3) & ~3;
+	// sweep 2: ordered compaction -- far samples first, then straddling
+	int off_far = 0, off_str = n_far4;
+	int mn[3] = { 255, 255, 255 }, mx[3] = { 0, 0, 0 };
 	for (int p = 0; p < passes; p++) {
 		for (int wv = 0; wv < warp; wv++) {
 			off_far += counts[p][wv][0];
@@ -221,12 +239,16 @@ __device__ __noinline__ void stage_samples(AceShared &sh, const AceConst &cs,
 			                           : off_str + __popc(ms & below);
 			const uint32_t px = cs.sample_px ? __ldg(cs.sample_px + k0 + k)
 			                                 : __ldg(in + (size_t)s.y * cs.w + s.x);
-			sh.tbl[dst].sx = s.x;
+			sh.tbl[dst].sx = (float)s.x;
+			sh.sxi[dst] = s.x;
 			sh.sy[dst] = s.y;
 #pragma unroll
 			for (int c = 0; c < 3; c++) {
-				const uint32_t v = (px >> (8 * c)) & 0xFF;
-				sh.tbl[dst].bias[c] = FAST ? (uint32_t)(cs.clamp_l - (int)v) : v;
+				const int v = (int)((px >> (8 * c)) & 0xFF);
+				// (in double: the rounding of b must stay below 2^-26, ace_score_eps)
+				sh.tbl[dst].b[c] = (float)(0.5 - (double)v * (double)cs.inv);
+				mn[c] = min(mn[c], v);
+				mx[c] = max(mx[c], v);
 			}
 		}
 		for (int wv = warp; wv < kWarps; wv++) {
@@ -234,192 +256,221 @@ __device__ __noinline__ void stage_samples(AceShared &sh, const AceConst &cs,
 			off_str += counts[p][wv][1];
 		}
 	}
+	// padding between the two classes: entries without weight
+	if ((int)threadIdx.x < n_far4 - n_far) {
+		const int dst = n_far + threadIdx.x;
+		sh.tbl[dst].sx = 0.f;
+		sh.sxi[dst] = 0;
+		sh.sy[dst] = kNoSample;
+#pragma unroll
+		for (int c = 0; c < 3; c++)
+			sh.tbl[dst].b[c] = 0.f;
+	}
+#pragma unroll
+	for (int c = 0; c < 3; c++) {
+		if (mn[c] <= mx[c]) {
+			atomicMin(&sh.smin[c], mn[c]);
+			atomicMax(&sh.smax[c], mx[c]);
+		}
+	}
 	if (threadIdx.x == kAceBlock - 1) {     // last thread: offsets are the totals
-		sh.n_far = n_far;
-		sh.n_str = off_str - n_far;
+		sh.n_far4 = n_far4;
+		sh.n_str = off_str - n_far4;
 	}
 	__syncthreads();
 }
 
-// One sample against the P pixels of a thread.  TEST: the sample straddles the
-// skip circle on this tile, so each pair is tested (weight forced to 0).
-template <bool FAST, bool NEWTON, bool TEST, int P>
-__device__ __forceinline__ void accumulate_sample(const AceShared &sh, int j, int x,
-		const uint32_t (&pix)[P], const uint32_t (&pv)[P][3],
-		int two_l, double too_close2, double top_value,
-		double (&acc)[P][3], double (&top)[P])
+// One sample against the kRows pixels of a thread (row pairs in f32x2
+// registers).  TEST: the sample straddles the skip circle on this tile, so
+// each pair is tested (exactly, in integers) and a skipped one gets weight 0.
+template <bool TEST>
+__device__ __forceinline__ void accumulate_sample(const AceShared &sh, int j, float fx, int x, int y0,
+		int too_close2, const float (&pv)[kRows][3], float inv, f32x2 (&acc)[kRows / 2][4])
 {
 	const SampleEntry se = sh.tbl[j];
-	const int dx = x - se.sx;
-	const double dx2 = (double)(dx * dx) * kD2Scale;
-	double wgt[P];
-#pragma unroll
-	for (int r = 0; r < P; r++) {
-		const double d2 = dx2 + sh.dy2[j * P + r];
-		double wv = weight_of<NEWTON>(d2);
-		if (TEST && d2 < too_close2)
-			wv = 0.0;
-		wgt[r] = wv;
-		// the channel that saturates high on every sample (u = 2L): same FMA
-		// sequence as acc[], so the ties the reference produces come out
-		// exactly: acc == top (saturated high everywhere), acc == top / 2
-		// (difference 0 everywhere: scaling every term by two commutes
-		// with every rounding) and acc == 0 (saturated low everywhere)
-		top[r] = fma(wv, top_value, top[r]);
+	const float dx = fx - se.sx;
+	const float dx2 = dx * dx;
+	const f32x2 dx22 = pack2(dx2, dx2);
+	int dxi2 = 0, dy0 = 0;
+	if (TEST) {
+		const int dxi = x - sh.sxi[j];
+		dxi2 = dxi * dxi;
+		dy0 = y0 - sh.sy[j];
 	}
-	if (FAST) {
 #pragma unroll
-		for (int r = 0; r < P; r++) {
-#pragma unroll
-			for (int c = 0; c < 3; c++) {
-				// clamp(p - s, -L, L) + L = max(min(p + (L - s), 2L), 0) is ONE
-				// instruction, VIADDMNMX.RELU, and its result IS the high word
-				// of the subnormal double u * 2^-1042: no conversion, no shuffle
-				const int u = __viaddmin_s32_relu((int)pv[r][c], (int)se.bias[c], two_l);
-				acc[r][c] = fma(wgt[r], __hiloint2double(u, 0), acc[r][c]);
-			}
+	for (int r = 0; r < kRows / 2; r++) {
+		const f32x2 dy22 = *reinterpret_cast<const f32x2 *>(&sh.dy2[j * kRows + 2 * r]);
+		float da, db;
+		unpack2(fadd2(dx22, dy22), da, db);
+		float wa = rsqrt_f32(da), wb = rsqrt_f32(db);
+		if (TEST) {
+			const int dya = dy0 + 2 * r, dyb = dya + 1;
+			if (dxi2 + dya * dya < too_close2)
+				wa = 0.f;
+			if (dxi2 + dyb * dyb < too_close2)
+				wb = 0.f;
 		}
-	} else {
+		const f32x2 wv = pack2(wa, wb);
+		acc[r][3] = fadd2(acc[r][3], wv);
 #pragma unroll
-		for (int r = 0; r < P; r++) {
-#pragma unroll
-			for (int c = 0; c < 3; c++) {
-				const int v = (pix[r] >> (8 * c)) & 0xFF;
-				acc[r][c] = fma(wgt[r], sh.lut[v - (int)se.bias[c] + 255], acc[r][c]);
-			}
-		}
+		for (int c = 0; c < 3; c++)
+			acc[r][c] = ffma2(wv, pack2(fma_sat(pv[2 * r][c], inv, se.b[c]),
+					fma_sat(pv[2 * r + 1][c], inv, se.b[c])), acc[r][c]);
 	}
 }
 
-// The accumulation pass.  Thread = one column, kRowsPerThread rows at a time.
-// FAST: L = limit/slope is an integer <= 127, clamp on the integer pipe.
-// !FAST: any slope/limit, saturation values read from a 511-entry table.
-#ifndef PF_ACE_MINBLOCKS_P8
-#define PF_ACE_MINBLOCKS_P8 3
-#endif
-template <bool FAST, bool NEWTON, int P>
-__global__ void __launch_bounds__(kAceBlock, (P == 2) ? 8 : ((P == 4) ? 6 : ((P == 6) ? 4 : PF_ACE_MINBLOCKS_P8)))
+__device__ __forceinline__ void zero_sums(f32x2 (&a)[kRows / 2][4])
+{
+#pragma unroll
+	for (int r = 0; r < kRows / 2; r++)
+#pragma unroll
+		for (int c = 0; c < 4; c++)
+			a[r][c] = 0ull;
+}
+
+__device__ __forceinline__ void flush_sums(f32x2 (&total)[kRows / 2][4], const f32x2 (&part)[kRows / 2][4])
+{
+#pragma unroll
+	for (int r = 0; r < kRows / 2; r++)
+#pragma unroll
+		for (int c = 0; c < 4; c++)
+			total[r][c] = fadd2(total[r][c], part[r][c]);
+}
+
+// The accumulation pass.  Thread = one column, kRows rows at a time; block =
+// one tile of 128 columns x kTileRows rows of a page-wide grid (so that a band
+// split across GPUs classifies and sums exactly like the whole page).
+__global__ void __launch_bounds__(kAceBlock, 4)
 ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
-		const AceConst cs, double *__restrict__ scores, double *__restrict__ minmax)
+		const AceConst cs, float *__restrict__ scores, int *__restrict__ fix_counts,
+		double *__restrict__ minmax)
 {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	AceShared &sh = *reinterpret_cast<AceShared *>(smem_raw);
 	pdl_wait();
 	const int x = blockIdx.x * kAceBlock + threadIdx.x;
 	const int xc = min(x, cs.w - 1);
-	// Tiles sit on a page-wide grid of tile_rows rows whatever the band is, so
-	// a band split (multi-GPU) classifies and sums exactly like the whole page.
-	const int tile_y0 = (cs.row_begin / cs.tile_rows + blockIdx.y) * cs.tile_rows;
-	const int tile_y1 = min(cs.h, tile_y0 + cs.tile_rows);      // exclusive
+	const int tile_y0 = (cs.row_begin / kTileRows + blockIdx.y) * kTileRows;
+	const int tile_y1 = min(cs.h, tile_y0 + kTileRows);      // exclusive
 	const int x_lo = blockIdx.x * kAceBlock;
 	const int x_hi = min(cs.w - 1, x_lo + kAceBlock - 1);
 	const size_t plane = (size_t)cs.score_plane;
+	const float fx = (float)x;
+	const float inv = cs.inv;
 
-	if (!FAST) {
-		for (int i = threadIdx.x; i < 511; i += kAceBlock) {
-			// the reference's calc_saturation on the integer difference i-255
-			double v = (double)(i - 255) * cs.slope;
-			if (v > cs.limit)
-				v = cs.limit;
-			else if (v < -cs.limit)
-				v = -cs.limit;
-			sh.lut[i] = v;
-		}
+	// the fix-up lists of this score block start empty (ace_scale_kernel fills them)
+	if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x < 2 * kAceFixupSlots)
+		fix_counts[threadIdx.x] = 0;      // list lengths, then the fix-up pass's tickets
+	if (threadIdx.x < 3) {
+		sh.smin[threadIdx.x] = 255;
+		sh.smax[threadIdx.x] = 0;
 	}
 
-	const int two_l = 2 * cs.clamp_l;
-	const double too_close2 = (double)cs.too_close2 * kD2Scale;
-	// what a channel saturated high contributes per unit weight
-	const double top_value = FAST ? __hiloint2double(two_l, 0) : cs.limit;
-
-	double mn[3] = { DBL_MAX, DBL_MAX, DBL_MAX };
-	double mx[3] = { -DBL_MAX, -DBL_MAX, -DBL_MAX };
+	float mn[3] = { FLT_MAX, FLT_MAX, FLT_MAX };
+	float mx[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
 
 	bool staged = false;
-	for (int y0 = tile_y0; y0 < tile_y1; y0 += P) {
-		if (y0 + P <= cs.row_begin || y0 >= cs.row_end)
+	for (int y0 = tile_y0; y0 < tile_y1; y0 += kRows) {
+		if (y0 + kRows <= cs.row_begin || y0 >= cs.row_end)
 			continue;       // row group outside this band (block-uniform)
-		// pixel values of this thread's P rows; rows of the group outside the band
+		// pixel values of this thread's rows; rows of the group outside the band
 		// repeat the nearest one inside (their scores are not stored), so only
 		// the band's own rows of `in` are ever read
-		uint32_t pix[P];
+		float pv[kRows][3];
 #pragma unroll
-		for (int r = 0; r < P; r++)
-			pix[r] = __ldg(in + (size_t)min(max(y0 + r, cs.row_begin), cs.row_end - 1) * cs.w + xc);
-		// one channel value per register (the clamp instruction wants them so)
-		uint32_t pv[P][3];
-#pragma unroll
-		for (int r = 0; r < P; r++)
+		for (int r = 0; r < kRows; r++) {
+			const uint32_t pix = __ldg(in + (size_t)min(max(y0 + r, cs.row_begin), cs.row_end - 1) * cs.w + xc);
 #pragma unroll
 			for (int c = 0; c < 3; c++)
-				pv[r][c] = (pix[r] >> (8 * c)) & 0xFF;
-
-		double acc[P][3], top[P];
-#pragma unroll
-		for (int r = 0; r < P; r++) {
-			top[r] = 0.0;
-#pragma unroll
-			for (int c = 0; c < 3; c++)
-				acc[r][c] = 0.0;
+				pv[r][c] = (float)((pix >> (8 * c)) & 0xFF);
 		}
+
+		f32x2 total[kRows / 2][4], part[kRows / 2][4];
+		zero_sums(total);
 
 		for (int k0 = 0; k0 < cs.nb_samples; k0 += kChunk) {
 			const int kn = min(kChunk, cs.nb_samples - k0);
 			// (re)stage when the chunk or the tile changes; with one chunk the
 			// table is staged once per tile
 			if (!staged || cs.nb_samples > kChunk) {
-				staged = true;
 				__syncthreads();
-				stage_samples<FAST>(sh, cs, in, samples_xy, k0, kn,
-						x_lo, x_hi, tile_y0, tile_y1 - 1);
+				staged = true;
+				stage_samples(sh, cs, in, samples_xy, k0, kn, x_lo, x_hi, tile_y0, tile_y1 - 1);
 			}
-			const int n_act = sh.n_far + sh.n_str;
+			const int n_far4 = sh.n_far4;
+			const int n_act = n_far4 + sh.n_str;
 			__syncthreads();
 			for (int j = threadIdx.x; j < n_act; j += kAceBlock) {
+				const int sy = sh.sy[j];
 #pragma unroll
-				for (int r = 0; r < P; r++) {
-					const int dy = y0 + r - sh.sy[j];
-					sh.dy2[j * P + r] = (double)(dy * dy) * kD2Scale;
+				for (int r = 0; r < kRows; r++) {
+					const float dy = (float)(y0 + r - sy);
+					sh.dy2[j * kRows + r] = (sy == kNoSample) ? __int_as_float(0x7f800000) : dy * dy;
 				}
 			}
 			__syncthreads();
 
-			const int n_far = sh.n_far;
-#pragma unroll kAceUnroll
-			for (int j = 0; j < n_far; j++)
-				accumulate_sample<FAST, NEWTON, false, P>(sh, j, x, pix, pv, two_l,
-						too_close2, top_value, acc, top);
-			for (int j = n_far; j < n_act; j++)
-				accumulate_sample<FAST, NEWTON, true, P>(sh, j, x, pix, pv, two_l,
-						too_close2, top_value, acc, top);
+			for (int j0 = 0; j0 < n_far4; j0 += kFlush) {
+				zero_sums(part);
+				const int j1 = min(n_far4, j0 + kFlush);
+				for (int j = j0; j < j1; j += 4) {
+#pragma unroll
+					for (int u = 0; u < 4; u++)
+						accumulate_sample<false>(sh, j + u, fx, x, y0, cs.too_close2, pv, inv, part);
+				}
+				flush_sums(total, part);
+			}
+			for (int j0 = n_far4; j0 < n_act; j0 += kFlush) {
+				zero_sums(part);
+				const int j1 = min(n_act, j0 + kFlush);
+				for (int j = j0; j < j1; j++)
+					accumulate_sample<true>(sh, j, fx, x, y0, cs.too_close2, pv, inv, part);
+				flush_sums(total, part);
+			}
 		}
 
-		// score = sum(sat/dist) / sum(limit/dist).  `top` is the numerator of a
-		// channel saturated high on every sample, i.e. limit * sum(1/dist) up
-		// to the common factor, accumulated by the same FMA sequence as acc.
-		// The reference gets exactly 1, 0 and -1 for a pixel whose difference
-		// to every sample saturates high, is zero, saturates low (flat page
-		// areas: large sets of tied scores, also at the extremes the rescale
-		// normalises with); the comparisons below reproduce those ties.
+		// score = 2 * sum(w u) / sum(w) - 1.  Ties first, by exact integer tests
+		// against the extremes of the tile's staged samples (a superset of the
+		// samples that count for this pixel: a tie that only holds for the
+		// subset is not claimed and takes the ordinary route).
+		const int smin[3] = { sh.smin[0], sh.smin[1], sh.smin[2] };
+		const int smax[3] = { sh.smax[0], sh.smax[1], sh.smax[2] };
 #pragma unroll
-		for (int r = 0; r < P; r++) {
+		for (int r = 0; r < kRows; r++) {
 			const int y = y0 + r;
 			if (y >= cs.row_begin && y < cs.row_end && y < tile_y1 && x < cs.w) {
 				const size_t o = (size_t)(y - cs.score_row0) * cs.w + x;
-				// FAST: acc holds sum(w (c + L)); c / L = (acc - top/2) / (top/2)
-				// Every sample skipped (top == 0): the reference divides 0 by 0.
-				// Here reciprocal(0) is NaN and so is the product below; only
-				// the tie comparisons (0 == 0) have to be kept from firing.
-				const bool live = top[r] > 0.0;
-				const double den = FAST ? 0.5 * top[r] : top[r];
-				const double inv = reciprocal(den);
+				float a[4], lo, hi;
+#pragma unroll
+				for (int c = 0; c < 4; c++) {
+					unpack2(total[r / 2][c], lo, hi);
+					a[c] = (r & 1) ? hi : lo;
+				}
+				// no sample counts for this pixel: the reference divides 0 by 0; a
+				// sample AT the pixel (pages of fewer than 5 rows skip nothing)
+				// makes its sums infinite or NaN, and its score NaN
+				const bool live = a[3] > 0.f && a[3] <= FLT_MAX;
+				const float den = 0.5f * a[3];
+				const float rden = __frcp_rn(den);
+				// (the pixel again, from L1/L2: not kept in registers across the loop)
+				const uint32_t pix = __ldg(in + (size_t)y * cs.w + x);
 #pragma unroll
 				for (int c = 0; c < 3; c++) {
-					const double num = FAST ? acc[r][c] - den : acc[r][c];
-					const bool tie_hi = live && num == den, tie_lo = live && num == -den;
-					double s = num * inv;           // exactly 0 when num is
-					s = tie_hi ? 1.0 : s;
-					s = tie_lo ? -1.0 : s;
+					const int p = (int)((pix >> (8 * c)) & 0xFF);
+					float s = (a[c] - den) * rden;
+					// keep approximate scores off the values that mean "tie"
+					if (s == 0.f)
+						s = 1e-30f;
+					else if (fabsf(s) >= 1.f)
+						s = copysignf(0.99999994f, s);
+					if (p - smax[c] >= cs.dsat)
+						s = 1.f;
+					else if (p - smin[c] <= -cs.dsat)
+						s = -1.f;
+					else if (smin[c] == p && smax[c] == p)
+						s = 0.f;
+					if (!live)
+						s = __int_as_float(0x7fc00000);
 					scores[c * plane + o] = s;
 					if (s < mn[c]) mn[c] = s;     // NaN never enters
 					if (s > mx[c]) mx[c] = s;
@@ -429,13 +480,13 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 	}
 
 	// block-wide min / max, then 6 atomics per block
-	__shared__ double red[2][3][kAceBlock / 32];
+	__shared__ float red[2][3][kAceBlock / 32];
 #pragma unroll
 	for (int c = 0; c < 3; c++) {
 #pragma unroll
 		for (int d = 16; d > 0; d >>= 1) {
-			mn[c] = fmin(mn[c], __shfl_xor_sync(0xFFFFFFFFu, mn[c], d));
-			mx[c] = fmax(mx[c], __shfl_xor_sync(0xFFFFFFFFu, mx[c], d));
+			mn[c] = fminf(mn[c], __shfl_xor_sync(0xFFFFFFFFu, mn[c], d));
+			mx[c] = fmaxf(mx[c], __shfl_xor_sync(0xFFFFFFFFu, mx[c], d));
 		}
 		if ((threadIdx.x & 31) == 0) {
 			red[0][c][threadIdx.x >> 5] = mn[c];
@@ -445,19 +496,22 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 	__syncthreads();
 	if (threadIdx.x < 3) {
 		const int c = threadIdx.x;
-		double a = red[0][c][0], b = red[1][c][0];
+		float a = red[0][c][0], b = red[1][c][0];
 		for (int i = 1; i < kAceBlock / 32; i++) {
-			a = fmin(a, red[0][c][i]);
-			b = fmax(b, red[1][c][i]);
+			a = fminf(a, red[0][c][i]);
+			b = fmaxf(b, red[1][c][i]);
 		}
-		atomic_min_double(minmax + c, a);
-		atomic_max_double(minmax + 3 + c, b);
+		// FLT_MAX (nothing seen) becomes DBL_MAX, the block's initial value
+		const double da = a == FLT_MAX ? DBL_MAX : (double)a;
+		const double db = b == -FLT_MAX ? -DBL_MAX : (double)b;
+		atomic_min_double(minmax + c, da);
+		atomic_max_double(minmax + 3 + c, db);
 		// and per tile of the page-wide grid (two bands may share a tile), for
 		// ace_refine_kernel to find the tiles that matter
 		double *tile = minmax + kMinmaxHead
-			+ 6 * ((size_t)(cs.row_begin / cs.tile_rows + blockIdx.y) * gridDim.x + blockIdx.x);
-		atomic_min_double(tile + c, a);
-		atomic_max_double(tile + 3 + c, b);
+			+ 6 * ((size_t)(cs.row_begin / kTileRows + blockIdx.y) * gridDim.x + blockIdx.x);
+		atomic_min_double(tile + c, da);
+		atomic_max_double(tile + 3 + c, db);
 	}
 }
 
@@ -469,142 +523,172 @@ __global__ void ace_minmax_init_kernel(double *minmax, size_t n)
 		minmax[i] = (i % 6 < 3) ? DBL_MAX : -DBL_MAX;
 }
 
+// ---------------------------------------------------------------------------
+// The pixels the fast pass cannot decide: first in FP64 (error ~1e-14, a
+// thread per pixel), then, for the handful that even that leaves open, in the
+// reference's own arithmetic (a warp per pixel).
+// ---------------------------------------------------------------------------
+
+__device__ __forceinline__ double rsqrt_f64(double x)
+{
+	// MUFU.RSQ64H (2^-22) and two Newton steps: a relative error of a few 2^-53
+	double y;
+	asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+#pragma unroll
+	for (int i = 0; i < 2; i++) {
+		const double t = x * y;
+		y = y * fma(-0.5 * t, y, 1.5);
+	}
+	return y;
+}
+
+// Bound on |ace_accurate_score - reference score|.  Both approximate the same
+// real number: the reference with one rounding in the square root, one in each
+// division and one per addition, this with the weight's few 2^-53, one
+// rounding per FMA and one division; (4 N + 64) * 2^-53 covers both with room.
+__device__ __forceinline__ double ace_accurate_eps(int nb_samples)
+{
+	return (4.0 * nb_samples + 64.0) * 0x1p-53;
+}
+
+// The scores of one pixel in FP64, by one thread: weights 1/dist from the
+// reciprocal square root, saturation values exactly the reference's.
+__device__ __forceinline__ void ace_accurate_score(const uint32_t *__restrict__ in,
+		const int *__restrict__ samples_xy, const AceConst &cs, int x, int y, double (&s)[3])
+{
+	const uint32_t p = __ldg(in + (size_t)y * cs.w + x);
+	double acc[4] = { 0.0, 0.0, 0.0, 0.0 };
+#pragma unroll 2
+	for (int k = 0; k < cs.nb_samples; k++) {
+		const int2 sxy = __ldg(reinterpret_cast<const int2 *>(samples_xy) + k);
+		const int dx = x - sxy.x, dy = y - sxy.y;
+		const int d2 = dx * dx + dy * dy;
+		if (d2 < cs.too_close2)
+			continue;
+		const uint32_t sp = cs.sample_px ? __ldg(cs.sample_px + k) : __ldg(in + (size_t)sxy.y * cs.w + sxy.x);
+		const double wgt = rsqrt_f64((double)d2);      // d2 == 0 (pages under 5 rows): inf, the sums turn NaN as in the reference
+#pragma unroll
+		for (int c = 0; c < 3; c++) {
+			double v = __dmul_rn((double)((int)((p >> (8 * c)) & 0xFF) - (int)((sp >> (8 * c)) & 0xFF)), cs.slope);
+			v = v > cs.limit ? cs.limit : (v < -cs.limit ? -cs.limit : v);
+			acc[c] = fma(wgt, v, acc[c]);
+		}
+		acc[3] = fma(wgt, cs.limit, acc[3]);
+	}
+#pragma unroll
+	for (int c = 0; c < 3; c++)
+		s[c] = acc[c] / acc[3];
+}
+
+constexpr int kExactChunk = 64;      // samples whose terms a warp holds at a time
+
+// The scores of one pixel in the reference's own arithmetic, by one warp:
+// upstream _ace.c ace_thread_adjustment / oracle ace_adjust_rows operation for
+// operation -- IEEE sqrt and divide, terms added in sample order, a skipped
+// sample adding nothing (+0.0 changes no sum).  The lanes compute the terms of
+// 64 samples at a time (that is where the time goes), then lanes 0..3 add them
+// up in order: R, G, B and the denominator.  terms: this warp's shared area.
+// All lanes return the three scores.
+__device__ __forceinline__ void ace_exact_score_warp(double (*terms)[4],
+		const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
+		const AceConst &cs, int x, int y, double (&r)[3])
+{
+	const int lane = threadIdx.x & 31;
+	const uint32_t p = __ldg(in + (size_t)y * cs.w + x);
+	const double too_close = (double)(cs.h / 5);
+	double acc = 0.0;
+	for (int k0 = 0; k0 < cs.nb_samples; k0 += kExactChunk) {
+#pragma unroll
+		for (int half = 0; half < kExactChunk / 32; half++) {
+			const int j = lane + 32 * half, k = k0 + j;
+			double t[4] = { 0.0, 0.0, 0.0, 0.0 };
+			if (k < cs.nb_samples) {
+				const int2 sxy = __ldg(reinterpret_cast<const int2 *>(samples_xy) + k);
+				const uint32_t sp = cs.sample_px ? __ldg(cs.sample_px + k)
+				                                 : __ldg(in + (size_t)sxy.y * cs.w + sxy.x);
+				const double ddx = (double)(x - sxy.x), ddy = (double)(y - sxy.y);
+				const double dist = __dsqrt_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)));
+				if (!(dist < too_close)) {
+#pragma unroll
+					for (int c = 0; c < 4; c++) {
+						double v = __dmul_rn((double)((int)((p >> (8 * c)) & 0xFF) - (int)((sp >> (8 * c)) & 0xFF)), cs.slope);
+						if (v > cs.limit || c == 3)
+							v = cs.limit;
+						else if (v < -cs.limit)
+							v = -cs.limit;
+						t[c] = __ddiv_rn(v, dist);
+					}
+				}
+			}
+#pragma unroll
+			for (int c = 0; c < 4; c++)
+				terms[j][c] = t[c];
+		}
+		__syncwarp();
+		if (lane < 4) {
+			const int n = min(kExactChunk, cs.nb_samples - k0);
+#pragma unroll 8
+			for (int j = 0; j < n; j++)
+				acc = __dadd_rn(acc, terms[j][lane]);
+		}
+		__syncwarp();
+	}
+	const double denom = __shfl_sync(0xFFFFFFFFu, acc, 3);
+	const double q = __ddiv_rn(acc, denom);
+#pragma unroll
+	for (int c = 0; c < 3; c++)
+		r[c] = __shfl_sync(0xFFFFFFFFu, q, c);
+}
+
 constexpr int kRefineThreads = 256;
 constexpr int kRefineSlab = 16;      // rows scanned before the candidates are worked off
-constexpr int kRefineTerms = 512;    // (candidate, sample) pairs whose terms are in flight
-constexpr int kRefineTable = 1024;   // samples kept in shared memory
 
 struct RefineShared {
-	double terms[kRefineTerms][4];
-	int sx[kRefineTable], sy[kRefineTable];
-	uint32_t spx[kRefineTable];
+	double terms[kRefineThreads / 32][kExactChunk][4];
 	unsigned short cand[kRefineSlab * kAceBlock];
+	unsigned short todo[kRefineSlab * kAceBlock];
 	int wanted[kRefineThreads];
-	int n_wanted, n_cand;
+	int n_wanted, n_cand, n_todo;
 };
 
-// The terms one sample contributes to one pixel in the reference's own
-// arithmetic (upstream _ace.c, ace_thread_adjustment; oracle/pf_oracle.c
-// ace_adjust_rows): IEEE sqrt and divisions.  A skipped sample contributes
-// +0.0, which changes no sum.
-// (This code runs once or a few times per page, from a cold instruction
-// cache: one copy of it, loops not unrolled.)
-__device__ __forceinline__ void ace_exact_terms(const RefineShared &sh, bool table,
-		const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
-		const AceConst &cs, int x, int y, int k, double *t)
+// The page's extremes exactly.  The rescale divides by (max - min) and
+// truncates, so the extremes must be the reference's to the last bit.
+//   The exact minimum is the exact score of SOME pixel whose approximate score
+// lies within 2 eps of the approximate minimum: the candidates.  Phase 1
+// computes the candidates' scores in FP64 (ace_accurate_score, error e2) and
+// takes the extremes of those; the exact minimum then belongs to a candidate
+// whose FP64 score lies within 2 e2 of that FP64 minimum -- a handful of
+// pixels -- and phase 2 recomputes those in the reference's own arithmetic.
+// Tied scores (0, +-1 in the planes) are exact as they are and take part as
+// they stand.  The two phases are one cooperative launch with a grid barrier
+// between them; each scans the same tiles (a few: the tile table the
+// accumulation kernel left says which can hold a candidate).
+template <int PHASE>
+__device__ __forceinline__ void refine_scan(RefineShared &sh, const uint32_t *__restrict__ in,
+		const int *__restrict__ samples_xy, const AceConst &cs, const float *__restrict__ scores,
+		double *__restrict__ minmax, int tiles_x, int tiles_y)
 {
-	int sx, sy;
-	uint32_t sp;
-	if (table) {
-		sx = sh.sx[k];
-		sy = sh.sy[k];
-		sp = sh.spx[k];
-	} else {
-		const int2 sxy = __ldg(reinterpret_cast<const int2 *>(samples_xy) + k);
-		sx = sxy.x;
-		sy = sxy.y;
-		sp = cs.sample_px ? __ldg(cs.sample_px + k) : __ldg(in + (size_t)sy * cs.w + sx);
-	}
-	const uint32_t p = __ldg(in + (size_t)y * cs.w + x);
-	const double ddx = (double)(x - sx), ddy = (double)(y - sy);
-	const double dist = __dsqrt_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)));
-	const bool skipped = dist < (double)(cs.h / 5);
-#pragma unroll 1
-	for (int c = 0; c < 4; c++) {
-		const int diff = (int)((p >> (8 * c)) & 0xFF) - (int)((sp >> (8 * c)) & 0xFF);
-		double v = __dmul_rn((double)diff, cs.slope);
-		if (v > cs.limit || c == 3)
-			v = cs.limit;
-		else if (v < -cs.limit)
-			v = -cs.limit;
-		t[c] = skipped ? 0.0 : __ddiv_rn(v, dist);
-	}
-}
-
-// Exact scores of the block's listed candidates sh.cand[0 .. n) (pixels of the
-// slab at (x_lo, ys)).  The whole block computes the terms -- one (candidate,
-// sample) pair per thread and round, that is where the time goes -- then four
-// threads per candidate add them up in sample order: that chain is the
-// reference's and cannot be split.
-__device__ __forceinline__ void ace_exact_candidates(RefineShared &sh, bool table,
-		const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
-		const AceConst &cs, int x_lo, int ys, int n,
-		double *__restrict__ scores, double *__restrict__ minmax)
-{
-	const int chunk = min(cs.nb_samples, kRefineTerms);      // samples per round
-	const int batch = kRefineTerms / chunk;                   // candidates per round
-	const size_t plane = (size_t)cs.score_plane;
-	for (int i0 = 0; i0 < n; i0 += batch) {
-		const int nb = min(batch, n - i0);
-		double acc = 0.0;
-		for (int k0 = 0; k0 < cs.nb_samples; k0 += chunk) {
-			const int kn = min(chunk, cs.nb_samples - k0);
-			for (int q = threadIdx.x; q < nb * kn; q += kRefineThreads) {
-				const int ci = q / kn, j = q - ci * kn;
-				const int cd = sh.cand[i0 + ci];
-				ace_exact_terms(sh, table, in, samples_xy, cs, x_lo + cd % kAceBlock,
-						ys + cd / kAceBlock, k0 + j, sh.terms[q]);
-			}
-			__syncthreads();
-			if (threadIdx.x < 4 * nb) {
-				const double (*tm)[4] = sh.terms + (threadIdx.x >> 2) * kn;
-				const int a = threadIdx.x & 3;
-#pragma unroll 8
-				for (int j = 0; j < kn; j++)
-					acc = __dadd_rn(acc, tm[j][a]);
-			}
-			__syncthreads();
-		}
-		// threads 4i .. 4i+3 hold candidate i's R, G, B sums and the denominator
-		const double denom = __shfl_sync(0xFFFFFFFFu, acc, (threadIdx.x & 31) | 3);
-		if (threadIdx.x < 4 * nb && (threadIdx.x & 3) < 3) {
-			const int cd = sh.cand[i0 + (threadIdx.x >> 2)], c = threadIdx.x & 3;
-			const int px = x_lo + cd % kAceBlock, y = ys + cd / kAceBlock;
-			const double r = __ddiv_rn(acc, denom);
-			scores[c * plane + (size_t)(y - cs.score_row0) * cs.w + px] = r;
-			atomic_min_double(minmax + 6 + c, r);      // NaN never enters
-			atomic_max_double(minmax + 9 + c, r);
-		}
-	}
-}
-
-// Second pass over the few tiles that reach the page's extremes.  The rescale
-// divides by (max - min) and truncates, so a score AT the maximum becomes 255
-// and one an ulp below it 254: where many pixels score the same up to rounding
-// (a flat mark on a flat page, with no sample on the mark), which of them are
-// 254 depends on the last bit of the reference's sums.  Scores within kNearEps
-// of either extreme are therefore recomputed exactly as the reference does,
-// and the extremes themselves are taken over the recomputed values, which
-// makes the rescale of those pixels bit-identical to the reference's.  Tied
-// scores (0, +-1) are exact already and are left alone.
-//
-// A few blocks per SM look through the tile table the accumulation kernel left
-// (neighbouring tiles go to different blocks); a block that finds a tile near
-// an extreme lists the tile's candidate pixels and works them off with all
-// its threads.  tiles_x * tiles_y is the accumulation grid.
-__global__ void __launch_bounds__(kRefineThreads)
-ace_refine_kernel(const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
-		const AceConst cs, double *__restrict__ scores, double *__restrict__ minmax,
-		int tiles_x, int tiles_y)
-{
-	__shared__ RefineShared sh;
-	pdl_wait();
-	double lo[3], hi[3];
+	double lo[3], hi[3], alo[3], ahi[3];
+	const double thr = 2.0 * (double)cs.eps;
+	const double thr2 = 2.0 * ace_accurate_eps(cs.nb_samples);
 #pragma unroll
 	for (int c = 0; c < 3; c++) {
-		const double mn = minmax[c], mx = minmax[3 + c];
-		const double thr = (mx - mn) * kNearEps;
-		lo[c] = mn + thr;
-		hi[c] = mx - thr;
+		lo[c] = minmax[c] + thr;
+		hi[c] = minmax[3 + c] - thr;
+		alo[c] = (PHASE == 2) ? minmax[12 + c] + thr2 : 0.0;
+		ahi[c] = (PHASE == 2) ? minmax[15 + c] - thr2 : 0.0;
 	}
 	const int col = threadIdx.x % kAceBlock;
-	const int tile_row0 = cs.row_begin / cs.tile_rows;
+	const int tile_row0 = cs.row_begin / kTileRows;
 	const size_t plane = (size_t)cs.score_plane;
 	const int n_tiles = tiles_x * tiles_y;
-	const bool table = cs.nb_samples <= kRefineTable;
-	bool staged = false;
+	// extremes this thread has seen: phase 1 the FP64 ones (and ties, which are
+	// exact, into the exact ones), phase 2 the exact ones
+	double mn1[3] = { DBL_MAX, DBL_MAX, DBL_MAX }, mx1[3] = { -DBL_MAX, -DBL_MAX, -DBL_MAX };
+	double emn[3] = { DBL_MAX, DBL_MAX, DBL_MAX }, emx[3] = { -DBL_MAX, -DBL_MAX, -DBL_MAX };
 
 	for (int base = 0; base < n_tiles; base += gridDim.x * kRefineThreads) {
+		__syncthreads();
 		if (threadIdx.x == 0)
 			sh.n_wanted = 0;
 		__syncthreads();
@@ -621,57 +705,120 @@ ace_refine_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 		}
 		__syncthreads();
 		const int n_wanted = sh.n_wanted;
-		if (n_wanted && table && !staged) {
-			staged = true;
-			for (int k = threadIdx.x; k < cs.nb_samples; k += kRefineThreads) {
-				const int2 sxy = __ldg(reinterpret_cast<const int2 *>(samples_xy) + k);
-				sh.sx[k] = sxy.x;
-				sh.sy[k] = sxy.y;
-				sh.spx[k] = cs.sample_px ? __ldg(cs.sample_px + k)
-				                         : __ldg(in + (size_t)sxy.y * cs.w + sxy.x);
-			}
-		}
 		for (int wi = 0; wi < n_wanted; wi++) {
 			const int tw = sh.wanted[wi];
 			const int x_lo = (tw % tiles_x) * kAceBlock;
-			const int tile_y0 = (tile_row0 + tw / tiles_x) * cs.tile_rows;
+			const int tile_y0 = (tile_row0 + tw / tiles_x) * kTileRows;
 			const int y_begin = max(tile_y0, cs.row_begin);
-			const int y_end = min(min(cs.h, tile_y0 + cs.tile_rows), cs.row_end);
+			const int y_end = min(min(cs.h, tile_y0 + kTileRows), cs.row_end);
 			for (int ys = y_begin; ys < y_end; ys += kRefineSlab) {
 				__syncthreads();
-				if (threadIdx.x == 0)
+				if (threadIdx.x == 0) {
 					sh.n_cand = 0;
+					sh.n_todo = 0;
+				}
 				__syncthreads();
-				// this thread's pixels of the slab: all loads first
 				constexpr int kStep = kRefineThreads / kAceBlock;
-				double sv[kRefineSlab / kStep][3];
 #pragma unroll
 				for (int i = 0; i < kRefineSlab / kStep; i++) {
 					const int y = ys + threadIdx.x / kAceBlock + i * kStep;
-					const bool in_tile = y < y_end && x_lo + col < cs.w;
-					const size_t o = in_tile ? (size_t)(y - cs.score_row0) * cs.w + x_lo + col : 0;
-#pragma unroll
-					for (int c = 0; c < 3; c++)
-						sv[i][c] = in_tile ? scores[c * plane + o] : 0.0;   // 0.0: a tie, never listed
-				}
-#pragma unroll
-				for (int i = 0; i < kRefineSlab / kStep; i++) {
+					if (y >= y_end || x_lo + col >= cs.w)
+						continue;
+					const size_t o = (size_t)(y - cs.score_row0) * cs.w + x_lo + col;
 					bool need = false;
 #pragma unroll
-					for (int c = 0; c < 3; c++)
-						need |= (sv[i][c] <= lo[c] || sv[i][c] >= hi[c])
-							&& !is_tie_score(sv[i][c]);                  // false for NaN
+					for (int c = 0; c < 3; c++) {
+						const float sv = scores[c * plane + o];
+						if (!((double)sv <= lo[c] || (double)sv >= hi[c]))    // also NaN
+							continue;
+						if (is_tie_score(sv)) {
+							if (PHASE == 1) {
+								emn[c] = fmin(emn[c], (double)sv);
+								emx[c] = fmax(emx[c], (double)sv);
+							}
+						} else {
+							need = true;
+						}
+					}
 					if (need)
 						sh.cand[atomicAdd(&sh.n_cand, 1)] = (unsigned short)
 							((threadIdx.x / kAceBlock + i * kStep) * kAceBlock + col);
 				}
 				__syncthreads();
 				const int n = sh.n_cand;
-				ace_exact_candidates(sh, table, in, samples_xy, cs, x_lo, ys, n, scores, minmax);
+				// a thread per candidate: its scores in FP64.  They take part in
+				// every channel (true scores of the page can only tighten the
+				// extremes toward the truth).
+				for (int i = threadIdx.x; i < n; i += kRefineThreads) {
+					const int cd = sh.cand[i];
+					double sa[3];
+					ace_accurate_score(in, samples_xy, cs, x_lo + cd % kAceBlock, ys + cd / kAceBlock, sa);
+					bool exact = false;
+#pragma unroll
+					for (int c = 0; c < 3; c++) {
+						if (PHASE == 1) {
+							if (sa[c] < mn1[c]) mn1[c] = sa[c];       // NaN never enters
+							if (sa[c] > mx1[c]) mx1[c] = sa[c];
+						} else {
+							exact |= sa[c] <= alo[c] || sa[c] >= ahi[c];
+						}
+					}
+					if (PHASE == 2 && exact)
+						sh.todo[atomicAdd(&sh.n_todo, 1)] = (unsigned short)cd;
+				}
+				if (PHASE == 2) {
+					__syncthreads();
+					// a warp per pixel that may hold an extreme: the reference's arithmetic
+					const int n_todo = sh.n_todo, warp = threadIdx.x >> 5;
+					for (int i = warp; i < n_todo; i += kRefineThreads / 32) {
+						const int cd = sh.todo[i];
+						double r[3];
+						ace_exact_score_warp(sh.terms[warp], in, samples_xy, cs,
+								x_lo + cd % kAceBlock, ys + cd / kAceBlock, r);
+#pragma unroll
+						for (int c = 0; c < 3; c++) {
+							if (r[c] < emn[c]) emn[c] = r[c];
+							if (r[c] > emx[c]) emx[c] = r[c];
+						}
+					}
+				}
 			}
 		}
-		__syncthreads();
 	}
+	// fold this thread's extremes into the block of the page
+#pragma unroll
+	for (int c = 0; c < 3; c++) {
+#pragma unroll
+		for (int d = 16; d > 0; d >>= 1) {
+			mn1[c] = fmin(mn1[c], __shfl_xor_sync(0xFFFFFFFFu, mn1[c], d));
+			mx1[c] = fmax(mx1[c], __shfl_xor_sync(0xFFFFFFFFu, mx1[c], d));
+			emn[c] = fmin(emn[c], __shfl_xor_sync(0xFFFFFFFFu, emn[c], d));
+			emx[c] = fmax(emx[c], __shfl_xor_sync(0xFFFFFFFFu, emx[c], d));
+		}
+		if ((threadIdx.x & 31) == 0) {
+			if (PHASE == 1 && mn1[c] != DBL_MAX)
+				atomic_min_double(minmax + 12 + c, mn1[c]);
+			if (PHASE == 1 && mx1[c] != -DBL_MAX)
+				atomic_max_double(minmax + 15 + c, mx1[c]);
+			if (emn[c] != DBL_MAX)
+				atomic_min_double(minmax + 6 + c, emn[c]);
+			if (emx[c] != -DBL_MAX)
+				atomic_max_double(minmax + 9 + c, emx[c]);
+		}
+	}
+}
+
+__global__ void __launch_bounds__(kRefineThreads)
+ace_refine_kernel(const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
+		const AceConst cs, const float *__restrict__ scores, double *minmax,
+		int tiles_x, int tiles_y)
+{
+	__shared__ RefineShared sh;
+	pdl_wait();
+	refine_scan<1>(sh, in, samples_xy, cs, scores, minmax, tiles_x, tiles_y);
+	__threadfence();
+	cooperative_groups::this_grid().sync();
+	refine_scan<2>(sh, in, samples_xy, cs, scores, minmax, tiles_x, tiles_y);
 }
 
 // The reference's linear scaling, operation for operation (true FP64 divide).
@@ -687,14 +834,7 @@ __device__ __noinline__ uint32_t ace_scale_exact(double s, double mn, double spa
 	return (uint32_t)__double2int_rz(fmin(v, 255.0));
 }
 
-// out[c] = trunc(clamp(255 * (score - min) / (max - min), 0, 255)); alpha 255.
-// The quotient is formed with a reciprocal multiply (within 2e-13 of the
-// reference's rounded quotient) and truncated by one round-toward-zero add
-// against 2^31 that also exposes 21 fraction bits; only a value within 2e-6
-// of an integer -- which includes the page minimum and maximum, and NaN --
-// goes through the exact divide.  Four pixels per thread, 16-byte stores.
-//
-// MULTI: the same rows are also stored to further images (`more`), which may
+// Destinations of a rescale: `out`, and optionally further images that may
 // live on other GPUs (peer memory over NVLink): the band exchange of a
 // row-band split rides on the rescale instead of following it.
 constexpr int kMaxScaleOuts = 16;
@@ -720,70 +860,218 @@ __device__ __forceinline__ void multimem_store4(void *addr, uint32_t v)
 }
 
 template <bool MULTI>
+__device__ __forceinline__ void store_pixel(uint32_t *out, const ScaleOuts &more, size_t i, uint32_t rgba)
+{
+	if (MULTI && more.multicast)
+		multimem_store4(out + i, rgba);
+	else
+		out[i] = rgba;
+	if (MULTI)
+		for (int d = 0; d < more.n; d++)
+			more.p[d][i] = rgba;
+}
+
+// The exact extremes of a channel (ace_refine_kernel's; every page has them
+// unless all its scores are NaN).
+__device__ __forceinline__ void exact_extremes(const double *__restrict__ minmax, int c, double &mn, double &span)
+{
+	mn = minmax[6 + c];
+	const double mx = minmax[9 + c];
+	span = (mn == DBL_MAX || mx == -DBL_MAX) ? 0.0 : mx - mn;
+}
+
+// out[c] = trunc(clamp(255 * (score - min) / (max - min), 0, 255)); alpha 255.
+// T = (s - min) * K + 2^23 + 2^14 with K = 255 / span * 2^14 is an FP32
+// subtraction and an FMA rounded toward zero: the low mantissa bits of T are
+// the value in units of 2^-14 output steps, shifted up by one step so that a
+// value a little below zero stays positive.  The approximate score is within
+// eps of the reference's, so T is within G = (eps + 1e-7) * K + 4 units of the
+// reference's quotient (1e-7: min rounded to FP32; 4: the roundings of the
+// difference, of K and of T); a value farther than that from an integer
+// truncates like the reference's.  The others go on the fix-up list, and the
+// tied scores (exactly 0, 1, -1) take their three precomputed results.
+template <bool MULTI>
 __global__ void __launch_bounds__(256)
-ace_scale_kernel(const double *__restrict__ scores, const double *__restrict__ minmax,
-		size_t npix, size_t plane, uint32_t *__restrict__ out, const ScaleOuts more)
+ace_scale_kernel(const float *__restrict__ scores, const double *__restrict__ minmax,
+		size_t npix, size_t plane, size_t pix_base, float eps,
+		uint32_t *__restrict__ out, const ScaleOuts more,
+		uint32_t *__restrict__ fix_list, int *__restrict__ fix_count)
 {
 	pdl_wait();
-	double mn[3], span[3], inv[3];
+	float kf[3], mnf[3];
+	uint32_t guard[3], tie_lo[3], tie_zero[3], tie_hi[3];
+	bool flat[3];
 #pragma unroll
 	for (int c = 0; c < 3; c++) {
-		// the extremes over the recomputed scores where ace_refine_kernel
-		// produced some; a tied extreme (exact as it is) takes part as well
-		const double mnf = minmax[c], mxf = minmax[3 + c];
-		const double mne = minmax[6 + c], mxe = minmax[9 + c];
-		mn[c] = (is_tie_score(mnf) || mne == DBL_MAX) ? fmin(mnf, mne) : mne;
-		const double mx = (is_tie_score(mxf) || mxe == -DBL_MAX) ? fmax(mxf, mxe) : mxe;
-		span[c] = mx - mn[c];
-		inv[c] = 1.0 / span[c];
+		double mn, span;
+		exact_extremes(minmax, c, mn, span);
+		flat[c] = !(span > 0.0);
+		const double k = flat[c] ? 0.0 : 255.0 / span * 16384.0;
+		kf[c] = (float)k;
+		mnf[c] = (float)mn;
+		const double g = ((double)eps + 1e-7) * k + 4.0;
+		guard[c] = g < 8192.0 ? (uint32_t)g + 1u : 8192u;       // 8192: everything is uncertain
+		tie_lo[c] = ace_scale_exact(-1.0, mn, span);
+		tie_zero[c] = ace_scale_exact(0.0, mn, span);
+		tie_hi[c] = ace_scale_exact(1.0, mn, span);
 	}
-	bool vec = (npix % 4 == 0) && (plane % 2 == 0)
+	bool vec = (npix % 4 == 0) && (plane % 4 == 0)
 		&& (((uintptr_t)scores | (uintptr_t)out) % 16 == 0);
 	if (MULTI)
 		for (int d = 0; d < more.n; d++)
 			vec = vec && ((uintptr_t)more.p[d] % 16 == 0);
 	const size_t ngroups = vec ? npix / 4 : 0;
-	for (size_t gi = (size_t)blockIdx.x * blockDim.x + threadIdx.x; gi < ngroups;
-			gi += (size_t)gridDim.x * blockDim.x) {
+	const size_t nwork = vec ? ngroups : npix;
+	const int lane = threadIdx.x & 31;
+	for (size_t g0 = (size_t)blockIdx.x * blockDim.x; g0 < nwork; g0 += (size_t)gridDim.x * blockDim.x) {
+		const size_t gi = g0 + threadIdx.x;
+		const bool in_range = gi < nwork;
 		uint32_t px[4] = { 0xFF000000u, 0xFF000000u, 0xFF000000u, 0xFF000000u };
+		unsigned risky = 0;
+		const int per = vec ? 4 : 1;
+		if (in_range) {
 #pragma unroll
-		for (int c = 0; c < 3; c++) {
-			const double2 a = __ldcs(reinterpret_cast<const double2 *>(scores + c * plane) + 2 * gi);
-			const double2 b = __ldcs(reinterpret_cast<const double2 *>(scores + c * plane) + 2 * gi + 1);
-			const double sv[4] = { a.x, a.y, b.x, b.y };
+			for (int c = 0; c < 3; c++) {
+				float sv[4] = { 0.f, 0.f, 0.f, 0.f };
+				if (vec) {
+					const float4 a = __ldcs(reinterpret_cast<const float4 *>(scores + c * plane) + gi);
+					sv[0] = a.x; sv[1] = a.y; sv[2] = a.z; sv[3] = a.w;
+				} else {
+					sv[0] = __ldcs(scores + c * plane + gi);
+				}
 #pragma unroll
-			for (int k = 0; k < 4; k++) {
-				const double t = (255.0 * (sv[k] - mn[c])) * inv[c];
-				const uint32_t fx = (uint32_t)__double2loint(__dadd_rz(t, 2147483648.0));
-				uint32_t q = min(fx >> 21, 255u);
-				if (((fx + 4u) & 0x1FFFFFu) < 8u || !(t >= 0.0))
-					q = ace_scale_exact(sv[k], mn[c], span[c]);
-				px[k] |= q << (8 * c);
+				for (int k = 0; k < 4; k++) {
+					if (k >= per)
+						break;
+					const float s = sv[k];
+					uint32_t q;
+					if (flat[c] || !(s == s)) {
+						q = 0u;                   // a flat channel, or no sample at all (NaN)
+					} else if (is_tie_score(s)) {
+						q = s < 0.f ? tie_lo[c] : (s > 0.f ? tie_hi[c] : tie_zero[c]);
+					} else {
+						const uint32_t fx = __float_as_uint(__fmaf_rz(s - mnf[c], kf[c], 8404992.0f))
+							- 0x4B000000u;
+						const uint32_t v = fx >> 14;          // integer part + 1
+						q = v < 1u ? 0u : (v > 256u ? 255u : v - 1u);
+						if (((fx + guard[c]) & 0x3FFFu) < 2u * guard[c] || fx >= (258u << 14))
+							risky |= 1u << k;
+					}
+					px[k] |= q << (8 * c);
+				}
+			}
+			if (vec) {
+				const uint4 v = make_uint4(px[0], px[1], px[2], px[3]);
+				if (MULTI && more.multicast)
+					multimem_store16(reinterpret_cast<uint4 *>(out) + gi, v);
+				else
+					reinterpret_cast<uint4 *>(out)[gi] = v;
+				if (MULTI)
+					for (int d = 0; d < more.n; d++)
+						reinterpret_cast<uint4 *>(more.p[d])[gi] = v;
+			} else {
+				store_pixel<MULTI>(out, more, gi, px[0]);
 			}
 		}
-		const uint4 v = make_uint4(px[0], px[1], px[2], px[3]);
-		if (MULTI && more.multicast)
-			multimem_store16(reinterpret_cast<uint4 *>(out) + gi, v);
-		else
-			reinterpret_cast<uint4 *>(out)[gi] = v;
-		if (MULTI)
-			for (int d = 0; d < more.n; d++)
-				reinterpret_cast<uint4 *>(more.p[d])[gi] = v;
-	}
-	// shapes that cannot be vectorised: the plain loop
-	for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x + 4 * ngroups; i < npix;
-			i += (size_t)gridDim.x * blockDim.x) {
-		uint32_t rgba = 0xFF000000u;
+		// warp-aggregated append of the uncertain pixels to the fix-up list
+		if (__ballot_sync(0xFFFFFFFFu, risky != 0)) {
+			const int nr = __popc(risky);
+			int pre = nr;
 #pragma unroll
-		for (int c = 0; c < 3; c++)
-			rgba |= ace_scale_exact(__ldcs(scores + c * plane + i), mn[c], span[c]) << (8 * c);
-		if (MULTI && more.multicast)
-			multimem_store4(out + i, rgba);
-		else
-			out[i] = rgba;
-		if (MULTI)
-			for (int d = 0; d < more.n; d++)
-				more.p[d][i] = rgba;
+			for (int dlt = 1; dlt < 32; dlt <<= 1) {
+				const int t = __shfl_up_sync(0xFFFFFFFFu, pre, dlt);
+				if (lane >= dlt)
+					pre += t;
+			}
+			int base = 0;
+			if (lane == 31)
+				base = atomicAdd(fix_count, pre);
+			base = __shfl_sync(0xFFFFFFFFu, base, 31) + pre - nr;
+#pragma unroll
+			for (int k = 0; k < 4; k++)
+				if (risky & (1u << k))
+					fix_list[base++] = (uint32_t)(pix_base + (size_t)per * gi + k);
+		}
+	}
+}
+
+// The listed pixels again, a thread per pixel: scores in FP64
+// (ace_accurate_score, error e2 ~ 1e-14), rescaled with a true division.  That
+// decides the truncation unless the value lies within the (now tiny) bound of
+// an integer; those last few -- the pixels AT the page's extremes among them
+// -- are redone by a whole warp in the reference's own arithmetic.  List
+// entries index the score block; `out` points at its pixel 0.
+template <bool MULTI>
+__global__ void __launch_bounds__(256)
+ace_fixup_kernel(const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
+		const AceConst cs, const double *__restrict__ minmax,
+		const uint32_t *__restrict__ fix_list, int *fix_count, int *fix_ticket,
+		uint32_t *__restrict__ out, const ScaleOuts more)
+{
+	__shared__ double terms[256 / 32][kExactChunk][4];
+	pdl_wait();
+	const int count = *reinterpret_cast<volatile int *>(fix_count);
+	if (count == 0)
+		return;
+	double mn[3], span[3], guard[3];
+#pragma unroll
+	for (int c = 0; c < 3; c++) {
+		exact_extremes(minmax, c, mn[c], span[c]);
+		// e2 on the score, and the reference's own three roundings of the rescale
+		guard[c] = 255.0 * (ace_accurate_eps(cs.nb_samples) / span[c] + 0x1p-48);
+	}
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	for (int i0 = blockIdx.x * blockDim.x; i0 < count; i0 += gridDim.x * blockDim.x) {
+		const int i = i0 + threadIdx.x;
+		const bool active = i < count;
+		const uint32_t idx = active ? fix_list[i] : 0u;
+		const int y = cs.score_row0 + (int)(idx / (uint32_t)cs.w), x = (int)(idx % (uint32_t)cs.w);
+		bool open = false;
+		if (active) {
+			double sa[3];
+			ace_accurate_score(in, samples_xy, cs, x, y, sa);
+			uint32_t rgba = 0xFF000000u;
+#pragma unroll
+			for (int c = 0; c < 3; c++) {
+				uint32_t q = 0u;
+				if (span[c] > 0.0 && sa[c] == sa[c]) {
+					const double t = 255.0 * (sa[c] - mn[c]) / span[c];
+					const double fl = floor(t);
+					if (t - fl < guard[c] || fl + 1.0 - t < guard[c])
+						open = true;
+					q = (uint32_t)fmin(fmax(fl, 0.0), 255.0);
+				}
+				rgba |= q << (8 * c);
+			}
+			if (!open)
+				store_pixel<MULTI>(out, more, idx, rgba);
+		}
+		// the undecided ones, one at a time by the whole warp
+		unsigned todo = __ballot_sync(0xFFFFFFFFu, open);
+		while (todo) {
+			const int src = __ffs(todo) - 1;
+			todo &= todo - 1;
+			const int ex = __shfl_sync(0xFFFFFFFFu, x, src), ey = __shfl_sync(0xFFFFFFFFu, y, src);
+			const uint32_t eidx = __shfl_sync(0xFFFFFFFFu, idx, src);
+			double r[3];
+			ace_exact_score_warp(terms[warp], in, samples_xy, cs, ex, ey, r);
+			if (lane == 0) {
+				uint32_t rgba = 0xFF000000u;
+#pragma unroll
+				for (int c = 0; c < 3; c++)
+					rgba |= ace_scale_exact(r[c], mn[c], span[c]) << (8 * c);
+				store_pixel<MULTI>(out, more, eidx, rgba);
+			}
+		}
+	}
+	// the last block to finish empties the list for the next rescale of this
+	// slot (every block has read the length before it gets here)
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		if (atomicAdd(fix_ticket, 1) == (int)gridDim.x - 1) {
+			*fix_ticket = 0;
+			*reinterpret_cast<volatile int *>(fix_count) = 0;
+		}
 	}
 }
 
@@ -801,6 +1089,20 @@ __global__ void fp64_peak_kernel(double *sink, int iters, double a, double b)
 		sink[0] = s;
 }
 
+// FP32 FMA rate probe (the accumulation kernel's pipe): 8 independent chains.
+__global__ void fp32_peak_kernel(float *sink, int iters, float a, float b)
+{
+	float v0 = threadIdx.x, v1 = v0 + 1, v2 = v0 + 2, v3 = v0 + 3;
+	float v4 = v0 + 4, v5 = v0 + 5, v6 = v0 + 6, v7 = v0 + 7;
+	for (int i = 0; i < iters; i++) {
+		v0 = fmaf(v0, a, b); v1 = fmaf(v1, a, b); v2 = fmaf(v2, a, b); v3 = fmaf(v3, a, b);
+		v4 = fmaf(v4, a, b); v5 = fmaf(v5, a, b); v6 = fmaf(v6, a, b); v7 = fmaf(v7, a, b);
+	}
+	const float s = v0 + v1 + v2 + v3 + v4 + v5 + v6 + v7;
+	if (s == 12345.678f)
+		sink[0] = s;
+}
+
 }  // namespace
 
 int launch_ace_minmax_init(double *minmax, int w, int h, cudaStream_t st)
@@ -813,29 +1115,33 @@ int launch_ace_minmax_init(double *minmax, int w, int h, cudaStream_t st)
 
 namespace {
 
-// Pixels a thread carries and rows a tile holds.  Knobs (read once per
-// process; tools/ace_time.py sweeps them); the defaults are the measured best
-// on B200 (profiles/README.md):
-//   PF_B200_ACE_ROWS = 2 | 4 | 6 | 8   pixels per thread (default 8)
-//   PF_B200_ACE_TILE_ROWS = n          rows per tile (default 16)
-int ace_rows_per_thread(bool fast)
+// Worst-case bound on |approximate score - reference score| (score range
+// [-1, 1]) for nb_samples samples; what the refinement threshold and the
+// rescale's guard band are derived from.
+//   weights:  MUFU.RSQ is within 2^-22.94 (measured over two binades,
+//       tools/ubench/ace_fp32_proto.cu), its argument d^2 within 2^-23 (three
+//       FP32 roundings), so a weight is within e_w = 1.25e-7 + 6e-8 of
+//       1/dist and the score moves by at most 2 e_w / (1 - e_w) < 3.8e-7
+//       (the same weight multiplies numerator and denominator);
+//   clamp:    u = sat(p * inv + b) with inv = slope / (2 limit) * (1 + 2^-22)
+//       rounded to FP32 and b = 1/2 - s * inv rounded from double: at most
+//       2^-23 + 2^-25 + 2^-26 off, i.e. 3.3e-7 on the score;
+//   sums:     first-level sums of at most kFlush terms, second level of at
+//       most levels2 partial sums, every operation rounding once (2^-24 of
+//       the running sum, all terms >= 0): relative error of a sum at most
+//       (kFlush - 1 + levels2) * 2^-24 =: g, of the quotient 2 g, of the
+//       score 4 g;
+//   epilogue: four FP32 operations on values <= 2 and a reciprocal: < 1e-6.
+double ace_score_eps(int nb_samples)
 {
-	static const int rows_env = getenv("PF_B200_ACE_ROWS") ? atoi(getenv("PF_B200_ACE_ROWS")) : 8;
-	if (!fast)
-		return 4;
-	return (rows_env == 2 || rows_env == 4 || rows_env == 6) ? rows_env : 8;
+	const int chunks = (nb_samples + kChunk - 1) / kChunk;
+	const int levels2 = (nb_samples + kFlush - 1) / kFlush + 2 * chunks;
+	const double g = (double)(kFlush - 1 + levels2) * 0x1p-24 * 1.01;
+	return 4.0 * g + 3.8e-7 + 3.3e-7 + 1.0e-6;
 }
 
-int ace_tile_rows(bool fast)
-{
-	static const int tile_env = getenv("PF_B200_ACE_TILE_ROWS") ? atoi(getenv("PF_B200_ACE_TILE_ROWS")) : 0;
-	const int rows_p = ace_rows_per_thread(fast);
-	// a tile is a whole number of row groups
-	return (tile_env >= rows_p && tile_env % rows_p == 0) ? tile_env : (rows_p == 6 ? 18 : 16);
-}
-
-// Checks the arguments and lays out the launch both ACE kernels share.
-int ace_setup(const AceParams &p, AceConst &cs, dim3 &grid, bool &fast)
+// Checks the arguments and lays out the launch the ACE kernels share.
+int ace_setup(const AceParams &p, AceConst &cs, dim3 &grid)
 {
 	if (p.nb_samples < 1)
 		return fail(PF_B200_EINVAL, "ace: nb_samples must be >= 1");
@@ -859,14 +1165,35 @@ int ace_setup(const AceParams &p, AceConst &cs, dim3 &grid, bool &fast)
 	cs.sample_px = p.sample_px;
 	cs.score_row0 = p.score_row0 >= 0 ? p.score_row0 : p.row_begin;
 	cs.score_plane = p.score_plane >= 0 ? p.score_plane : (long)(p.row_end - p.row_begin) * p.w;
-	// fast path: saturate(slope*d) == slope*clamp(d, -L, L) with integer L <= 127
-	const double l = p.limit / p.slope;
-	fast = l >= 1.0 && l <= 127.0 && l == floor(l) && p.slope * l == p.limit;
-	cs.clamp_l = fast ? (int)l : 0;
-	cs.tile_rows = ace_tile_rows(fast);
+	// inv a little above slope / (2 limit): a difference that saturates in the
+	// reference then reaches 0 or 1 before the rounding of the FMA can matter,
+	// and equal values give exactly 1/2 (ace_score_eps, "clamp")
+	cs.inv = (float)(p.slope / (2.0 * p.limit) * (1.0 + 0x1p-22));
+	cs.eps = (float)(ace_score_eps(p.nb_samples) * 1.001);
+	// the reference saturates a difference d when slope * d (rounded) exceeds
+	// the limit; reaching it exactly gives the same value
+	volatile double prod;
+	cs.dsat = 256;
+	for (int d = 1; d <= 255; d++) {
+		prod = (double)d * p.slope;
+		if (prod >= p.limit) {
+			cs.dsat = d;
+			break;
+		}
+	}
 	grid = dim3((p.w + kAceBlock - 1) / kAceBlock,
-			(p.row_end - 1) / cs.tile_rows - p.row_begin / cs.tile_rows + 1);
+			(p.row_end - 1) / kTileRows - p.row_begin / kTileRows + 1);
 	return PF_B200_OK;
+}
+
+ScaleOuts scale_outs(uint32_t *const *outs, int nb_outs, bool multicast)
+{
+	ScaleOuts more = {};
+	for (int d = 1; d < nb_outs; d++)
+		more.p[d - 1] = outs[d];
+	more.n = nb_outs - 1;
+	more.multicast = multicast ? 1 : 0;
+	return more;
 }
 
 }  // namespace
@@ -874,105 +1201,147 @@ int ace_setup(const AceParams &p, AceConst &cs, dim3 &grid, bool &fast)
 size_t ace_minmax_doubles(int w, int h)
 {
 	// a band of the page never has more tile rows than the page has, plus one
-	const int tile_rows = ace_tile_rows(true) < ace_tile_rows(false) ? ace_tile_rows(true)
-	                                                                 : ace_tile_rows(false);
-	const size_t tiles = (size_t)((w + kAceBlock - 1) / kAceBlock) * ((h + tile_rows - 1) / tile_rows + 1);
+	const size_t tiles = (size_t)((w + kAceBlock - 1) / kAceBlock) * ((h + kTileRows - 1) / kTileRows + 1);
 	return kMinmaxHead + 6 * tiles;
 }
 
+size_t ace_scores_bytes(int w, int rows)
+{
+	const size_t n = (size_t)w * rows;
+	return (kAceScoreHeader + 16 * n + 255) / 256 * 256;
+}
+
+AceScores ace_scores_at(void *block, size_t plane)
+{
+	AceScores s;
+	s.counts = static_cast<int *>(block);
+	s.planes = reinterpret_cast<float *>(static_cast<char *>(block) + kAceScoreHeader);
+	s.list = reinterpret_cast<uint32_t *>(s.planes + 3 * plane);
+	s.plane = plane;
+	return s;
+}
+
 int launch_ace_scores(const uint32_t *in, const int *samples_xy,
-		const AceParams &p, double *scores, double *minmax, cudaStream_t st)
+		const AceParams &p, const AceScores &sc, double *minmax, cudaStream_t st)
 {
 	AceConst cs;
 	dim3 grid;
-	bool fast;
-	const int rc = ace_setup(p, cs, grid, fast);
+	const int rc = ace_setup(p, cs, grid);
 	if (rc)
 		return rc;
 	const size_t smem = sizeof(AceShared);
-	//   PF_B200_ACE_NEWTON = 1         one Newton step on MUFU.RSQ64H's 1/dist:
-	//       weights good to ~2^-43 instead of ~2^-22.  Off by default: both
-	//       settings sit three orders of magnitude inside the +-1 LSB / 0.1 %
-	//       bar (1.1e-4 % vs 3e-5 % of channel values differ on the test page)
-	//       and the step costs 3 of 8 FP64 instructions per pair.
-	const int rows_env = ace_rows_per_thread(fast);
-	static const int newton_env = getenv("PF_B200_ACE_NEWTON") ? atoi(getenv("PF_B200_ACE_NEWTON")) : 0;
-	void (*kern)(const uint32_t *, const int *, const AceConst, double *, double *) = nullptr;
-	if (!fast)
-		kern = ace_scores_kernel<false, true, 4>;
-	else if (newton_env)
-		kern = rows_env == 2 ? ace_scores_kernel<true, true, 2>
-			: rows_env == 8 ? ace_scores_kernel<true, true, 8> : ace_scores_kernel<true, true, 4>;
-	else
-		kern = rows_env == 2 ? ace_scores_kernel<true, false, 2>
-			: rows_env == 8 ? ace_scores_kernel<true, false, 8>
-			: rows_env == 6 ? ace_scores_kernel<true, false, 6> : ace_scores_kernel<true, false, 4>;
-	PFB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-	PFB_CUDA(launch_pdl(kern, grid, dim3(kAceBlock), smem, st, in, samples_xy, cs, scores, minmax));
+	PFB_CUDA(cudaFuncSetAttribute(ace_scores_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+	PFB_CUDA(launch_pdl(ace_scores_kernel, grid, dim3(kAceBlock), smem, st, in, samples_xy, cs,
+			sc.planes, sc.counts, minmax));
 	return PF_B200_OK;
 }
 
-
 int launch_ace_refine(const uint32_t *in, const int *samples_xy,
-		const AceParams &p, double *scores, double *minmax, cudaStream_t st)
+		const AceParams &p, const AceScores &sc, double *minmax, cudaStream_t st)
 {
 	AceConst cs;
 	dim3 grid;
-	bool fast;
-	const int rc = ace_setup(p, cs, grid, fast);
+	const int rc = ace_setup(p, cs, grid);
 	if (rc)
 		return rc;
-	PFB_CUDA(launch_pdl(ace_refine_kernel, dim3(sm_count() * 4), dim3(kRefineThreads), 0, st,
-			in, samples_xy, cs, scores, minmax, (int)grid.x, (int)grid.y));
+	// a cooperative launch (grid barrier between the two phases) that may also
+	// be scheduled early behind the accumulation
+	int per_sm = 0;
+	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ace_refine_kernel, kRefineThreads, 0)
+			!= cudaSuccess || per_sm < 1) {
+		cudaGetLastError();
+		per_sm = 1;
+	}
+	cudaLaunchConfig_t cfg = {};
+	cfg.gridDim = dim3(sm_count() * (per_sm < 4 ? per_sm : 4));
+	cfg.blockDim = dim3(kRefineThreads);
+	cfg.stream = st;
+	cudaLaunchAttribute attr[2];
+	attr[0].id = cudaLaunchAttributeCooperative;
+	attr[0].val.cooperative = 1;
+	attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+	attr[1].val.programmaticStreamSerializationAllowed = 1;
+	cfg.attrs = attr;
+	cfg.numAttrs = pdl_enabled() ? 2 : 1;
+	PFB_CUDA(cudaLaunchKernelEx(&cfg, ace_refine_kernel, in, samples_xy, cs, (const float *)sc.planes,
+			minmax, (int)grid.x, (int)grid.y));
 	return PF_B200_OK;
 }
 
-int launch_ace_scale(const double *scores, const double *minmax, int w,
-		int rows, uint32_t *out, cudaStream_t st, long plane)
-{
-	const size_t npix = (size_t)w * rows;
-	const size_t work = (npix + 3) / 4;       // 4 pixels per thread
-	const int blocks = (int)((work + 255) / 256 < (size_t)sm_count() * 8
-			? (work + 255) / 256 : (size_t)sm_count() * 8);
-	ScaleOuts more = {};
-	PFB_CUDA(launch_pdl(ace_scale_kernel<false>, dim3(blocks), dim3(256), 0, st,
-			scores, minmax, npix, plane >= 0 ? (size_t)plane : npix, out, more));
-	return PF_B200_OK;
-}
-
-int launch_ace_scale_multi(const double *scores, const double *minmax, int w, int rows,
-		uint32_t *const *outs, int nb_outs, cudaStream_t st, bool multicast)
+int launch_ace_scale(const AceParams &p, const AceScores &sc, const double *minmax,
+		int row0, int rows, int slot, uint32_t *const *outs, int nb_outs, bool multicast,
+		cudaStream_t st)
 {
 	if (nb_outs < 1 || nb_outs > kMaxScaleOuts)
 		return fail(PF_B200_EINVAL, "ace: %d destinations (1..%d)", nb_outs, kMaxScaleOuts);
-	ScaleOuts more = {};
-	for (int d = 1; d < nb_outs; d++)
-		more.p[d - 1] = outs[d];
-	more.n = nb_outs - 1;
-	more.multicast = multicast ? 1 : 0;
-	const size_t npix = (size_t)w * rows;
-	const size_t work = (npix + 3) / 4;
+	if (slot < 0 || slot >= kAceFixupSlots)
+		return fail(PF_B200_EINVAL, "ace: fix-up slot %d", slot);
+	AceConst cs;
+	dim3 grid;
+	const int rc = ace_setup(p, cs, grid);
+	if (rc)
+		return rc;
+	const size_t npix = (size_t)p.w * rows;
+	const size_t pix_base = (size_t)(row0 - cs.score_row0) * p.w;
+	const size_t work = (npix + 3) / 4;       // 4 pixels per thread
 	const int blocks = (int)((work + 255) / 256 < (size_t)sm_count() * 8
 			? (work + 255) / 256 : (size_t)sm_count() * 8);
-	PFB_CUDA(launch_pdl(ace_scale_kernel<true>, dim3(blocks), dim3(256), 0, st,
-			scores, minmax, npix, npix, outs[0], more));
+	const ScaleOuts more = scale_outs(outs, nb_outs, multicast);
+	const float *planes = sc.planes + pix_base;
+	// the list of a slot starts at the slot's first pixel: slots cover disjoint rows
+	uint32_t *list = sc.list + pix_base;
+	if (nb_outs == 1 && !multicast)
+		PFB_CUDA(launch_pdl(ace_scale_kernel<false>, dim3(blocks), dim3(256), 0, st, planes, minmax,
+				npix, sc.plane, pix_base, cs.eps, outs[0], more, list, sc.counts + slot));
+	else
+		PFB_CUDA(launch_pdl(ace_scale_kernel<true>, dim3(blocks), dim3(256), 0, st, planes, minmax,
+				npix, sc.plane, pix_base, cs.eps, outs[0], more, list, sc.counts + slot));
 	return PF_B200_OK;
 }
 
-double measure_fp64_peak_tflops()
+int launch_ace_fixup(const uint32_t *in, const int *samples_xy, const AceParams &p,
+		const AceScores &sc, const double *minmax, int row0, int slot,
+		uint32_t *const *outs, int nb_outs, bool multicast, cudaStream_t st)
 {
-	double *sink = nullptr;
+	if (nb_outs < 1 || nb_outs > kMaxScaleOuts)
+		return fail(PF_B200_EINVAL, "ace: %d destinations (1..%d)", nb_outs, kMaxScaleOuts);
+	AceConst cs;
+	dim3 grid;
+	const int rc = ace_setup(p, cs, grid);
+	if (rc)
+		return rc;
+	const size_t pix_base = (size_t)(row0 - cs.score_row0) * p.w;
+	// `outs` point at row0; list entries index the score block
+	uint32_t *shifted[kMaxScaleOuts];
+	for (int d = 0; d < nb_outs; d++)
+		shifted[d] = outs[d] - pix_base;
+	const ScaleOuts more = scale_outs(shifted, nb_outs, multicast);
+	const uint32_t *list = sc.list + pix_base;
+	const int blocks = sm_count() * 4;
+	if (nb_outs == 1 && !multicast)
+		PFB_CUDA(launch_pdl(ace_fixup_kernel<false>, dim3(blocks), dim3(256), 0, st, in, samples_xy, cs,
+				minmax, list, sc.counts + slot, sc.counts + kAceFixupSlots + slot, shifted[0], more));
+	else
+		PFB_CUDA(launch_pdl(ace_fixup_kernel<true>, dim3(blocks), dim3(256), 0, st, in, samples_xy, cs,
+				minmax, list, sc.counts + slot, sc.counts + kAceFixupSlots + slot, shifted[0], more));
+	return PF_B200_OK;
+}
+
+template <typename T, typename K>
+static double measure_fma_peak(K kern, T a, T b, const char *what)
+{
+	T *sink = nullptr;
 	if (cudaMalloc(&sink, 64) != cudaSuccess)
-		return -(double)fail(PF_B200_ECUDA, "fp64 probe: cudaMalloc failed");
+		return -(double)fail(PF_B200_ECUDA, "%s probe: cudaMalloc failed", what);
 	const int blocks = sm_count() * 8, threads = 256, iters = 1 << 15;
 	cudaEvent_t e0, e1;
 	cudaEventCreate(&e0);
 	cudaEventCreate(&e1);
-	fp64_peak_kernel<<<blocks, threads>>>(sink, 1024, 1.0000001, 1e-9);   // warm-up
+	kern<<<blocks, threads>>>(sink, 1024, a, b);   // warm-up
 	double best_ms = 1e30;
 	for (int rep = 0; rep < 5; rep++) {
 		cudaEventRecord(e0);
-		fp64_peak_kernel<<<blocks, threads>>>(sink, iters, 1.0000001, 1e-9);
+		kern<<<blocks, threads>>>(sink, iters, a, b);
 		cudaEventRecord(e1);
 		cudaEventSynchronize(e1);
 		float ms = 0.f;
@@ -985,9 +1354,19 @@ double measure_fp64_peak_tflops()
 	const cudaError_t err = cudaGetLastError();
 	cudaFree(sink);
 	if (err != cudaSuccess)
-		return -(double)fail(PF_B200_ECUDA, "fp64 probe: %s", cudaGetErrorString(err));
+		return -(double)fail(PF_B200_ECUDA, "%s probe: %s", what, cudaGetErrorString(err));
 	const double flops = 2.0 * 8.0 * (double)iters * blocks * threads;
 	return flops / (best_ms * 1e-3) / 1e12;
+}
+
+double measure_fp64_peak_tflops()
+{
+	return measure_fma_peak<double>(fp64_peak_kernel, 1.0000001, 1e-9, "fp64");
+}
+
+double measure_fp32_peak_tflops()
+{
+	return measure_fma_peak<float>(fp32_peak_kernel, 1.0000001f, 1e-9f, "fp32");
 }
 
 }  // namespace pfb

@@ -841,11 +841,12 @@ static int run_stencil(Op op, const struct pf_bitmap *in, struct pf_bitmap *out,
 // ACE on ordinary (pageable) memory on both sides: the same pipeline as
 // run_stencil_pageable.  Bands are staged in by the pool and accumulated as
 // they arrive (the samples' pixel values go ahead); after the page-wide
-// extremes are known the rescale writes band after band into the second
-// staging area and the pool copies each out as soon as it is there.
+// extremes are known each band is rescaled and its uncertain pixels redone
+// (launch_ace_scale / launch_ace_fixup) into the second staging area, and the
+// pool copies each band out as soon as it is there.
 static int run_ace_pageable(Context &c, const struct pf_bitmap *in, struct pf_bitmap *out,
 		AceParams p, const int *sample_xy, const int *d_xy, uint32_t *d_spx,
-		double *minmax, double *scores)
+		double *minmax, const AceScores &sc)
 {
 	const int w = in->size.x, h = in->size.y;
 	const size_t npix = (size_t)w * h;
@@ -879,8 +880,6 @@ static int run_ace_pageable(Context &c, const struct pf_bitmap *in, struct pf_bi
 	PFB_CUDA(cudaMemcpyAsync(d_spx, spx, sizeof(uint32_t) * (size_t)p.nb_samples,
 			cudaMemcpyHostToDevice, c.st));
 	p.sample_px = d_spx;
-	p.score_row0 = 0;
-	p.score_plane = (long)npix;
 
 	std::atomic<int> in_ready[kMaxBands], out_ready[kMaxBands];
 	for (int b = 0; b < nb; b++) {
@@ -933,18 +932,19 @@ static int run_ace_pageable(Context &c, const struct pf_bitmap *in, struct pf_bi
 		if (!rc) {
 			p.row_begin = b * rows;
 			p.row_end = (p.row_begin + rows < h) ? p.row_begin + rows : h;
-			rc = launch_ace_scores(din, d_xy, p, scores, minmax, c.st);
+			rc = launch_ace_scores(din, d_xy, p, sc, minmax, c.st);
 		}
 	}
-	if (!rc) {
-		p.row_begin = 0;
-		p.row_end = h;
-		rc = launch_ace_refine(din, d_xy, p, scores, minmax, c.st);
-	}
+	p.row_begin = 0;
+	p.row_end = h;
+	if (!rc)
+		rc = launch_ace_refine(din, d_xy, p, sc, minmax, c.st);
 	for (int b = 0; b < nb && !rc; b++) {
 		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
-		rc = launch_ace_scale(scores + (size_t)y0 * w, minmax, w, y1 - y0,
-				direct + (size_t)y0 * w, c.st, (long)npix);
+		uint32_t *to = direct + (size_t)y0 * w;
+		rc = launch_ace_scale(p, sc, minmax, y0, y1 - y0, b, &to, 1, false, c.st);
+		if (!rc)
+			rc = launch_ace_fixup(din, d_xy, p, sc, minmax, y0, b, &to, 1, false, c.st);
 		if (!rc)
 			rc = cuda_rc(cudaEventRecord(c.ev_done[b], c.st), "rescale");
 		if (!rc)
@@ -985,7 +985,7 @@ static int run_ace_impl(const struct pf_bitmap *in, struct pf_bitmap *out,
 	const size_t mm_bytes = (ace_minmax_doubles(w, h) * sizeof(double) + 63) / 64 * 64;
 	const size_t small = mm_bytes + sizeof(int) * 3 * (size_t)nb_samples;
 	if ((rc = grow(c.d_in, bytes, false)) || (rc = grow(c.d_out, bytes, false))
-			|| (rc = grow(c.d_scores, 3 * npix * sizeof(double), false))
+			|| (rc = grow(c.d_scores, ace_scores_bytes(w, h), false))
 			|| (rc = grow(c.d_small, small, false)))
 		return rc;
 	double *minmax = static_cast<double *>(c.d_small.p);
@@ -993,20 +993,25 @@ static int run_ace_impl(const struct pf_bitmap *in, struct pf_bitmap *out,
 	uint32_t *d_spx = reinterpret_cast<uint32_t *>(d_xy + 2 * (size_t)nb_samples);
 	const uint32_t *din = static_cast<const uint32_t *>(c.d_in.p);
 	uint32_t *dout = static_cast<uint32_t *>(c.d_out.p);
-	double *scores = static_cast<double *>(c.d_scores.p);
+	// one score block for the page: bands of a call share its planes
+	const AceScores sc = ace_scores_at(c.d_scores.p, npix);
 	// the table is tiny; pageable copies are staged by the runtime before it
 	// returns, so the caller's array is free to reuse
 	PFB_CUDA(cudaMemcpyAsync(d_xy, sample_xy, sizeof(int) * 2 * (size_t)nb_samples,
 			cudaMemcpyHostToDevice, c.st));
 	AceParams p = { w, h, 0, h, nb_samples, slope, limit };
+	p.score_row0 = 0;
+	p.score_plane = (long)npix;
 	if ((rc = launch_ace_minmax_init(minmax, w, h, c.st)))
 		return rc;
 
 	if (h >= 512 && nb_samples <= 4096 && is_pinned(in->pixels) && is_pinned(out->pixels)) {
 		// Streamed: with the samples' pixel values sent ahead (gathered here
 		// from the caller's page), a band of rows can be accumulated as soon
-		// as it has arrived; the rescale needs the page-wide min/max, so it
-		// starts after the last band and overlaps the way back.
+		// as it has arrived.  The rescale needs the page-wide extremes, so it
+		// starts after the last band; it writes its rows straight into the
+		// caller's page (posted PCIe writes, like the stencils), and the
+		// fix-up pass stores its few pixels there again.
 		const uint32_t *src = reinterpret_cast<const uint32_t *>(in->pixels);
 		uint32_t *dst = reinterpret_cast<uint32_t *>(out->pixels);
 		uint32_t spx[4096];
@@ -1024,44 +1029,39 @@ static int run_ace_impl(const struct pf_bitmap *in, struct pf_bitmap *out,
 			PFB_CUDA(cudaEventRecord(c.ev_up[b], c.st_up));
 		}
 		p.sample_px = d_spx;
-		p.score_row0 = 0;
-		p.score_plane = (long)npix;
 		for (int b = 0; b < nb; b++) {
 			p.row_begin = b * rows;
 			p.row_end = (p.row_begin + rows < h) ? p.row_begin + rows : h;
 			PFB_CUDA(cudaStreamWaitEvent(c.st, c.ev_up[b], 0));
-			if ((rc = launch_ace_scores(din, d_xy, p, scores, minmax, c.st)))
+			if ((rc = launch_ace_scores(din, d_xy, p, sc, minmax, c.st)))
 				return rc;
 		}
 		p.row_begin = 0;
 		p.row_end = h;
-		if ((rc = launch_ace_refine(din, d_xy, p, scores, minmax, c.st)))
+		if ((rc = launch_ace_refine(din, d_xy, p, sc, minmax, c.st)))
 			return rc;
-		for (int b = 0; b < nb; b++) {
-			const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
-			if ((rc = launch_ace_scale(scores + (size_t)y0 * w, minmax, w, y1 - y0,
-					dout + (size_t)y0 * w, c.st, (long)npix)))
-				return rc;
-			PFB_CUDA(cudaEventRecord(c.ev_done[b], c.st));
-			PFB_CUDA(cudaStreamWaitEvent(c.st_down, c.ev_done[b], 0));
-			PFB_CUDA(cudaMemcpyAsync(dst + (size_t)y0 * w, dout + (size_t)y0 * w,
-					(size_t)(y1 - y0) * w * sizeof(uint32_t), cudaMemcpyDeviceToHost, c.st_down));
-		}
-		PFB_CUDA(cudaStreamSynchronize(c.st_down));
+		static const bool direct_env = !getenv("PF_B200_DIRECT_OUT") || atoi(getenv("PF_B200_DIRECT_OUT"));
+		uint32_t *direct = direct_env ? static_cast<uint32_t *>(device_alias(out->pixels)) : nullptr;
+		uint32_t *to = direct ? direct : dout;
+		if ((rc = launch_ace_scale(p, sc, minmax, 0, h, 0, &to, 1, false, c.st))
+				|| (rc = launch_ace_fixup(din, d_xy, p, sc, minmax, 0, 0, &to, 1, false, c.st)))
+			return rc;
+		if (!direct)
+			PFB_CUDA(cudaMemcpyAsync(dst, dout, bytes, cudaMemcpyDeviceToHost, c.st));
+		PFB_CUDA(cudaStreamSynchronize(c.st));
 		return PF_B200_OK;
 	}
 
 	static const bool pipe_env = !getenv("PF_B200_PAGEABLE_PIPELINE") || atoi(getenv("PF_B200_PAGEABLE_PIPELINE"));
 	if (pipe_env && h >= 512 && nb_samples <= 4096 && bytes >= kParallelMin && bytes <= kParallelMax
 			&& !is_pinned(in->pixels))
-		return run_ace_pageable(c, in, out, p, sample_xy, d_xy, d_spx, minmax, scores);
+		return run_ace_pageable(c, in, out, p, sample_xy, d_xy, d_spx, minmax, sc);
 	if ((rc = upload(c, c.d_in.p, in->pixels, bytes)))
 		return rc;
-	if ((rc = launch_ace_scores(din, d_xy, p, scores, minmax, c.st)))
-		return rc;
-	if ((rc = launch_ace_refine(din, d_xy, p, scores, minmax, c.st)))
-		return rc;
-	if ((rc = launch_ace_scale(scores, minmax, w, h, dout, c.st)))
+	if ((rc = launch_ace_scores(din, d_xy, p, sc, minmax, c.st))
+			|| (rc = launch_ace_refine(din, d_xy, p, sc, minmax, c.st))
+			|| (rc = launch_ace_scale(p, sc, minmax, 0, h, 0, &dout, 1, false, c.st))
+			|| (rc = launch_ace_fixup(din, d_xy, p, sc, minmax, 0, 0, &dout, 1, false, c.st)))
 		return rc;
 	return download(c, out->pixels, c.d_out.p, bytes);
 }
@@ -1301,6 +1301,16 @@ size_t pf_b200_ace_minmax_bytes(int width, int height)
 	return ace_minmax_doubles(width, height) * sizeof(double);
 }
 
+size_t pf_b200_ace_scores_bytes(int width, int nb_rows)
+{
+	clear_error();
+	if (width <= 0 || nb_rows <= 0) {
+		fail(PF_B200_EINVAL, "size %d x %d", width, nb_rows);
+		return 0;
+	}
+	return ace_scores_bytes(width, nb_rows);
+}
+
 int pf_b200_dev_ace_minmax_init(double *d_minmax, int width, int height, void *stream)
 {
 	clear_error();
@@ -1311,114 +1321,137 @@ int pf_b200_dev_ace_minmax_init(double *d_minmax, int width, int height, void *s
 	return launch_ace_minmax_init(d_minmax, width, height, static_cast<cudaStream_t>(stream));
 }
 
-int pf_b200_dev_ace_refine(const uint32_t *d_in, int width, int height,
-		int row_begin, int row_end,
-		const int *d_samples, int nb_samples, double slope, double limit,
-		double *d_scores, double *d_minmax, void *stream)
-{
-	clear_error();
-	if (!d_in || !d_samples || !d_scores || !d_minmax)
-		return fail(PF_B200_EINVAL, "NULL device pointer");
-	if (width <= 0 || height <= 0)
-		return fail(PF_B200_EINVAL, "size %d x %d", width, height);
-	AceParams p = { width, height, row_begin, row_end, nb_samples, slope, limit };
-	return launch_ace_refine(d_in, d_samples, p, d_scores, d_minmax,
-			static_cast<cudaStream_t>(stream));
-}
+// One pass over a band.  d_band points at row row_begin; with d_sample_px ==
+// NULL the memory around it is the whole page (the samples are read from it).
+enum AcePass { ACE_SCORES, ACE_REFINE, ACE_SCALE };
 
-int pf_b200_dev_ace_scores(const uint32_t *d_in, int width, int height,
-		int row_begin, int row_end,
-		const int *d_samples, int nb_samples, double slope, double limit,
-		double *d_scores, double *d_minmax, void *stream)
-{
-	clear_error();
-	if (!d_in || !d_samples || !d_scores || !d_minmax)
-		return fail(PF_B200_EINVAL, "NULL device pointer");
-	if (width <= 0 || height <= 0)
-		return fail(PF_B200_EINVAL, "size %d x %d", width, height);
-	AceParams p = { width, height, row_begin, row_end, nb_samples, slope, limit };
-	return launch_ace_scores(d_in, d_samples, p, d_scores, d_minmax,
-			static_cast<cudaStream_t>(stream));
-}
-
-int pf_b200_dev_ace_scale(const double *d_scores, const double *d_minmax,
-		int width, int nb_rows, uint32_t *d_out_band, void *stream)
-{
-	clear_error();
-	if (!d_scores || !d_minmax || !d_out_band)
-		return fail(PF_B200_EINVAL, "NULL device pointer");
-	if (width <= 0 || nb_rows <= 0)
-		return fail(PF_B200_EINVAL, "size %d x %d", width, nb_rows);
-	return launch_ace_scale(d_scores, d_minmax, width, nb_rows, d_out_band,
-			static_cast<cudaStream_t>(stream));
-}
-
-int pf_b200_dev_ace_scale_to(const double *d_scores, const double *d_minmax,
-		int width, int nb_rows, uint32_t *const *d_outs, int nb_outs, void *stream)
-{
-	clear_error();
-	if (!d_scores || !d_minmax || !d_outs)
-		return fail(PF_B200_EINVAL, "NULL pointer");
-	if (width <= 0 || nb_rows <= 0)
-		return fail(PF_B200_EINVAL, "size %d x %d", width, nb_rows);
-	for (int i = 0; i < nb_outs && i < 16; i++)
-		if (!d_outs[i])
-			return fail(PF_B200_EINVAL, "NULL destination %d", i);
-	return launch_ace_scale_multi(d_scores, d_minmax, width, nb_rows, d_outs, nb_outs,
-			static_cast<cudaStream_t>(stream));
-}
-
-int pf_b200_dev_ace_scale_multicast(const double *d_scores, const double *d_minmax,
-		int width, int nb_rows, uint32_t *d_multicast_band, void *stream)
-{
-	clear_error();
-	if (!d_scores || !d_minmax || !d_multicast_band)
-		return fail(PF_B200_EINVAL, "NULL pointer");
-	if (width <= 0 || nb_rows <= 0)
-		return fail(PF_B200_EINVAL, "size %d x %d", width, nb_rows);
-	uint32_t *outs[1] = { d_multicast_band };
-	return launch_ace_scale_multi(d_scores, d_minmax, width, nb_rows, outs, 1,
-			static_cast<cudaStream_t>(stream), true);
-}
-
-static int ace_band_call(bool refine, const uint32_t *d_band, int width, int height,
+static int ace_band_pass(AcePass pass, const uint32_t *d_band, int width, int height,
 		int row_begin, int row_end, const int *d_samples, const uint32_t *d_sample_px,
-		int nb_samples, double slope, double limit, double *d_scores, double *d_minmax,
-		void *stream)
+		int nb_samples, double slope, double limit, void *d_scores, double *d_minmax,
+		uint32_t *const *d_outs, int nb_outs, bool multicast, void *stream)
 {
 	clear_error();
-	if (!d_band || !d_samples || !d_sample_px || !d_scores || !d_minmax)
+	if (!d_band || !d_samples || !d_scores || !d_minmax)
 		return fail(PF_B200_EINVAL, "NULL device pointer");
 	if (width <= 0 || height <= 0)
 		return fail(PF_B200_EINVAL, "size %d x %d", width, height);
 	if (row_begin < 0 || row_begin >= row_end || row_end > height)
 		return fail(PF_B200_EINVAL, "ace: bad row band [%d, %d) of %d rows", row_begin, row_end, height);
+	if ((uintptr_t)d_scores & 255)
+		return fail(PF_B200_EINVAL, "ace: the score block must be 256-byte aligned");
 	AceParams p = { width, height, row_begin, row_end, nb_samples, slope, limit };
 	p.sample_px = d_sample_px;
 	// the kernels index the page; with the samples' values given they only
 	// ever read rows [row_begin, row_end) of it
 	const uint32_t *page = d_band - (size_t)row_begin * width;
+	const AceScores sc = ace_scores_at(d_scores, (size_t)(row_end - row_begin) * width);
 	cudaStream_t st = static_cast<cudaStream_t>(stream);
-	return refine ? launch_ace_refine(page, d_samples, p, d_scores, d_minmax, st)
-	              : launch_ace_scores(page, d_samples, p, d_scores, d_minmax, st);
+	switch (pass) {
+	case ACE_SCORES:
+		return launch_ace_scores(page, d_samples, p, sc, d_minmax, st);
+	case ACE_REFINE:
+		return launch_ace_refine(page, d_samples, p, sc, d_minmax, st);
+	default:
+		break;
+	}
+	if (!d_outs)
+		return fail(PF_B200_EINVAL, "NULL pointer");
+	for (int i = 0; i < nb_outs && i < 16; i++)
+		if (!d_outs[i])
+			return fail(PF_B200_EINVAL, "NULL destination %d", i);
+	int rc = launch_ace_scale(p, sc, d_minmax, row_begin, row_end - row_begin, 0, d_outs, nb_outs,
+			multicast, st);
+	if (rc)
+		return rc;
+	return launch_ace_fixup(page, d_samples, p, sc, d_minmax, row_begin, 0, d_outs, nb_outs,
+			multicast, st);
+}
+
+int pf_b200_dev_ace_scores(const uint32_t *d_in, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, int nb_samples, double slope, double limit,
+		void *d_scores, double *d_minmax, void *stream)
+{
+	return ace_band_pass(ACE_SCORES, d_in ? d_in + (size_t)(row_begin > 0 ? row_begin : 0) * width : nullptr,
+			width, height, row_begin, row_end, d_samples, nullptr, nb_samples, slope, limit,
+			d_scores, d_minmax, nullptr, 0, false, stream);
+}
+
+int pf_b200_dev_ace_refine(const uint32_t *d_in, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, int nb_samples, double slope, double limit,
+		void *d_scores, double *d_minmax, void *stream)
+{
+	return ace_band_pass(ACE_REFINE, d_in ? d_in + (size_t)(row_begin > 0 ? row_begin : 0) * width : nullptr,
+			width, height, row_begin, row_end, d_samples, nullptr, nb_samples, slope, limit,
+			d_scores, d_minmax, nullptr, 0, false, stream);
+}
+
+int pf_b200_dev_ace_scale(const uint32_t *d_in, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, int nb_samples, double slope, double limit,
+		void *d_scores, double *d_minmax, uint32_t *d_out_band, void *stream)
+{
+	uint32_t *outs[1] = { d_out_band };
+	return ace_band_pass(ACE_SCALE, d_in ? d_in + (size_t)(row_begin > 0 ? row_begin : 0) * width : nullptr,
+			width, height, row_begin, row_end, d_samples, nullptr, nb_samples, slope, limit,
+			d_scores, d_minmax, outs, 1, false, stream);
 }
 
 int pf_b200_dev_ace_scores_band(const uint32_t *d_band, int width, int height,
 		int row_begin, int row_end,
 		const int *d_samples, const uint32_t *d_sample_px, int nb_samples,
-		double slope, double limit, double *d_scores, double *d_minmax, void *stream)
+		double slope, double limit, void *d_scores, double *d_minmax, void *stream)
 {
-	return ace_band_call(false, d_band, width, height, row_begin, row_end, d_samples, d_sample_px,
-			nb_samples, slope, limit, d_scores, d_minmax, stream);
+	if (!d_sample_px)
+		return fail(PF_B200_EINVAL, "NULL device pointer");
+	return ace_band_pass(ACE_SCORES, d_band, width, height, row_begin, row_end, d_samples, d_sample_px,
+			nb_samples, slope, limit, d_scores, d_minmax, nullptr, 0, false, stream);
 }
 
 int pf_b200_dev_ace_refine_band(const uint32_t *d_band, int width, int height,
 		int row_begin, int row_end,
 		const int *d_samples, const uint32_t *d_sample_px, int nb_samples,
-		double slope, double limit, double *d_scores, double *d_minmax, void *stream)
+		double slope, double limit, void *d_scores, double *d_minmax, void *stream)
 {
-	return ace_band_call(true, d_band, width, height, row_begin, row_end, d_samples, d_sample_px,
-			nb_samples, slope, limit, d_scores, d_minmax, stream);
+	if (!d_sample_px)
+		return fail(PF_B200_EINVAL, "NULL device pointer");
+	return ace_band_pass(ACE_REFINE, d_band, width, height, row_begin, row_end, d_samples, d_sample_px,
+			nb_samples, slope, limit, d_scores, d_minmax, nullptr, 0, false, stream);
+}
+
+int pf_b200_dev_ace_scale_band(const uint32_t *d_band, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, const uint32_t *d_sample_px, int nb_samples,
+		double slope, double limit, void *d_scores, double *d_minmax,
+		uint32_t *d_out_band, void *stream)
+{
+	if (!d_sample_px)
+		return fail(PF_B200_EINVAL, "NULL device pointer");
+	uint32_t *outs[1] = { d_out_band };
+	return ace_band_pass(ACE_SCALE, d_band, width, height, row_begin, row_end, d_samples, d_sample_px,
+			nb_samples, slope, limit, d_scores, d_minmax, outs, 1, false, stream);
+}
+
+int pf_b200_dev_ace_scale_to(const uint32_t *d_band, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, const uint32_t *d_sample_px, int nb_samples,
+		double slope, double limit, void *d_scores, double *d_minmax,
+		uint32_t *const *d_outs, int nb_outs, void *stream)
+{
+	return ace_band_pass(ACE_SCALE, d_band, width, height, row_begin, row_end, d_samples, d_sample_px,
+			nb_samples, slope, limit, d_scores, d_minmax, d_outs, nb_outs, false, stream);
+}
+
+int pf_b200_dev_ace_scale_multicast(const uint32_t *d_band, int width, int height,
+		int row_begin, int row_end,
+		const int *d_samples, const uint32_t *d_sample_px, int nb_samples,
+		double slope, double limit, void *d_scores, double *d_minmax,
+		uint32_t *d_multicast_band, void *stream)
+{
+	uint32_t *outs[1] = { d_multicast_band };
+	return ace_band_pass(ACE_SCALE, d_band, width, height, row_begin, row_end, d_samples, d_sample_px,
+			nb_samples, slope, limit, d_scores, d_minmax, outs, 1, true, stream);
 }
 
 size_t pf_b200_ace_workspace_bytes(int width, int height)
@@ -1428,8 +1461,7 @@ size_t pf_b200_ace_workspace_bytes(int width, int height)
 		fail(PF_B200_EINVAL, "size %d x %d", width, height);
 		return 0;
 	}
-	const size_t scores = 3 * sizeof(double) * (size_t)width * height;
-	return (scores + 255) / 256 * 256 + ace_minmax_doubles(width, height) * sizeof(double);
+	return ace_scores_bytes(width, height) + ace_minmax_doubles(width, height) * sizeof(double);
 }
 
 int pf_b200_dev_ace(const uint32_t *d_in, uint32_t *d_out, int width, int height,
@@ -1447,15 +1479,16 @@ int pf_b200_dev_ace(const uint32_t *d_in, uint32_t *d_out, int width, int height
 		return fail(PF_B200_EINVAL, "ace: work area of %zu bytes, need %zu, 256-byte aligned",
 				workspace_bytes, pf_b200_ace_workspace_bytes(width, height));
 	cudaStream_t st = static_cast<cudaStream_t>(stream);
-	double *scores = static_cast<double *>(d_workspace);
-	const size_t score_bytes = (3 * sizeof(double) * (size_t)width * height + 255) / 256 * 256;
-	double *minmax = reinterpret_cast<double *>(static_cast<char *>(d_workspace) + score_bytes);
+	const AceScores sc = ace_scores_at(d_workspace, (size_t)width * height);
+	double *minmax = reinterpret_cast<double *>(static_cast<char *>(d_workspace)
+			+ ace_scores_bytes(width, height));
 	AceParams p = { width, height, 0, height, nb_samples, slope, limit };
 	int rc;
 	if ((rc = launch_ace_minmax_init(minmax, width, height, st))
-			|| (rc = launch_ace_scores(d_in, d_samples, p, scores, minmax, st))
-			|| (rc = launch_ace_refine(d_in, d_samples, p, scores, minmax, st))
-			|| (rc = launch_ace_scale(scores, minmax, width, height, d_out, st)))
+			|| (rc = launch_ace_scores(d_in, d_samples, p, sc, minmax, st))
+			|| (rc = launch_ace_refine(d_in, d_samples, p, sc, minmax, st))
+			|| (rc = launch_ace_scale(p, sc, minmax, 0, height, 0, &d_out, 1, false, st))
+			|| (rc = launch_ace_fixup(d_in, d_samples, p, sc, minmax, 0, 0, &d_out, 1, false, st)))
 		return rc;
 	return PF_B200_OK;
 }
@@ -1466,6 +1499,14 @@ double pf_b200_fp64_peak_tflops(void)
 	if (pf_b200_device_count() <= 0)
 		return -(double)fail(PF_B200_ENODEV, "no CUDA device");
 	return measure_fp64_peak_tflops();
+}
+
+double pf_b200_fp32_peak_tflops(void)
+{
+	clear_error();
+	if (pf_b200_device_count() <= 0)
+		return -(double)fail(PF_B200_ENODEV, "no CUDA device");
+	return measure_fp32_peak_tflops();
 }
 
 }  // extern "C"

@@ -111,33 +111,57 @@ struct AceParams {
 	int row_begin, row_end;
 	int nb_samples;
 	double slope, limit;
-	// Optional (host-pointer streaming path): the samples' pixel values, so
-	// that the accumulation of a band does not need the rest of the page;
-	// NULL = read them from the page.
+	// Optional (host-pointer streaming path, row bands on other GPUs): the
+	// samples' pixel values, so that the passes over a band do not need the
+	// rest of the page; NULL = read them from the page.
 	const uint32_t *sample_px = nullptr;
-	// Where score row `score_row0` lives and how far apart the planes are.
-	// Defaults (< 0): a band-local buffer, row_begin first, planes of
-	// (row_end-row_begin)*w doubles.
+	// Which score row is stored first in the score block and how far apart the
+	// planes are.  Defaults (< 0): a band-local block, row_begin first, planes
+	// of (row_end-row_begin)*w floats.
 	int score_row0 = -1;
 	long score_plane = -1;
 };
+
+// A score block (device memory, ace_scores_bytes(w, rows) bytes, 256-byte
+// aligned): a header with the lengths of the fix-up lists, the R, G, B score
+// planes (FP32), and room for the fix-up list (one entry per pixel at most).
+// A rescale call appends to the list of one slot; slots used on one block must
+// cover disjoint rows (a slot's list starts at its first row's pixel index).
+constexpr int kAceScoreHeader = 256;     // bytes
+constexpr int kAceFixupSlots = 16;
+struct AceScores {
+	int *counts;         // kAceFixupSlots list lengths, then as many tickets; the accumulation pass zeroes them, the fix-up pass leaves them zero
+	float *planes;
+	uint32_t *list;
+	size_t plane;        // floats between planes = capacity of the list
+};
+size_t ace_scores_bytes(int w, int rows);
+AceScores ace_scores_at(void *block, size_t plane);
+
 // `minmax` is a block of ace_minmax_doubles(w, h) doubles: the page-wide
 // extremes first, then one entry per tile (pf_ace.cu, kMinmaxHead).
 size_t ace_minmax_doubles(int w, int h);
 int launch_ace_minmax_init(double *minmax, int w, int h, cudaStream_t st);
+// Pass 1, rows [row_begin, row_end): approximate scores (error bounded) into
+// the planes, their extremes folded into minmax[0..5] and the tile table.
 int launch_ace_scores(const uint32_t *in, const int *samples_xy,
-		const AceParams &p, double *scores, double *minmax, cudaStream_t st);
-// After launch_ace_scores of every band (and, across GPUs, the min/max
-// exchange), same parameters: recomputes the scores at the page's extremes in
-// the reference's arithmetic.
+		const AceParams &p, const AceScores &sc, double *minmax, cudaStream_t st);
+// Pass 2, after pass 1 of every band (and, across GPUs, the min/max exchange),
+// same parameters: the exact extremes of the band into minmax[6..11].
 int launch_ace_refine(const uint32_t *in, const int *samples_xy,
-		const AceParams &p, double *scores, double *minmax, cudaStream_t st);
-// plane < 0: planes of rows*w doubles (a band-local buffer)
-int launch_ace_scale(const double *scores, const double *minmax, int w,
-		int rows, uint32_t *out, cudaStream_t st, long plane = -1);
-// the same rows to nb_outs images at once (band-local score planes)
-int launch_ace_scale_multi(const double *scores, const double *minmax, int w, int rows,
-		uint32_t *const *outs, int nb_outs, cudaStream_t st, bool multicast = false);
+		const AceParams &p, const AceScores &sc, double *minmax, cudaStream_t st);
+// Pass 3, after pass 2 of every band (and the second exchange): rows
+// [row0, row0 + rows) of the block rescaled to RGBA8 into nb_outs images
+// (outs[d] points at row0 of image d); uncertain pixels listed under `slot`.
+int launch_ace_scale(const AceParams &p, const AceScores &sc, const double *minmax,
+		int row0, int rows, int slot, uint32_t *const *outs, int nb_outs, bool multicast,
+		cudaStream_t st);
+// Pass 4, same row0 / slot / outs: the listed pixels recomputed in the
+// reference's arithmetic and stored again.
+int launch_ace_fixup(const uint32_t *in, const int *samples_xy, const AceParams &p,
+		const AceScores &sc, const double *minmax, int row0, int slot,
+		uint32_t *const *outs, int nb_outs, bool multicast, cudaStream_t st);
 double measure_fp64_peak_tflops();
+double measure_fp32_peak_tflops();
 
 }  // namespace pfb

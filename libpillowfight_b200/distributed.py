@@ -33,7 +33,10 @@ def page_shard(n_pages, world, rank):
 
 
 class CudaAceCompute:
-    """ACE band arithmetic on the current CUDA device through the C-ABI."""
+    """ACE band arithmetic on the current CUDA device through the C-ABI.
+
+    A band's `scores` is its score block (include/pillowfight_b200.h): an
+    opaque uint8 CUDA tensor of pf_b200_ace_scores_bytes(width, rows) bytes."""
 
     def __init__(self):
         from . import _capi
@@ -42,19 +45,28 @@ class CudaAceCompute:
 
     def new_minmax(self, device, width, height):
         """The min/max block of one page (include/pillowfight_b200.h): [0:3]
-        min, [3:6] max of the scores, [6:9], [9:12] of the refined ones."""
+        min, [3:6] max of the approximate scores, [6:9], [9:12] the exact ones."""
         n = self._lib.pf_b200_ace_minmax_bytes(width, height) // 8
         mm = torch.empty(n, dtype=torch.float64, device=device)
         st = torch.cuda.current_stream().cuda_stream
         self._capi.check(self._lib.pf_b200_dev_ace_minmax_init(mm.data_ptr(), width, height, st))
         return mm
 
-    def scores(self, page, xy, slope, limit, band, minmax):
+    def new_scores(self, device, width, rows):
+        return torch.empty(self._lib.pf_b200_ace_scores_bytes(width, rows), dtype=torch.uint8,
+                           device=device)
+
+    @staticmethod
+    def score_planes(scores, width, rows):
+        """The three FP32 score planes inside a score block, (3, rows, W)."""
+        return scores[256:256 + 12 * width * rows].view(torch.float32).view(3, rows, width)
+
+    def scores(self, page, xy, slope, limit, band, minmax, out=None):
         """page: (H, W, 4) uint8 CUDA tensor; xy: int32 CUDA tensor (2N);
-        returns (3, rows, W) float64 scores, folds min/max into `minmax`."""
+        returns the band's score block, folds min/max into `minmax`."""
         h, w = page.shape[0], page.shape[1]
         b0, b1 = band
-        out = torch.empty((3, b1 - b0, w), dtype=torch.float64, device=page.device)
+        out = out if out is not None else self.new_scores(page.device, w, b1 - b0)
         st = torch.cuda.current_stream().cuda_stream
         self._capi.check(self._lib.pf_b200_dev_ace_scores(
             page.data_ptr(), w, h, b0, b1, xy.data_ptr(), xy.numel() // 2,
@@ -62,8 +74,8 @@ class CudaAceCompute:
         return out
 
     def refine(self, page, xy, slope, limit, band, scores, minmax):
-        """Recomputes the band's scores at the page's extremes exactly; their
-        min/max go to minmax[6:12].  True: those need the exchange too."""
+        """The band's part of the exact extremes, into minmax[6:12].  True:
+        those need the exchange too."""
         h, w = page.shape[0], page.shape[1]
         st = torch.cuda.current_stream().cuda_stream
         self._capi.check(self._lib.pf_b200_dev_ace_refine(
@@ -77,11 +89,11 @@ class CudaAceCompute:
         idx = xy[1::2].long() * page.shape[1] + xy[0::2].long()
         return px.index_select(0, idx).contiguous()
 
-    def scores_band(self, rows, height, band, xy, spx, slope, limit, minmax):
+    def scores_band(self, rows, height, band, xy, spx, slope, limit, minmax, out=None):
         """rows: (b1-b0, W, 4) uint8 CUDA tensor holding only the band."""
         b0, b1 = band
         w = rows.shape[1]
-        out = torch.empty((3, b1 - b0, w), dtype=torch.float64, device=rows.device)
+        out = out if out is not None else self.new_scores(rows.device, w, b1 - b0)
         st = torch.cuda.current_stream().cuda_stream
         self._capi.check(self._lib.pf_b200_dev_ace_scores_band(
             rows.data_ptr(), w, height, b0, b1, xy.data_ptr(), spx.data_ptr(), xy.numel() // 2,
@@ -96,12 +108,24 @@ class CudaAceCompute:
             xy.numel() // 2, float(slope), float(limit), scores.data_ptr(), minmax.data_ptr(), st))
         return True
 
-    def scale(self, scores, minmax):
-        rows, w = scores.shape[1], scores.shape[2]
-        out = torch.empty((rows, w, 4), dtype=torch.uint8, device=scores.device)
+    def scale(self, page, xy, slope, limit, band, scores, minmax):
+        """The band's rows of the result, (rows, W, 4) uint8."""
+        h, w = page.shape[0], page.shape[1]
+        out = torch.empty((band[1] - band[0], w, 4), dtype=torch.uint8, device=page.device)
         st = torch.cuda.current_stream().cuda_stream
         self._capi.check(self._lib.pf_b200_dev_ace_scale(
-            scores.data_ptr(), minmax.data_ptr(), w, rows, out.data_ptr(), st))
+            page.data_ptr(), w, h, band[0], band[1], xy.data_ptr(), xy.numel() // 2,
+            float(slope), float(limit), scores.data_ptr(), minmax.data_ptr(), out.data_ptr(), st))
+        return out
+
+    def scale_band(self, rows, height, band, xy, spx, slope, limit, scores, minmax):
+        w = rows.shape[1]
+        out = torch.empty((band[1] - band[0], w, 4), dtype=torch.uint8, device=rows.device)
+        st = torch.cuda.current_stream().cuda_stream
+        self._capi.check(self._lib.pf_b200_dev_ace_scale_band(
+            rows.data_ptr(), w, height, band[0], band[1], xy.data_ptr(), spx.data_ptr(),
+            xy.numel() // 2, float(slope), float(limit), scores.data_ptr(), minmax.data_ptr(),
+            out.data_ptr(), st))
         return out
 
 
@@ -117,7 +141,7 @@ def ace_sharded(page, xy, slope, limit, compute, group=None, src=0):
     if world == 1:
         scores = compute.scores(page, xy, slope, limit, (0, h), minmax)
         compute.refine(page, xy, slope, limit, (0, h), scores, minmax)
-        return compute.scale(scores, minmax)
+        return compute.scale(page, xy, slope, limit, (0, h), scores, minmax)
 
     bands = row_bands(h, world)
     max_rows = max(b1 - b0 for b0, b1 in bands)
@@ -149,7 +173,7 @@ def ace_sharded(page, xy, slope, limit, compute, group=None, src=0):
     if compute.refine_band(rows, h, (b0, b1), xy, spx, slope, limit, scores, minmax):
         dist.all_reduce(minmax[6:9], op=dist.ReduceOp.MIN, group=group)
         dist.all_reduce(minmax[9:12], op=dist.ReduceOp.MAX, group=group)
-    band = compute.scale(scores, minmax)
+    band = compute.scale_band(rows, h, (b0, b1), xy, spx, slope, limit, scores, minmax)
     out = torch.empty((h, w, 4), dtype=torch.uint8, device=page.device)
     if h % world == 0:
         # equal bands: gather straight into the result
@@ -228,18 +252,18 @@ class AcePeerBands:
         self._exchange(minmax, 6)
         st = torch.cuda.current_stream().cuda_stream
         mc = self._ho.multicast_ptr if self.use_multicast else 0
+        args = (rows.data_ptr(), w, h, b0, b1, xy.data_ptr(), spx.data_ptr(), n, float(slope),
+                float(limit), scores.data_ptr(), minmax.data_ptr())
         if mc:
             # one multimem.st per 16 bytes: the NVSwitch delivers the band to all GPUs
-            self._capi.check(self._lib.pf_b200_dev_ace_scale_multicast(
-                scores.data_ptr(), minmax.data_ptr(), w, b1 - b0, mc + b0 * w * 4, st))
+            self._capi.check(self._lib.pf_b200_dev_ace_scale_multicast(*args, mc + b0 * w * 4, st))
         else:
             import ctypes
             if self._dests is None:          # own image first, then the peers'
                 order = [self.rank] + [r for r in range(self.world) if r != self.rank]
                 self._dests = [self._ho.get_buffer(r, (h, w, 4), torch.uint8)[b0:b1] for r in order]
             ptrs = (ctypes.c_void_p * len(self._dests))(*[d.data_ptr() for d in self._dests])
-            self._capi.check(self._lib.pf_b200_dev_ace_scale_to(
-                scores.data_ptr(), minmax.data_ptr(), w, b1 - b0, ptrs, len(self._dests), st))
+            self._capi.check(self._lib.pf_b200_dev_ace_scale_to(*args, ptrs, len(self._dests), st))
         self._ho.barrier()          # every band has landed everywhere
         return self.out
 

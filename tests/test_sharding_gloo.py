@@ -52,7 +52,13 @@ class OracleAceCompute:
             minmax[3 + c] = max(float(minmax[3 + c]), float(np.nanmax(s[c])))
         return torch.from_numpy(np.ascontiguousarray(s))
 
-    def scale(self, scores, minmax):
+    def scale(self, page, xy, slope, limit, band, scores, minmax):
+        return self._scale(scores, minmax)
+
+    def scale_band(self, rows, height, band, xy, spx, slope, limit, scores, minmax):
+        return self._scale(scores, minmax)
+
+    def _scale(self, scores, minmax):
         s = scores.numpy()
         mn = minmax[:3].numpy()[:, None, None]
         mx = minmax[3:6].numpy()[:, None, None]

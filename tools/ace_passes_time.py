@@ -17,11 +17,11 @@ lib, chk = _capi.lib, _capi.check
 pages = [torch.from_numpy(synthetic_page(w, h, i)).to(dev) for i in range(4)]
 out = torch.empty_like(pages[0])
 xy = xy_tensor(pf.ace_samples(100, w, h, 12345), dev)
-scores = torch.empty((3, h, w), dtype=torch.float64, device=dev)
+scores = torch.empty(lib.pf_b200_ace_scores_bytes(w, h), dtype=torch.uint8, device=dev)
 mm = torch.empty(lib.pf_b200_ace_minmax_bytes(w, h) // 8, dtype=torch.float64, device=dev)
 st = torch.cuda.current_stream().cuda_stream
 args = lambda p: (p.data_ptr(), w, h, 0, h, xy.data_ptr(), 100, 10.0, 1000.0, scores.data_ptr(), mm.data_ptr(), st)
-names = ["init", "scores", "refine", "scale"]
+names = ["init", "scores", "refine", "scale+fixup"]
 tot = np.zeros(4)
 reps = 12
 for it in range(reps + 3):
@@ -31,15 +31,15 @@ for it in range(reps + 3):
     chk(lib.pf_b200_dev_ace_minmax_init(mm.data_ptr(), w, h, st)); ev[1].record()
     chk(lib.pf_b200_dev_ace_scores(*args(p))); ev[2].record()
     chk(lib.pf_b200_dev_ace_refine(*args(p))); ev[3].record()
-    chk(lib.pf_b200_dev_ace_scale(scores.data_ptr(), mm.data_ptr(), w, h, out.data_ptr(), st)); ev[4].record()
+    chk(lib.pf_b200_dev_ace_scale(*args(p)[:-1], out.data_ptr(), st)); ev[4].record()
     torch.cuda.synchronize()
     if it >= 3:
         tot += [ev[i].elapsed_time(ev[i + 1]) for i in range(4)]
     if it == 3:
         m = mm.cpu().numpy()
         tiles = m[12:].reshape(-1, 6)
-        span = m[3:6] - m[0:3]
-        wanted = ((tiles[:, :3] <= m[0:3] + span * 2.0 ** -15) | (tiles[:, 3:] >= m[3:6] - span * 2.0 ** -15)).any(1)
-        print("fast min/max", m[:6], "refined", m[6:12], "tiles wanted", int(wanted.sum()), "of", len(tiles))
+        thr = 2 * 8e-6
+        wanted = ((tiles[:, :3] <= m[0:3] + thr) | (tiles[:, 3:] >= m[3:6] - thr)).any(1)
+        print("fast min/max", m[:6], "exact", m[6:12], "tiles wanted", int(wanted.sum()), "of", len(tiles))
 for n, t in zip(names, tot / reps):
-    print("%-7s %.4f ms" % (n, t))
+    print("%-12s %.4f ms" % (n, t))

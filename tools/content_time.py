@@ -35,7 +35,7 @@ contents = {"texture": np.ascontiguousarray(texture), "synthetic": synthetic_pag
             "white": white, "flat gray": gray, "text on white": text}
 out = torch.empty((h, w, 4), dtype=torch.uint8, device=dev)
 scratch = torch.empty(lib.pf_b200_canny_scratch_bytes(w, h), dtype=torch.uint8, device=dev)
-scores = torch.empty((3, h, w), dtype=torch.float64, device=dev)
+scores = torch.empty(lib.pf_b200_ace_scores_bytes(w, h), dtype=torch.uint8, device=dev)
 mm = torch.empty(lib.pf_b200_ace_minmax_bytes(w, h) // 8, dtype=torch.float64, device=dev)
 xy = xy_tensor(pf.ace_samples(100, w, h, 12345), dev)
 
@@ -53,7 +53,7 @@ def timed(fn, n=20):
     return a.elapsed_time(b) / n * 1e3
 
 
-print("%-14s %9s %9s %9s %9s %9s %9s  (us)" % ("content", "gaussian", "sobel", "canny", "ace", "refine", "scale"))
+print("%-14s %9s %9s %9s %9s %9s %9s  (us)" % ("content", "gaussian", "sobel", "canny", "ace", "refine", "scale+fix"))
 for name, arr in contents.items():
     page = torch.from_numpy(arr).to(dev)
     ace_args = (page.data_ptr(), w, h, 0, h, xy.data_ptr(), 100, 10.0, 1000.0, scores.data_ptr(), mm.data_ptr(), st)
@@ -69,7 +69,7 @@ for name, arr in contents.items():
                                                  scratch.numel(), st))),
          timed(ace_all),
          timed(lambda: chk(lib.pf_b200_dev_ace_refine(*ace_args))),
-         timed(lambda: chk(lib.pf_b200_dev_ace_scale(scores.data_ptr(), mm.data_ptr(), w, h, out.data_ptr(), st)))]
+         timed(lambda: chk(lib.pf_b200_dev_ace_scale(*ace_args[:-1], out.data_ptr(), st)))]
     import ctypes
     hdr = torch.zeros(2, dtype=torch.int32)
     hdr.copy_(scratch[:8].view(torch.int32))

@@ -116,10 +116,10 @@ def run(cases, seed, pinned=False):
                 xyp = xy.ctypes.data_as(ctypes.POINTER(ctypes.c_int))
                 checks.append(("ace(%g,%g,%d)" % (slope, limit, ns),
                                lambda: pin.call(pin.lib.pf_b200_ace, img, ns, xyp, slope, limit),
-                               lambda: o.ace_with_samples(img, xy, slope, limit, nb_threads=8), 1))
+                               lambda: o.ace_with_samples(img, xy, slope, limit, nb_threads=8), 0))
             else:
                 checks.append(("ace(%g,%g,%d)" % (slope, limit, ns), lambda: pf.ace(img, slope, limit, ns, seed=seed),
-                               lambda: o.ace_with_samples(img, xy, slope, limit, nb_threads=4), 1))
+                               lambda: o.ace_with_samples(img, xy, slope, limit, nb_threads=4), 0))
         for name, fg, fr, tol in checks:
             got, ref = fg(), fr()
             d = np.abs(got.astype(np.int16) - ref.astype(np.int16))

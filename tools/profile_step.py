@@ -19,7 +19,7 @@ page = torch.from_numpy(synthetic_page(w, h, 0)).to(dev)
 out = torch.empty_like(page)
 out2 = torch.empty_like(page)
 xy = xy_tensor(pf.ace_samples(100, w, h, 12345), dev)
-scores = torch.empty((3, h, w), dtype=torch.float64, device=dev)
+scores = torch.empty(lib.pf_b200_ace_scores_bytes(w, h), dtype=torch.uint8, device=dev)
 mm = torch.empty(lib.pf_b200_ace_minmax_bytes(w, h) // 8, dtype=torch.float64, device=dev)
 scratch = torch.empty(lib.pf_b200_canny_scratch_bytes(w, h), dtype=torch.uint8, device=dev)
 st = torch.cuda.current_stream().cuda_stream
@@ -29,7 +29,8 @@ for _ in range(reps):
                                    scores.data_ptr(), mm.data_ptr(), st))
     chk(lib.pf_b200_dev_ace_refine(page.data_ptr(), w, h, 0, h, xy.data_ptr(), 100, 10.0, 1000.0,
                                    scores.data_ptr(), mm.data_ptr(), st))
-    chk(lib.pf_b200_dev_ace_scale(scores.data_ptr(), mm.data_ptr(), w, h, out.data_ptr(), st))
+    chk(lib.pf_b200_dev_ace_scale(page.data_ptr(), w, h, 0, h, xy.data_ptr(), 100, 10.0, 1000.0,
+                                  scores.data_ptr(), mm.data_ptr(), out.data_ptr(), st))
     chk(lib.pf_b200_dev_gaussian(page.data_ptr(), out.data_ptr(), w, h, 2.0, 5, st))
     chk(lib.pf_b200_dev_sobel(out.data_ptr(), out2.data_ptr(), w, h, st))
     chk(lib.pf_b200_dev_canny(page.data_ptr(), out.data_ptr(), w, h, 1, scratch.data_ptr(),

@@ -231,6 +231,185 @@ proto_kernel(const uint32_t *__restrict__ in, const int2 *__restrict__ sxy, cons
 	}
 }
 
+__device__ __forceinline__ float fma_sat(float a, float b, float c)
+{
+	float d;
+	asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+	return d;
+}
+
+struct EntryF { float sx; float b[3]; };
+
+template <int P>
+struct SharedF {
+	EntryF tbl[kChunk];
+	float dy2[kChunk * P];
+	int sy[kChunk];
+};
+
+// The clamp on the FMA pipe: u' = sat(p * inv + (0.5 - s * inv)) = clamp((p - s + L) / 2L, 0, 1)
+// with inv = (1 + 2^-22) / 2L, so that p - s >= L gives exactly 1, p - s <= -L exactly 0 and
+// p == s exactly 0.5.  ACC2: accumulate with FFMA2 over row pairs, else scalar FFMA.
+// NALU: that many of the three channels use the integer clamp (ALU pipe) instead.
+template <int P, bool ACC2, int MINB, int UNROLL, int NALU>
+__global__ void __launch_bounds__(kBlock, MINB)
+sat_kernel(const uint32_t *__restrict__ in, const int2 *__restrict__ sxy, const uint32_t *__restrict__ spx,
+		int w, int h, int n, int clamp_l, float *__restrict__ scores)
+{
+	extern __shared__ __align__(16) unsigned char raw[];
+	SharedF<P> &sh = *reinterpret_cast<SharedF<P> *>(raw);
+	const int x = blockIdx.x * kBlock + threadIdx.x;
+	const int xc = min(x, w - 1);
+	const int tile_rows = 16;
+	const int ty0 = blockIdx.y * tile_rows, ty1 = min(h, ty0 + tile_rows);
+	const int npad = (n + UNROLL - 1) / UNROLL * UNROLL;
+	const float inv = (float)((1.0 + 0x1p-22) / (2.0 * clamp_l));
+	for (int k = threadIdx.x; k < npad; k += kBlock) {
+		if (k < n) {
+			const int2 s = sxy[k];
+			const uint32_t px = spx[k];
+			sh.tbl[k].sx = (float)s.x;
+			sh.sy[k] = s.y;
+			for (int c = 0; c < 3; c++)
+				sh.tbl[k].b[c] = (float)(0.5 - (double)((px >> (8 * c)) & 0xFF) * (double)inv);
+		} else {
+			sh.tbl[k].sx = 0.f;
+			sh.sy[k] = 1 << 30;
+			for (int c = 0; c < 3; c++)
+				sh.tbl[k].b[c] = 0.f;
+		}
+	}
+	const float fx = (float)x;
+	const size_t plane = (size_t)w * h;
+	for (int y0 = ty0; y0 < ty1; y0 += P) {
+		float pv[P][3];
+#pragma unroll
+		for (int r = 0; r < P; r++) {
+			const uint32_t p = __ldg(in + (size_t)min(y0 + r, h - 1) * w + xc);
+#pragma unroll
+			for (int c = 0; c < 3; c++)
+				pv[r][c] = (float)((p >> (8 * c)) & 0xFF);
+		}
+		__syncthreads();
+		for (int j = threadIdx.x; j < npad; j += kBlock) {
+#pragma unroll
+			for (int r = 0; r < P; r++) {
+				const int sy = sh.sy[j];
+				const float dy = (float)(y0 + r - sy);
+				sh.dy2[j * P + r] = (sy == (1 << 30)) ? __int_as_float(0x7f800000) : dy * dy;
+			}
+		}
+		__syncthreads();
+		if (!ACC2) {
+			float S[P][4], c4[P][4];
+#pragma unroll
+			for (int r = 0; r < P; r++)
+#pragma unroll
+				for (int c = 0; c < 4; c++)
+					S[r][c] = 0.f;
+			for (int j0 = 0; j0 < npad; j0 += 16) {
+#pragma unroll
+				for (int r = 0; r < P; r++)
+#pragma unroll
+					for (int c = 0; c < 4; c++)
+						c4[r][c] = 0.f;
+				const int j1 = min(npad, j0 + 16);
+#pragma unroll UNROLL
+				for (int j = j0; j < j1; j++) {
+					const EntryF se = sh.tbl[j];
+					const float dx = fx - se.sx;
+					const float dx2 = dx * dx;
+#pragma unroll
+					for (int r = 0; r < P; r++) {
+						const float wv = rsqrt_f32(dx2 + sh.dy2[j * P + r]);
+						c4[r][3] += wv;
+#pragma unroll
+						for (int c = 0; c < 3; c++)
+							c4[r][c] = fmaf(wv, fma_sat(pv[r][c], inv, se.b[c]), c4[r][c]);
+					}
+				}
+#pragma unroll
+				for (int r = 0; r < P; r++)
+#pragma unroll
+					for (int c = 0; c < 4; c++)
+						S[r][c] += c4[r][c];
+			}
+#pragma unroll
+			for (int r = 0; r < P; r++) {
+				const int y = y0 + r;
+				if (y < ty1 && x < w) {
+					const float den = 0.5f * S[r][3];
+#pragma unroll
+					for (int c = 0; c < 3; c++)
+						scores[c * plane + (size_t)y * w + x] = __fdiv_rn(S[r][c] - den, den);
+				}
+			}
+		} else {
+			unsigned long long S[P / 2][4], c4[P / 2][4];
+#pragma unroll
+			for (int r = 0; r < P / 2; r++)
+#pragma unroll
+				for (int c = 0; c < 4; c++)
+					S[r][c] = 0ull;
+			for (int j0 = 0; j0 < npad; j0 += 16) {
+#pragma unroll
+				for (int r = 0; r < P / 2; r++)
+#pragma unroll
+					for (int c = 0; c < 4; c++)
+						c4[r][c] = 0ull;
+				const int j1 = min(npad, j0 + 16);
+#pragma unroll UNROLL
+				for (int j = j0; j < j1; j++) {
+					const EntryF se = sh.tbl[j];
+					const float dx = fx - se.sx;
+					const float dx2 = dx * dx;
+					const unsigned long long dx22 = pack2(dx2, dx2);
+#pragma unroll
+					for (int r = 0; r < P / 2; r++) {
+						const unsigned long long dy22 = *reinterpret_cast<const unsigned long long *>(&sh.dy2[j * P + 2 * r]);
+						const unsigned long long d2 = fadd2(dx22, dy22);
+						float da, db;
+						unpack2(d2, da, db);
+						const unsigned long long wv = pack2(rsqrt_f32(da), rsqrt_f32(db));
+						c4[r][3] = fadd2(c4[r][3], wv);
+#pragma unroll
+						for (int c = 0; c < 3; c++) {
+							if (c < NALU) {      // timing experiment only: integer clamp on the ALU pipe
+								const int ua = __viaddmin_s32_relu(__float_as_int(pv[2 * r][c]), __float_as_int(se.b[c]), clamp_l);
+								const int ub = __viaddmin_s32_relu(__float_as_int(pv[2 * r + 1][c]), __float_as_int(se.b[c]), clamp_l);
+								c4[r][c] = ffma2(wv, pack2(__int_as_float(ua), __int_as_float(ub)), c4[r][c]);
+							} else {
+								c4[r][c] = ffma2(wv, pack2(fma_sat(pv[2 * r][c], inv, se.b[c]),
+										fma_sat(pv[2 * r + 1][c], inv, se.b[c])), c4[r][c]);
+							}
+						}
+					}
+				}
+#pragma unroll
+				for (int r = 0; r < P / 2; r++)
+#pragma unroll
+					for (int c = 0; c < 4; c++)
+						S[r][c] = fadd2(S[r][c], c4[r][c]);
+			}
+#pragma unroll
+			for (int r = 0; r < P / 2; r++) {
+				float t0, t1;
+				unpack2(S[r][3], t0, t1);
+#pragma unroll
+				for (int c = 0; c < 3; c++) {
+					float a0, a1;
+					unpack2(S[r][c], a0, a1);
+					const int y = y0 + 2 * r;
+					if (y < ty1 && x < w)
+						scores[c * plane + (size_t)y * w + x] = __fdiv_rn(a0 - 0.5f * t0, 0.5f * t0);
+					if (y + 1 < ty1 && x < w)
+						scores[c * plane + (size_t)(y + 1) * w + x] = __fdiv_rn(a1 - 0.5f * t1, 0.5f * t1);
+				}
+			}
+		}
+	}
+}
+
 // exhaustive accuracy of rsqrt.approx.f32 over two binades (odd and even exponent)
 __global__ void rsqrt_err_kernel(float *worst)
 {
@@ -244,12 +423,10 @@ __global__ void rsqrt_err_kernel(float *worst)
 	atomicMax(reinterpret_cast<int *>(worst), __float_as_int(mx));
 }
 
-template <int P, int MODE, int FLUSH, int MINB>
-void run(const char *name, const uint32_t *d_in, const int2 *d_xy, const uint32_t *d_spx, int w, int h, int n,
+template <typename K>
+void run_k(const char *name, K kern, size_t smem, const uint32_t *d_in, const int2 *d_xy, const uint32_t *d_spx, int w, int h, int n,
 		float *d_scores, const std::vector<uint32_t> &page, const std::vector<int2> &xy, bool check = true)
 {
-	auto kern = proto_kernel<P, MODE, FLUSH, MINB>;
-	const size_t smem = sizeof(Shared<P>);
 	cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 	dim3 grid((w + kBlock - 1) / kBlock, (h + 15) / 16);
 	cudaFuncAttributes fa;
@@ -301,6 +478,20 @@ void run(const char *name, const uint32_t *d_in, const int2 *d_xy, const uint32_
 			worst, cudaGetErrorString(err));
 }
 
+template <int P, int MODE, int FLUSH, int MINB>
+void run(const char *name, const uint32_t *d_in, const int2 *d_xy, const uint32_t *d_spx, int w, int h, int n,
+		float *d_scores, const std::vector<uint32_t> &page, const std::vector<int2> &xy, bool check = true)
+{
+	run_k(name, proto_kernel<P, MODE, FLUSH, MINB>, sizeof(Shared<P>), d_in, d_xy, d_spx, w, h, n, d_scores, page, xy, check);
+}
+
+template <int P, bool ACC2, int MINB, int UNROLL, int NALU = 0>
+void run_sat(const char *name, const uint32_t *d_in, const int2 *d_xy, const uint32_t *d_spx, int w, int h, int n,
+		float *d_scores, const std::vector<uint32_t> &page, const std::vector<int2> &xy, bool check = true)
+{
+	run_k(name, sat_kernel<P, ACC2, MINB, UNROLL, NALU>, sizeof(SharedF<P>), d_in, d_xy, d_spx, w, h, n, d_scores, page, xy, check);
+}
+
 int main(int argc, char **argv)
 {
 	const int w = 2480, h = 3508;
@@ -328,7 +519,12 @@ int main(int argc, char **argv)
 	cudaMemcpy(d_spx, spx.data(), n * 4, cudaMemcpyHostToDevice);
 	cudaMemcpy(d_xy, xy.data(), n * 8, cudaMemcpyHostToDevice);
 	if (one) {
-		run<8, 1, 16, 4>("P=8 FFMA2 flush16", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy, false);
+		if (atoi(argv[2]) == 1)
+			run<8, 1, 16, 4>("P=8 FFMA2 flush16", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy, false);
+		else if (atoi(argv[2]) == 2)
+			run_sat<8, true, 4, 4>("sat P=8 FFMA2", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy, false);
+		else
+			run_sat<8, false, 4, 4>("sat P=8 scalar", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy, false);
 		return 0;
 	}
 	cudaMemset(d_worst, 0, 4);
@@ -345,5 +541,16 @@ int main(int argc, char **argv)
 	run<8, 2, 16, 4>("P=8 FFMA2 no rsqrt", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy, false);
 	run<8, 3, 16, 4>("P=8 FFMA2 no clamp", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy, false);
 	run<4, 2, 16, 6>("P=4 FFMA2 no rsqrt", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy, false);
+	run_sat<8, false, 4, 4>("sat clamp P=8 scalar u4", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy);
+	run_sat<8, true, 4, 4>("sat clamp P=8 FFMA2 u4", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy);
+	run_sat<8, true, 4, 2>("sat clamp P=8 FFMA2 u2", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy);
+	run_sat<8, true, 3, 4>("sat clamp P=8 FFMA2 u4 3 blocks", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy);
+	run_sat<4, false, 6, 4>("sat clamp P=4 scalar u4", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy);
+	run_sat<4, true, 6, 4>("sat clamp P=4 FFMA2 u4", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy);
+	run_sat<4, true, 8, 4>("sat clamp P=4 FFMA2 u4 8 blocks", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy);
+	run_sat<8, true, 4, 8>("sat clamp P=8 FFMA2 u8", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy);
+	run_sat<6, true, 5, 4>("sat clamp P=6 FFMA2 u4 5 blocks", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy, false);
+	run_sat<8, true, 4, 4, 1>("sat P=8 FFMA2, 1 channel on ALU", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy, false);
+	run_sat<8, true, 4, 4, 2>("sat P=8 FFMA2, 2 channels on ALU", d_in, d_xy, d_spx, w, h, n, d_scores, page, xy, false);
 	return 0;
 }
