@@ -359,8 +359,8 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 	const float inv = cs.inv;
 
 	// the fix-up lists of this score block start empty (ace_scale_kernel fills them)
-	if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x < 2 * kAceFixupSlots)
-		fix_counts[threadIdx.x] = 0;      // list lengths, then the fix-up pass's tickets
+	if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x < 3 * kAceFixupSlots)
+		fix_counts[threadIdx.x] = 0;      // list lengths, the fix-up pass's tickets, its statistics
 	if (threadIdx.x < 3) {
 		sh.smin[threadIdx.x] = 255;
 		sh.smax[threadIdx.x] = 0;
@@ -529,55 +529,109 @@ __global__ void ace_minmax_init_kernel(double *minmax, size_t n)
 // reference's own arithmetic (a warp per pixel).
 // ---------------------------------------------------------------------------
 
+// 1/sqrt(x) for an integer-valued x < 2^31: MUFU.RSQ64H looks at the high word
+// of x only (20 mantissa bits: x is off by up to 2^-20, its root by 2^-21) and
+// is itself good to ~2^-22, so the estimate is within 2^-20.4; one Newton
+// step squares that: 1.5 * 2^-40.8 < 2^-40.  (The step: e = 1 - x y^2,
+// y' = y + (y/2) e; y/2 is an exponent decrement of the high word.)
 __device__ __forceinline__ double rsqrt_f64(double x)
 {
-	// MUFU.RSQ64H (2^-22) and two Newton steps: a relative error of a few 2^-53
 	double y;
 	asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
-#pragma unroll
-	for (int i = 0; i < 2; i++) {
-		const double t = x * y;
-		y = y * fma(-0.5 * t, y, 1.5);
-	}
-	return y;
+	const double e = fma(-(x * y), y, 1.0);
+	const double h = __hiloint2double(__double2hiint(y) - 0x00100000, __double2loint(y));
+	return fma(h, e, y);
 }
 
-// Bound on |ace_accurate_score - reference score|.  Both approximate the same
-// real number: the reference with one rounding in the square root, one in each
-// division and one per addition, this with the weight's few 2^-53, one
-// rounding per FMA and one division; (4 N + 64) * 2^-53 covers both with room.
+// Bound on |FP64 score (ace_accurate_sums) - reference score|.  Both
+// approximate the same real number: the reference with one rounding in the
+// square root, one in each division and one per addition; this with weights
+// within 2^-40 (the score moves by at most twice that: the same weight is in
+// numerator and denominator), one rounding per FMA (in any order) and one
+// division: 2^-39 + (4 N + 64) * 2^-53, doubled for room.
 __device__ __forceinline__ double ace_accurate_eps(int nb_samples)
 {
-	return (4.0 * nb_samples + 64.0) * 0x1p-53;
+	return 2.0 * (0x1p-39 + (4.0 * nb_samples + 64.0) * 0x1p-53);
 }
 
-// The scores of one pixel in FP64, by one thread: weights 1/dist from the
-// reciprocal square root, saturation values exactly the reference's.
-__device__ __forceinline__ void ace_accurate_score(const uint32_t *__restrict__ in,
-		const int *__restrict__ samples_xy, const AceConst &cs, int x, int y, double (&s)[3])
+// What the exact passes read per sample, staged once per block: coordinates
+// and pixel value, and the reference's saturation value for every possible
+// channel difference (upstream _ace.c calc_saturation: slope * d, clamped).
+constexpr int kTableMax = 512;       // samples kept in shared memory; more are read from global memory
+struct ExactTable {
+	double sat[511];                 // [d + 255]
+	int4 smp[kTableMax];             // x, y, pixel, -
+	int4 off[kTableMax];             // byte offsets (255 - s_c) * 8 into sat, per channel
+};
+
+// Fills the table (all threads of the block).  Samples beyond kTableMax are
+// read from global memory by the loops below.
+__device__ __forceinline__ void stage_exact_table(ExactTable &tb, const uint32_t *__restrict__ in,
+		const int *__restrict__ samples_xy, const AceConst &cs)
 {
-	const uint32_t p = __ldg(in + (size_t)y * cs.w + x);
-	double acc[4] = { 0.0, 0.0, 0.0, 0.0 };
-#pragma unroll 2
-	for (int k = 0; k < cs.nb_samples; k++) {
-		const int2 sxy = __ldg(reinterpret_cast<const int2 *>(samples_xy) + k);
-		const int dx = x - sxy.x, dy = y - sxy.y;
-		const int d2 = dx * dx + dy * dy;
-		if (d2 < cs.too_close2)
-			continue;
-		const uint32_t sp = cs.sample_px ? __ldg(cs.sample_px + k) : __ldg(in + (size_t)sxy.y * cs.w + sxy.x);
-		const double wgt = rsqrt_f64((double)d2);      // d2 == 0 (pages under 5 rows): inf, the sums turn NaN as in the reference
-#pragma unroll
-		for (int c = 0; c < 3; c++) {
-			double v = __dmul_rn((double)((int)((p >> (8 * c)) & 0xFF) - (int)((sp >> (8 * c)) & 0xFF)), cs.slope);
-			v = v > cs.limit ? cs.limit : (v < -cs.limit ? -cs.limit : v);
-			acc[c] = fma(wgt, v, acc[c]);
-		}
-		acc[3] = fma(wgt, cs.limit, acc[3]);
+	for (int i = threadIdx.x; i < 511; i += blockDim.x) {
+		double v = __dmul_rn((double)(i - 255), cs.slope);
+		tb.sat[i] = v > cs.limit ? cs.limit : (v < -cs.limit ? -cs.limit : v);
 	}
+	const int n = min(cs.nb_samples, kTableMax);
+	for (int k = threadIdx.x; k < n; k += blockDim.x) {
+		const int2 sxy = __ldg(reinterpret_cast<const int2 *>(samples_xy) + k);
+		const uint32_t px = cs.sample_px ? __ldg(cs.sample_px + k) : __ldg(in + (size_t)sxy.y * cs.w + sxy.x);
+		tb.smp[k] = make_int4(sxy.x, sxy.y, (int)px, 0);
+		tb.off[k] = make_int4((255 - (int)(px & 0xFF)) * 8, (255 - (int)((px >> 8) & 0xFF)) * 8,
+				(255 - (int)((px >> 16) & 0xFF)) * 8, 0);
+	}
+	__syncthreads();
+}
+
+// sample k: coordinates and pixel, from the table or from global memory
+__device__ __forceinline__ int4 exact_sample(const ExactTable &tb, const uint32_t *__restrict__ in,
+		const int *__restrict__ samples_xy, const AceConst &cs, int k)
+{
+	if (k < kTableMax)
+		return tb.smp[k];
+	const int2 sxy = __ldg(reinterpret_cast<const int2 *>(samples_xy) + k);
+	const uint32_t px = cs.sample_px ? __ldg(cs.sample_px + k) : __ldg(in + (size_t)sxy.y * cs.w + sxy.x);
+	return make_int4(sxy.x, sxy.y, (int)px, 0);
+}
+
+// Sums of one pixel (value p at x, y) over samples k_begin, k_begin + k_step,
+// ... in FP64: weights 1/dist from the reciprocal square root, saturation
+// values exactly the reference's.  acc[0..2]: R, G, B; acc[3]: the denominator.
+__device__ __forceinline__ void ace_accurate_sums(const ExactTable &tb,
+		const uint32_t *__restrict__ in, const int *__restrict__ samples_xy, const AceConst &cs,
+		uint32_t p, int x, int y, int k_begin, int k_step, double (&acc)[4])
+{
+	const char *sat = reinterpret_cast<const char *>(tb.sat);
+	const int po[3] = { (int)(p & 0xFF) * 8, (int)((p >> 8) & 0xFF) * 8, (int)((p >> 16) & 0xFF) * 8 };
+	const int too_close2 = cs.too_close2;
+	const double limit = cs.limit;
+	const int n_tab = min(cs.nb_samples, kTableMax);
+#pragma unroll 4
+	for (int k = k_begin; k < n_tab; k += k_step) {
+		const int4 sm = tb.smp[k], of = tb.off[k];
+		const int dx = x - sm.x, dy = y - sm.y;
+		const int d2 = dx * dx + dy * dy;
+		// (2^52 + d2) - 2^52: the integer as a double without the conversion unit;
+		// d2 == 0 (pages under 5 rows) gives inf, and the sums turn NaN as in the reference
+		double wgt = rsqrt_f64(__hiloint2double(0x43300000, d2) - 4503599627370496.0);
+		wgt = d2 < too_close2 ? 0.0 : wgt;
+		acc[0] = fma(wgt, *reinterpret_cast<const double *>(sat + po[0] + of.x), acc[0]);
+		acc[1] = fma(wgt, *reinterpret_cast<const double *>(sat + po[1] + of.y), acc[1]);
+		acc[2] = fma(wgt, *reinterpret_cast<const double *>(sat + po[2] + of.z), acc[2]);
+		acc[3] = fma(wgt, limit, acc[3]);
+	}
+	for (int k = kTableMax + k_begin; k < cs.nb_samples; k += k_step) {      // (k_step divides kTableMax)
+		const int4 sm = exact_sample(tb, in, samples_xy, cs, k);
+		const int dx = x - sm.x, dy = y - sm.y;
+		const int d2 = dx * dx + dy * dy;
+		double wgt = rsqrt_f64(__hiloint2double(0x43300000, d2) - 4503599627370496.0);
+		wgt = d2 < too_close2 ? 0.0 : wgt;
 #pragma unroll
-	for (int c = 0; c < 3; c++)
-		s[c] = acc[c] / acc[3];
+		for (int c = 0; c < 3; c++)
+			acc[c] = fma(wgt, tb.sat[(int)((p >> (8 * c)) & 0xFF) - (int)(((uint32_t)sm.z >> (8 * c)) & 0xFF) + 255], acc[c]);
+		acc[3] = fma(wgt, limit, acc[3]);
+	}
 }
 
 constexpr int kExactChunk = 64;      // samples whose terms a warp holds at a time
@@ -589,9 +643,9 @@ constexpr int kExactChunk = 64;      // samples whose terms a warp holds at a ti
 // 64 samples at a time (that is where the time goes), then lanes 0..3 add them
 // up in order: R, G, B and the denominator.  terms: this warp's shared area.
 // All lanes return the three scores.
-__device__ __forceinline__ void ace_exact_score_warp(double (*terms)[4],
-		const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
-		const AceConst &cs, int x, int y, double (&r)[3])
+__device__ __forceinline__ void ace_exact_score_warp(double (*terms)[4], const ExactTable &tb,
+		const uint32_t *__restrict__ in, const int *__restrict__ samples_xy, const AceConst &cs,
+		int x, int y, double (&r)[3])
 {
 	const int lane = threadIdx.x & 31;
 	const uint32_t p = __ldg(in + (size_t)y * cs.w + x);
@@ -603,21 +657,15 @@ __device__ __forceinline__ void ace_exact_score_warp(double (*terms)[4],
 			const int j = lane + 32 * half, k = k0 + j;
 			double t[4] = { 0.0, 0.0, 0.0, 0.0 };
 			if (k < cs.nb_samples) {
-				const int2 sxy = __ldg(reinterpret_cast<const int2 *>(samples_xy) + k);
-				const uint32_t sp = cs.sample_px ? __ldg(cs.sample_px + k)
-				                                 : __ldg(in + (size_t)sxy.y * cs.w + sxy.x);
-				const double ddx = (double)(x - sxy.x), ddy = (double)(y - sxy.y);
+				const int4 sm = exact_sample(tb, in, samples_xy, cs, k);
+				const uint32_t sp = (uint32_t)sm.z;
+				const double ddx = (double)(x - sm.x), ddy = (double)(y - sm.y);
 				const double dist = __dsqrt_rn(__dadd_rn(__dmul_rn(ddx, ddx), __dmul_rn(ddy, ddy)));
 				if (!(dist < too_close)) {
 #pragma unroll
-					for (int c = 0; c < 4; c++) {
-						double v = __dmul_rn((double)((int)((p >> (8 * c)) & 0xFF) - (int)((sp >> (8 * c)) & 0xFF)), cs.slope);
-						if (v > cs.limit || c == 3)
-							v = cs.limit;
-						else if (v < -cs.limit)
-							v = -cs.limit;
-						t[c] = __ddiv_rn(v, dist);
-					}
+					for (int c = 0; c < 3; c++)
+						t[c] = __ddiv_rn(tb.sat[(int)((p >> (8 * c)) & 0xFF) - (int)((sp >> (8 * c)) & 0xFF) + 255], dist);
+					t[3] = __ddiv_rn(cs.limit, dist);
 				}
 			}
 #pragma unroll
@@ -644,6 +692,7 @@ constexpr int kRefineThreads = 256;
 constexpr int kRefineSlab = 16;      // rows scanned before the candidates are worked off
 
 struct RefineShared {
+	ExactTable tb;
 	double terms[kRefineThreads / 32][kExactChunk][4];
 	unsigned short cand[kRefineSlab * kAceBlock];
 	unsigned short todo[kRefineSlab * kAceBlock];
@@ -655,7 +704,7 @@ struct RefineShared {
 // truncates, so the extremes must be the reference's to the last bit.
 //   The exact minimum is the exact score of SOME pixel whose approximate score
 // lies within 2 eps of the approximate minimum: the candidates.  Phase 1
-// computes the candidates' scores in FP64 (ace_accurate_score, error e2) and
+// computes the candidates' scores in FP64 (ace_accurate_sums, error e2) and
 // takes the extremes of those; the exact minimum then belongs to a candidate
 // whose FP64 score lies within 2 e2 of that FP64 minimum -- a handful of
 // pixels -- and phase 2 recomputes those in the reference's own arithmetic.
@@ -664,8 +713,8 @@ struct RefineShared {
 // between them; each scans the same tiles (a few: the tile table the
 // accumulation kernel left says which can hold a candidate).
 template <int PHASE>
-__device__ __forceinline__ void refine_scan(RefineShared &sh, const uint32_t *__restrict__ in,
-		const int *__restrict__ samples_xy, const AceConst &cs, const float *__restrict__ scores,
+__device__ __forceinline__ void refine_scan(RefineShared &sh, const int *__restrict__ samples_xy,
+		const uint32_t *__restrict__ in, const AceConst &cs, const float *__restrict__ scores,
 		double *__restrict__ minmax, int tiles_x, int tiles_y)
 {
 	double lo[3], hi[3], alo[3], ahi[3];
@@ -696,10 +745,28 @@ __device__ __forceinline__ void refine_scan(RefineShared &sh, const uint32_t *__
 		if (t < n_tiles) {
 			const double *tile = minmax + kMinmaxHead
 				+ 6 * ((size_t)(tile_row0 + t / tiles_x) * tiles_x + t % tiles_x);
-			bool wanted = false;
+			bool wanted = false, uniform = true;
+			double tv[3];
 #pragma unroll
-			for (int c = 0; c < 3; c++)
+			for (int c = 0; c < 3; c++) {
+				tv[c] = tile[c];
 				wanted |= (tile[c] <= lo[c]) || (tile[3 + c] >= hi[c]);
+				uniform = uniform && tile[c] == tile[3 + c] && (tv[c] == 0.0 || tv[c] == 1.0 || tv[c] == -1.0);
+			}
+			if (wanted && uniform) {
+				// every score of the tile is the same tie (flat areas of a page):
+				// exact as it stands, nothing to look at
+				if (PHASE == 1) {
+#pragma unroll
+					for (int c = 0; c < 3; c++) {
+						if (tv[c] <= lo[c] || tv[c] >= hi[c]) {
+							emn[c] = fmin(emn[c], tv[c]);
+							emx[c] = fmax(emx[c], tv[c]);
+						}
+					}
+				}
+				wanted = false;
+			}
 			if (wanted)
 				sh.wanted[atomicAdd(&sh.n_wanted, 1)] = t;
 		}
@@ -746,24 +813,40 @@ __device__ __forceinline__ void refine_scan(RefineShared &sh, const uint32_t *__
 				}
 				__syncthreads();
 				const int n = sh.n_cand;
-				// a thread per candidate: its scores in FP64.  They take part in
-				// every channel (true scores of the page can only tighten the
-				// extremes toward the truth).
-				for (int i = threadIdx.x; i < n; i += kRefineThreads) {
+				// The candidates' scores in FP64.  They take part in every channel
+				// (true scores of the page can only move the extremes toward the
+				// truth).  A few candidates: a warp each, the samples dealt out
+				// over the lanes (latency); many: a thread each (throughput).
+				const int lane = threadIdx.x & 31;
+				const bool by_warp = n <= 2 * (kRefineThreads / 32);
+				for (int i = by_warp ? (int)(threadIdx.x >> 5) : (int)threadIdx.x; i < n;
+						i += by_warp ? kRefineThreads / 32 : kRefineThreads) {
 					const int cd = sh.cand[i];
-					double sa[3];
-					ace_accurate_score(in, samples_xy, cs, x_lo + cd % kAceBlock, ys + cd / kAceBlock, sa);
+					const int px = x_lo + cd % kAceBlock, py = ys + cd / kAceBlock;
+					double acc[4] = { 0.0, 0.0, 0.0, 0.0 };
+					const uint32_t pv = __ldg(in + (size_t)py * cs.w + px);
+					if (by_warp) {
+						ace_accurate_sums(sh.tb, in, samples_xy, cs, pv, px, py, lane, 32, acc);
+#pragma unroll
+						for (int c = 0; c < 4; c++)
+#pragma unroll
+							for (int d = 16; d > 0; d >>= 1)
+								acc[c] += __shfl_xor_sync(0xFFFFFFFFu, acc[c], d);
+					} else {
+						ace_accurate_sums(sh.tb, in, samples_xy, cs, pv, px, py, 0, 1, acc);
+					}
 					bool exact = false;
 #pragma unroll
 					for (int c = 0; c < 3; c++) {
+						const double sa = acc[c] / acc[3];
 						if (PHASE == 1) {
-							if (sa[c] < mn1[c]) mn1[c] = sa[c];       // NaN never enters
-							if (sa[c] > mx1[c]) mx1[c] = sa[c];
+							if (sa < mn1[c]) mn1[c] = sa;       // NaN never enters
+							if (sa > mx1[c]) mx1[c] = sa;
 						} else {
-							exact |= sa[c] <= alo[c] || sa[c] >= ahi[c];
+							exact |= sa <= alo[c] || sa >= ahi[c];
 						}
 					}
-					if (PHASE == 2 && exact)
+					if (PHASE == 2 && exact && (!by_warp || lane == 0))
 						sh.todo[atomicAdd(&sh.n_todo, 1)] = (unsigned short)cd;
 				}
 				if (PHASE == 2) {
@@ -773,7 +856,7 @@ __device__ __forceinline__ void refine_scan(RefineShared &sh, const uint32_t *__
 					for (int i = warp; i < n_todo; i += kRefineThreads / 32) {
 						const int cd = sh.todo[i];
 						double r[3];
-						ace_exact_score_warp(sh.terms[warp], in, samples_xy, cs,
+						ace_exact_score_warp(sh.terms[warp], sh.tb, in, samples_xy, cs,
 								x_lo + cd % kAceBlock, ys + cd / kAceBlock, r);
 #pragma unroll
 						for (int c = 0; c < 3; c++) {
@@ -815,10 +898,11 @@ ace_refine_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 {
 	__shared__ RefineShared sh;
 	pdl_wait();
-	refine_scan<1>(sh, in, samples_xy, cs, scores, minmax, tiles_x, tiles_y);
+	stage_exact_table(sh.tb, in, samples_xy, cs);
+	refine_scan<1>(sh, samples_xy, in, cs, scores, minmax, tiles_x, tiles_y);
 	__threadfence();
 	cooperative_groups::this_grid().sync();
-	refine_scan<2>(sh, in, samples_xy, cs, scores, minmax, tiles_x, tiles_y);
+	refine_scan<2>(sh, samples_xy, in, cs, scores, minmax, tiles_x, tiles_y);
 }
 
 // The reference's linear scaling, operation for operation (true FP64 divide).
@@ -897,106 +981,134 @@ ace_scale_kernel(const float *__restrict__ scores, const double *__restrict__ mi
 		uint32_t *__restrict__ out, const ScaleOuts more,
 		uint32_t *__restrict__ fix_list, int *__restrict__ fix_count)
 {
+	// per channel: K, min (FP32), guard band, and the results of the three tie values
+	__shared__ float s_k[3], s_mn[3];
+	__shared__ uint32_t s_guard[3], s_tie[3][3];
 	pdl_wait();
-	float kf[3], mnf[3];
-	uint32_t guard[3], tie_lo[3], tie_zero[3], tie_hi[3];
-	bool flat[3];
-#pragma unroll
-	for (int c = 0; c < 3; c++) {
+	if (threadIdx.x < 9) {
+		const int c = threadIdx.x / 3, v = threadIdx.x % 3;
 		double mn, span;
 		exact_extremes(minmax, c, mn, span);
-		flat[c] = !(span > 0.0);
-		const double k = flat[c] ? 0.0 : 255.0 / span * 16384.0;
-		kf[c] = (float)k;
-		mnf[c] = (float)mn;
-		const double g = ((double)eps + 1e-7) * k + 4.0;
-		guard[c] = g < 8192.0 ? (uint32_t)g + 1u : 8192u;       // 8192: everything is uncertain
-		tie_lo[c] = ace_scale_exact(-1.0, mn, span);
-		tie_zero[c] = ace_scale_exact(0.0, mn, span);
-		tie_hi[c] = ace_scale_exact(1.0, mn, span);
+		s_tie[c][v] = ace_scale_exact((double)(v - 1), mn, span);
+		if (v == 0) {
+			// a flat channel (span 0: every score equal, or none) comes out 0 through
+			// K = 0, with an empty guard band
+			const bool flat = !(span > 0.0);
+			const double k = flat ? 0.0 : 255.0 / span * 16384.0;
+			const double g = ((double)eps + 1e-7) * k + 4.0;
+			s_k[c] = (float)k;
+			s_mn[c] = flat ? 0.f : (float)mn;
+			s_guard[c] = flat ? 0u : (g < 8192.0 ? (uint32_t)g + 1u : 8192u);   // 8192: everything is uncertain
+		}
+	}
+	__syncthreads();
+	float kf[3], mnf[3];
+	uint32_t guard[3];
+#pragma unroll
+	for (int c = 0; c < 3; c++) {
+		kf[c] = s_k[c];
+		mnf[c] = s_mn[c];
+		guard[c] = s_guard[c];
 	}
 	bool vec = (npix % 4 == 0) && (plane % 4 == 0)
 		&& (((uintptr_t)scores | (uintptr_t)out) % 16 == 0);
 	if (MULTI)
 		for (int d = 0; d < more.n; d++)
 			vec = vec && ((uintptr_t)more.p[d] % 16 == 0);
-	const size_t ngroups = vec ? npix / 4 : 0;
-	const size_t nwork = vec ? ngroups : npix;
-	const int lane = threadIdx.x & 31;
+	const size_t nwork = vec ? npix / 4 : npix;
+	const int per = vec ? 4 : 1;
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	// Uncertain pixels are rare (about one in a hundred): each warp collects
+	// its own in shared memory and the block appends them to the list with one
+	// atomic at the end; a warp whose buffer is full appends directly.
+	constexpr int kBuf = 192;
+	__shared__ uint32_t s_buf[256 / 32][kBuf];
+	__shared__ int s_n[256 / 32], s_base[256 / 32];
+	if (lane == 0)
+		s_n[warp] = 0;
+	__syncwarp();
 	for (size_t g0 = (size_t)blockIdx.x * blockDim.x; g0 < nwork; g0 += (size_t)gridDim.x * blockDim.x) {
 		const size_t gi = g0 + threadIdx.x;
-		const bool in_range = gi < nwork;
-		uint32_t px[4] = { 0xFF000000u, 0xFF000000u, 0xFF000000u, 0xFF000000u };
-		unsigned risky = 0;
-		const int per = vec ? 4 : 1;
-		if (in_range) {
+		if (gi >= nwork)
+			continue;
+		float sv[3][4];
+		if (vec) {
 #pragma unroll
 			for (int c = 0; c < 3; c++) {
-				float sv[4] = { 0.f, 0.f, 0.f, 0.f };
-				if (vec) {
-					const float4 a = __ldcs(reinterpret_cast<const float4 *>(scores + c * plane) + gi);
-					sv[0] = a.x; sv[1] = a.y; sv[2] = a.z; sv[3] = a.w;
-				} else {
-					sv[0] = __ldcs(scores + c * plane + gi);
-				}
-#pragma unroll
-				for (int k = 0; k < 4; k++) {
-					if (k >= per)
-						break;
-					const float s = sv[k];
-					uint32_t q;
-					if (flat[c] || !(s == s)) {
-						q = 0u;                   // a flat channel, or no sample at all (NaN)
-					} else if (is_tie_score(s)) {
-						q = s < 0.f ? tie_lo[c] : (s > 0.f ? tie_hi[c] : tie_zero[c]);
-					} else {
-						const uint32_t fx = __float_as_uint(__fmaf_rz(s - mnf[c], kf[c], 8404992.0f))
-							- 0x4B000000u;
-						const uint32_t v = fx >> 14;          // integer part + 1
-						q = v < 1u ? 0u : (v > 256u ? 255u : v - 1u);
-						if (((fx + guard[c]) & 0x3FFFu) < 2u * guard[c] || fx >= (258u << 14))
-							risky |= 1u << k;
-					}
-					px[k] |= q << (8 * c);
-				}
+				const float4 a = __ldcs(reinterpret_cast<const float4 *>(scores + c * plane) + gi);
+				sv[c][0] = a.x; sv[c][1] = a.y; sv[c][2] = a.z; sv[c][3] = a.w;
 			}
-			if (vec) {
-				const uint4 v = make_uint4(px[0], px[1], px[2], px[3]);
-				if (MULTI && more.multicast)
-					multimem_store16(reinterpret_cast<uint4 *>(out) + gi, v);
-				else
-					reinterpret_cast<uint4 *>(out)[gi] = v;
-				if (MULTI)
-					for (int d = 0; d < more.n; d++)
-						reinterpret_cast<uint4 *>(more.p[d])[gi] = v;
-			} else {
-				store_pixel<MULTI>(out, more, gi, px[0]);
+		} else {
+#pragma unroll
+			for (int c = 0; c < 3; c++) {
+				sv[c][0] = __ldcs(scores + c * plane + gi);
+				sv[c][1] = sv[c][2] = sv[c][3] = 0.5f;
 			}
 		}
-		// warp-aggregated append of the uncertain pixels to the fix-up list
-		if (__ballot_sync(0xFFFFFFFFu, risky != 0)) {
-			const int nr = __popc(risky);
-			int pre = nr;
+		uint32_t px[4] = { 0xFF000000u, 0xFF000000u, 0xFF000000u, 0xFF000000u };
+		unsigned risky = 0;
 #pragma unroll
-			for (int dlt = 1; dlt < 32; dlt <<= 1) {
-				const int t = __shfl_up_sync(0xFFFFFFFFu, pre, dlt);
-				if (lane >= dlt)
-					pre += t;
+		for (int c = 0; c < 3; c++) {
+#pragma unroll
+			for (int k = 0; k < 4; k++) {
+				const float s = sv[c][k];
+				// low 14 bits: the fraction; above them the integer part + 1
+				const uint32_t fx = __float_as_uint(__fmaf_rz(s - mnf[c], kf[c], 8404992.0f)) - 0x4B000000u;
+				uint32_t q = (uint32_t)__viaddmin_s32_relu((int)(fx >> 14), -1, 255);
+				bool unsure = ((fx + guard[c]) & 0x3FFFu) < 2u * guard[c] || fx >= (258u << 14);
+				if (!(fabsf(s) < 1.f) || s == 0.f) {
+					// a tie (exactly 0, 1, -1) or no score at all (NaN)
+					q = s == 0.f ? s_tie[c][1] : (s == 1.f ? s_tie[c][2] : (s == -1.f ? s_tie[c][0] : 0u));
+					unsure = false;
+				}
+				if (unsure)
+					risky |= 1u << k;
+				px[k] |= q << (8 * c);
 			}
-			int base = 0;
-			if (lane == 31)
-				base = atomicAdd(fix_count, pre);
-			base = __shfl_sync(0xFFFFFFFFu, base, 31) + pre - nr;
-#pragma unroll
-			for (int k = 0; k < 4; k++)
-				if (risky & (1u << k))
-					fix_list[base++] = (uint32_t)(pix_base + (size_t)per * gi + k);
+		}
+		if (vec) {
+			const uint4 v = make_uint4(px[0], px[1], px[2], px[3]);
+			if (MULTI && more.multicast)
+				multimem_store16(reinterpret_cast<uint4 *>(out) + gi, v);
+			else
+				reinterpret_cast<uint4 *>(out)[gi] = v;
+			if (MULTI)
+				for (int d = 0; d < more.n; d++)
+					reinterpret_cast<uint4 *>(more.p[d])[gi] = v;
+		} else {
+			store_pixel<MULTI>(out, more, gi, px[0]);
+			risky &= 1u;
+		}
+		while (risky) {
+			const int k = __ffs(risky) - 1;
+			risky &= risky - 1;
+			const uint32_t entry = (uint32_t)(pix_base + (size_t)per * gi + k);
+			const int at = atomicAdd(&s_n[warp], 1);
+			if (at < kBuf)
+				s_buf[warp][at] = entry;
+			else
+				fix_list[atomicAdd(fix_count, 1)] = entry;
 		}
 	}
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		int total = 0;
+		for (int wv = 0; wv < 256 / 32; wv++) {
+			s_n[wv] = min(s_n[wv], kBuf);
+			s_base[wv] = total;
+			total += s_n[wv];
+		}
+		const int base = total ? atomicAdd(fix_count, total) : 0;
+		for (int wv = 0; wv < 256 / 32; wv++)
+			s_base[wv] += base;
+	}
+	__syncthreads();
+	for (int i = lane; i < s_n[warp]; i += 32)
+		fix_list[s_base[warp] + i] = s_buf[warp][i];
 }
 
 // The listed pixels again, a thread per pixel: scores in FP64
-// (ace_accurate_score, error e2 ~ 1e-14), rescaled with a true division.  That
+// (ace_accurate_sums, error e2 ~ 1e-14), rescaled with a true division.  That
 // decides the truncation unless the value lies within the (now tiny) bound of
 // an integer; those last few -- the pixels AT the page's extremes among them
 // -- are redone by a whole warp in the reference's own arithmetic.  List
@@ -1009,10 +1121,12 @@ ace_fixup_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sample
 		uint32_t *__restrict__ out, const ScaleOuts more)
 {
 	__shared__ double terms[256 / 32][kExactChunk][4];
+	__shared__ ExactTable tb;
 	pdl_wait();
 	const int count = *reinterpret_cast<volatile int *>(fix_count);
 	if (count == 0)
 		return;
+	stage_exact_table(tb, in, samples_xy, cs);
 	double mn[3], span[3], guard[3];
 #pragma unroll
 	for (int c = 0; c < 3; c++) {
@@ -1028,14 +1142,15 @@ ace_fixup_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sample
 		const int y = cs.score_row0 + (int)(idx / (uint32_t)cs.w), x = (int)(idx % (uint32_t)cs.w);
 		bool open = false;
 		if (active) {
-			double sa[3];
-			ace_accurate_score(in, samples_xy, cs, x, y, sa);
+			double acc[4] = { 0.0, 0.0, 0.0, 0.0 };
+			ace_accurate_sums(tb, in, samples_xy, cs, __ldg(in + (size_t)y * cs.w + x), x, y, 0, 1, acc);
 			uint32_t rgba = 0xFF000000u;
 #pragma unroll
 			for (int c = 0; c < 3; c++) {
 				uint32_t q = 0u;
-				if (span[c] > 0.0 && sa[c] == sa[c]) {
-					const double t = 255.0 * (sa[c] - mn[c]) / span[c];
+				const double sa = acc[c] / acc[3];
+				if (span[c] > 0.0 && sa == sa) {
+					const double t = 255.0 * (sa - mn[c]) / span[c];
 					const double fl = floor(t);
 					if (t - fl < guard[c] || fl + 1.0 - t < guard[c])
 						open = true;
@@ -1054,7 +1169,7 @@ ace_fixup_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sample
 			const int ex = __shfl_sync(0xFFFFFFFFu, x, src), ey = __shfl_sync(0xFFFFFFFFu, y, src);
 			const uint32_t eidx = __shfl_sync(0xFFFFFFFFu, idx, src);
 			double r[3];
-			ace_exact_score_warp(terms[warp], in, samples_xy, cs, ex, ey, r);
+			ace_exact_score_warp(terms[warp], tb, in, samples_xy, cs, ex, ey, r);
 			if (lane == 0) {
 				uint32_t rgba = 0xFF000000u;
 #pragma unroll
@@ -1070,6 +1185,7 @@ ace_fixup_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sample
 	if (threadIdx.x == 0) {
 		if (atomicAdd(fix_ticket, 1) == (int)gridDim.x - 1) {
 			*fix_ticket = 0;
+			fix_ticket[kAceFixupSlots] = count;       // statistics: the length of the list just worked off
 			*reinterpret_cast<volatile int *>(fix_count) = 0;
 		}
 	}

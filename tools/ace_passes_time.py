@@ -41,5 +41,6 @@ for it in range(reps + 3):
         thr = 2 * 8e-6
         wanted = ((tiles[:, :3] <= m[0:3] + thr) | (tiles[:, 3:] >= m[3:6] - thr)).any(1)
         print("fast min/max", m[:6], "exact", m[6:12], "tiles wanted", int(wanted.sum()), "of", len(tiles))
+print("pixels redone by the fix-up pass: %d of %d" % (int(scores[:256].view(torch.int32)[32]), w * h))
 for n, t in zip(names, tot / reps):
     print("%-12s %.4f ms" % (n, t))
