@@ -252,9 +252,25 @@ static int drained(Context &c, int rc)
 		cudaStreamSynchronize(c.st_up);
 		cudaStreamSynchronize(c.st);
 		cudaStreamSynchronize(c.st_down);
+		// (a Canny pass cut short may have left its scratch header in use)
+		if (c.d_scratch.p)
+			cudaMemset(c.d_scratch.p, 0, 256);
 		cudaGetLastError();
 	}
 	return rc;
+}
+
+// The context's Canny scratch: its header is cleared when the buffer is (re)allocated;
+// every Canny pass leaves it clear, so no call has to.
+static int grow_canny_scratch(Context &c, int w, int h)
+{
+	const size_t before = c.d_scratch.cap;
+	const int rc = grow(c.d_scratch, canny_scratch_bytes(w, h), false);
+	if (rc)
+		return rc;
+	if (c.d_scratch.cap != before)
+		PFB_CUDA(cudaMemsetAsync(c.d_scratch.p, 0, 256, c.st));
+	return PF_B200_OK;
 }
 
 static bool is_pinned(const void *p)
@@ -625,14 +641,14 @@ static int run_canny_streamed(Context &c, const struct pf_bitmap *in, struct pf_
 	const int rows = band_rows_for(h);
 	const int nb = (h + rows - 1) / rows;
 	int rc;
-	if ((rc = grow(c.d_scratch, canny_scratch_bytes(w, h), false)) || (rc = grow(c.h_stage, 64, true)))
+	if ((rc = grow_canny_scratch(c, w, h)) || (rc = grow(c.h_stage, 64, true)))
 		return rc;
 	const uint32_t *src = reinterpret_cast<const uint32_t *>(in->pixels);
 	uint32_t *dst = reinterpret_cast<uint32_t *>(out->pixels);
 	const uint32_t *din = static_cast<const uint32_t *>(c.d_in.p);
 	uint32_t *dout = static_cast<uint32_t *>(c.d_out.p);
 	int *weak_count = static_cast<int *>(c.h_stage.p);
-	if ((rc = launch_canny_begin(w, h, c.d_scratch.p, c.d_scratch.cap, c.st)))
+	if ((rc = launch_canny_begin(w, h, c.d_scratch.p, c.d_scratch.cap, c.st, true)))
 		return rc;
 	for (int b = 0; b < nb; b++) {
 		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
@@ -653,7 +669,9 @@ static int run_canny_streamed(Context &c, const struct pf_bitmap *in, struct pf_
 	}
 	if ((rc = launch_canny_resolve(dout, w, h, c.d_scratch.p, c.st)))
 		return rc;
-	PFB_CUDA(cudaMemcpyAsync(weak_count, c.d_scratch.p, sizeof(int), cudaMemcpyDeviceToHost, c.st));
+	// (header word 3: the length of the list just resolved)
+	PFB_CUDA(cudaMemcpyAsync(weak_count, static_cast<int *>(c.d_scratch.p) + 3, sizeof(int),
+			cudaMemcpyDeviceToHost, c.st));
 	// what follows on the kernel stream comes after the last band's download
 	PFB_CUDA(cudaEventRecord(c.ev_up[0], c.st_down));
 	PFB_CUDA(cudaStreamWaitEvent(c.st, c.ev_up[0], 0));
@@ -825,11 +843,10 @@ static int run_stencil(Op op, const struct pf_bitmap *in, struct pf_bitmap *out,
 		rc = launch_sobel(din, dout, w, h, 1, c.st);
 		break;
 	case OP_CANNY: {
-		const size_t sb = canny_scratch_bytes(w, h);
-		if ((rc = grow(c.d_scratch, sb, false)))
+		if ((rc = grow_canny_scratch(c, w, h)))
 			return rc;
 		rc = launch_canny(din, dout, w, h, 1, canny_thresholds(),
-				c.d_scratch.p, c.d_scratch.cap, c.st);
+				c.d_scratch.p, c.d_scratch.cap, c.st, true);
 		break;
 	}
 	}

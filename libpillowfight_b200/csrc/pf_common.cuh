@@ -53,13 +53,17 @@ struct CannyThresholds {
 };
 CannyThresholds canny_thresholds();   // upstream _canny.c LOW / HIGH as integer tests
 size_t canny_scratch_bytes(int w, int h);
+// header_is_clear: the scratch's 256-byte header is known to be zero (fresh
+// from a memset, or left by an earlier call: every call leaves it zero);
+// otherwise it is cleared on the stream first.
 int launch_canny(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 		CannyThresholds thr, void *scratch, size_t scratch_bytes,
-		cudaStream_t st);
+		cudaStream_t st, bool header_is_clear = false);
 // One page in steps (row bands classified as they arrive): begin, classify
 // every band (each needs two rows above and below it in `in`), resolve; patch
 // copies the weak pixels' final values into a second image.
-int launch_canny_begin(int w, int h, void *scratch, size_t scratch_bytes, cudaStream_t st);
+int launch_canny_begin(int w, int h, void *scratch, size_t scratch_bytes, cudaStream_t st,
+		bool header_is_clear = false);
 int launch_canny_classify_rows(const uint32_t *in, uint32_t *out, int w, int h,
 		int y_begin, int y_end, CannyThresholds thr, void *scratch, cudaStream_t st);
 int launch_canny_resolve(uint32_t *out, int w, int h, void *scratch, cudaStream_t st);

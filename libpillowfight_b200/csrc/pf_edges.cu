@@ -291,6 +291,19 @@ __device__ __forceinline__ void canny_march(const uint32_t *__restrict__ in,
 	}
 }
 
+struct PageGeom {
+	int w, h, npix;
+};
+
+// Scratch header (ints): the work list's length; (unused); a ticket counter of
+// the final pass's blocks; the length of the list last resolved (what
+// canny_patch_kernel and the host read afterwards).  The header's first three
+// words are zero between calls: whoever resolves a list leaves them so.
+enum { kHdrCount = 0, kHdrResolveTicket = 2, kHdrLastCount = 3 };
+
+constexpr int kHystThreads = 1024;
+constexpr int kSmallList = 2 * kHystThreads;   // weak pixels one block resolves in shared memory
+
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 canny_classify_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out,
 		const StripGeom g, CannyThresholds thr,
@@ -308,13 +321,6 @@ canny_classify_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ ou
 	else
 		canny_march<false>(in + page, out + page, g, wp, thr, ws);
 }
-
-struct PageGeom {
-	int w, h, npix;
-};
-
-constexpr int kHystThreads = 1024;
-constexpr int kSmallList = 2 * kHystThreads;   // weak pixels one block resolves in shared memory
 
 __device__ __forceinline__ int sm_find(int *parent, int i)
 {
@@ -359,7 +365,7 @@ __device__ void canny_resolve_small(uint32_t *out, PageGeom pg, const int *list,
 		s_keep[i] = 0;
 	}
 	__syncthreads();
-	unsigned strong_mask = 0;     // bit k: this thread's k-th entry touches a strong pixel (k < 2)
+	unsigned strong_mask = 0;     // bit k: this thread's k-th entry touches a strong pixel (k < 32: blocks of >= 64 threads)
 	int k = 0;
 	for (int i = threadIdx.x; i < count; i += nt, k++) {
 		const int idx = s_pix[i];
@@ -440,38 +446,45 @@ __device__ __forceinline__ void uf_union(int *parent, int a, int b)
 
 constexpr int kStrongBit = (int)0x80000000;   // in list[root]: component touches a strong pixel
 
-// One cooperative launch resolves the weak pixels.  A short list is handled by
-// block 0 alone in shared memory; a long one by the whole grid in three steps
-// with grid-wide barriers between them:
+// The weak pixels that the classification kernel did not resolve itself (a
+// long list, or bands classified by several launches) in three kernels, the
+// launch boundaries being the grid-wide barriers between:
 //   1. join every weak pixel with its weak neighbours (each undirected edge
-//      once, from the pixel with the smaller address: E, SW, S, SE);
+//      once, from the pixel with the smaller address: E, SW, S, SE); a short
+//      list is resolved here by block 0 alone, in shared memory;
 //   2. a weak pixel next to a strong one marks its component's root;
-//   3. every weak pixel takes its component's verdict.
+//   3. every weak pixel takes its component's verdict, and the block that
+//      finishes last clears the header for the next call.
+// With nothing on the list each is a launch that returns at once.
+//
+// Two entries per thread and round, all their neighbour loads issued before
+// any is used: these loops are bound by memory latency, not by work.  The
+// image is only read until kernel 3 writes the verdicts, so the reads may go
+// through L1 (entries that follow one another in the list are neighbours in
+// the page and share sectors).
 __global__ void __launch_bounds__(kHystThreads)
-canny_hysteresis_kernel(uint32_t *out, PageGeom pg, int *list, int *parent,
-		const int *__restrict__ hdr)
+canny_link_kernel(uint32_t *out, PageGeom pg, int *list, int *parent, int *hdr)
 {
 	__shared__ int s_pix[kSmallList];
 	__shared__ int s_parent[kSmallList];
 	__shared__ unsigned char s_keep[kSmallList];
 	pdl_wait();
-	const int count = hdr[0];
+	const int count = *reinterpret_cast<volatile int *>(&hdr[kHdrCount]);
 	if (count == 0)
 		return;
 	if (count <= kSmallList) {
-		if (blockIdx.x == 0)
+		if (blockIdx.x == 0) {
 			canny_resolve_small(out, pg, list, count, s_pix, s_parent, s_keep);
+			__syncthreads();
+			if (threadIdx.x == 0) {
+				hdr[kHdrLastCount] = count;
+				hdr[kHdrCount] = 0;
+			}
+		}
 		return;
 	}
-	cooperative_groups::grid_group grid = cooperative_groups::this_grid();
 	const int first = blockIdx.x * blockDim.x + threadIdx.x;
 	const int step = gridDim.x * blockDim.x;
-
-	// Two entries per thread and round, all their neighbour loads issued before
-	// any is used: these loops are bound by memory latency, not by work.  The
-	// image is only read until the last loop of this kernel writes the
-	// verdicts, so the reads may go through L1 (entries that follow one
-	// another in the list are neighbours in the page and share sectors).
 	for (int i0 = first; i0 < count; i0 += 2 * step) {
 		uint32_t nv[2][4];
 #pragma unroll
@@ -503,7 +516,18 @@ canny_hysteresis_kernel(uint32_t *out, PageGeom pg, int *list, int *parent,
 				if (nv[u][n] < kBlack)
 					uf_union(parent, i0 + u * step, (int)nv[u][n]);
 	}
-	grid.sync();
+}
+
+__global__ void __launch_bounds__(kHystThreads)
+canny_seed_kernel(const uint32_t *__restrict__ out, PageGeom pg, int *list, int *parent,
+		const int *__restrict__ hdr)
+{
+	pdl_wait();
+	const int count = hdr[kHdrCount];
+	if (count == 0)
+		return;
+	const int first = blockIdx.x * blockDim.x + threadIdx.x;
+	const int step = gridDim.x * blockDim.x;
 	for (int i0 = first; i0 < count; i0 += 2 * step) {
 		bool strong[2] = { false, false };
 #pragma unroll
@@ -531,11 +555,29 @@ canny_hysteresis_kernel(uint32_t *out, PageGeom pg, int *list, int *parent,
 			if (strong[u])
 				atomicOr(&list[uf_find(parent, i0 + u * step)], kStrongBit);
 	}
-	grid.sync();
+}
+
+__global__ void __launch_bounds__(kHystThreads)
+canny_verdict_kernel(uint32_t *out, int *list, int *parent, int *hdr)
+{
+	pdl_wait();
+	const int count = *reinterpret_cast<volatile int *>(&hdr[kHdrCount]);
+	if (count == 0)
+		return;
+	const int first = blockIdx.x * blockDim.x + threadIdx.x;
+	const int step = gridDim.x * blockDim.x;
 	for (int i = first; i < count; i += step) {
 		const int root = uf_find(parent, i);
 		const bool keep = (__ldcg(list + root) & kStrongBit) != 0;
 		out[__ldcg(list + i) & ~kStrongBit] = keep ? kWhite : kBlack;
+	}
+	// the block that finishes last clears the header (every block has read
+	// the length before it gets here)
+	__syncthreads();
+	if (threadIdx.x == 0 && atomicAdd(&hdr[kHdrResolveTicket], 1) == (int)gridDim.x - 1) {
+		hdr[kHdrResolveTicket] = 0;
+		hdr[kHdrLastCount] = count;
+		hdr[kHdrCount] = 0;
 	}
 }
 
@@ -545,7 +587,7 @@ __global__ void canny_patch_kernel(const uint32_t *__restrict__ out, uint32_t *_
 		const int *__restrict__ list, const int *__restrict__ hdr)
 {
 	pdl_wait();
-	const int count = hdr[0];
+	const int count = hdr[kHdrLastCount];
 	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
 		const int idx = list[i] & ~kStrongBit;
 		mirror[idx] = out[idx];
@@ -554,38 +596,26 @@ __global__ void canny_patch_kernel(const uint32_t *__restrict__ out, uint32_t *_
 
 }  // namespace
 
-// Blocks of the hysteresis kernel: its grid must be resident at once (grid
-// barriers); two blocks per SM hide the latency of the long-list path better
-// than one (PF_B200_HYST_BLOCKS).
+// Blocks of the three hysteresis kernels (PF_B200_HYST_BLOCKS per SM, default 2).
 static int hysteresis_blocks()
 {
-	int per_sm = 0;
-	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, canny_hysteresis_kernel,
-			kHystThreads, 0) != cudaSuccess || per_sm < 1) {
-		cudaGetLastError();
-		per_sm = 1;
-	}
 	static const int want = getenv("PF_B200_HYST_BLOCKS") ? atoi(getenv("PF_B200_HYST_BLOCKS")) : 2;
-	return sm_count() * (want < per_sm ? (want < 1 ? 1 : want) : per_sm);
+	return sm_count() * (want < 1 ? 1 : (want > 2 ? 2 : want));
 }
 
-// The hysteresis kernel: a cooperative launch (its long-list path uses grid
-// barriers) that may also be scheduled early behind the classification.
+// The weak pixels the classification left on the list: link, seed, verdict.
 static cudaError_t launch_hysteresis(uint32_t *out, PageGeom pg, int *list, int *parent,
-		const int *hdr, int blocks, cudaStream_t st)
+		int *hdr, int blocks, cudaStream_t st)
 {
-	cudaLaunchConfig_t cfg = {};
-	cfg.gridDim = dim3(blocks);
-	cfg.blockDim = dim3(kHystThreads);
-	cfg.stream = st;
-	cudaLaunchAttribute attr[2];
-	attr[0].id = cudaLaunchAttributeCooperative;
-	attr[0].val.cooperative = 1;
-	attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-	attr[1].val.programmaticStreamSerializationAllowed = 1;
-	cfg.attrs = attr;
-	cfg.numAttrs = pdl_enabled() ? 2 : 1;
-	return cudaLaunchKernelEx(&cfg, canny_hysteresis_kernel, out, pg, list, parent, hdr);
+	cudaError_t e = launch_pdl(canny_link_kernel, dim3(blocks), dim3(kHystThreads), 0, st,
+			out, pg, list, parent, hdr);
+	if (e == cudaSuccess)
+		e = launch_pdl(canny_seed_kernel, dim3(blocks), dim3(kHystThreads), 0, st,
+				(const uint32_t *)out, pg, list, parent, (const int *)hdr);
+	if (e == cudaSuccess)
+		e = launch_pdl(canny_verdict_kernel, dim3(blocks), dim3(kHystThreads), 0, st,
+				out, list, parent, hdr);
+	return e;
 }
 
 int launch_sobel(const uint32_t *in, uint32_t *out, int w, int h, int pages,
@@ -611,7 +641,7 @@ size_t canny_scratch_bytes(int w, int h)
 
 int launch_canny(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 		CannyThresholds thr, void *scratch, size_t scratch_bytes,
-		cudaStream_t st)
+		cudaStream_t st, bool header_is_clear)
 {
 	const size_t npix = (size_t)w * h;
 	if (npix >= 0x7F000000ull)
@@ -638,7 +668,10 @@ int launch_canny(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 		const uint32_t *pin = in + (size_t)p0 * npix;
 		uint32_t *pout = out + (size_t)p0 * npix;
 		int *parent = list + (size_t)np * npix;
-		PFB_CUDA(cudaMemsetAsync(hdr, 0, 256, st));
+		// every pass leaves the header clear; only scratch in an unknown state
+		// (a caller's, on its first use) has to be cleared here
+		if (!header_is_clear && p0 == 0)
+			PFB_CUDA(cudaMemsetAsync(hdr, 0, 256, st));
 		const StripGeom g = make_geom(canny_classify_kernel, pin, pout, w, h, np, 4, 0, -1, 3);
 		const int warps = g.warp_cols * g.strips;
 		dim3 grid((warps + kWarpsPerBlock - 1) / kWarpsPerBlock, np);
@@ -662,12 +695,14 @@ static int canny_check(int w, int h, void *scratch, size_t scratch_bytes)
 	return PF_B200_OK;
 }
 
-int launch_canny_begin(int w, int h, void *scratch, size_t scratch_bytes, cudaStream_t st)
+int launch_canny_begin(int w, int h, void *scratch, size_t scratch_bytes, cudaStream_t st,
+		bool header_is_clear)
 {
 	const int rc = canny_check(w, h, scratch, scratch_bytes);
 	if (rc)
 		return rc;
-	PFB_CUDA(cudaMemsetAsync(scratch, 0, 256, st));
+	if (!header_is_clear)
+		PFB_CUDA(cudaMemsetAsync(scratch, 0, 256, st));
 	return PF_B200_OK;
 }
 
