@@ -805,3 +805,66 @@ def test_size_independent_properties(gpu):
         assert a[..., ch].min() == 0 and a[..., ch].max() >= 254
     assert np.array_equal(a, gpu.ace(page, 10, 1000, 50, seed=3))
     assert not np.array_equal(a, gpu.ace(page, 10, 1000, 50, seed=4))
+
+
+def test_config4_ace_600dpi_400_samples(gpu, oracle):
+    """BASELINE.json config 4 at full size: ACE on 4960 x 7016 with 400 samples,
+    through pf_b200_ace (host pointers) and through the row-band entry points the
+    multi-GPU split uses (here: three bands on one GPU), against the oracle."""
+    import os
+    import torch
+    from libpillowfight_b200.distributed import CudaAceCompute, ace_sharded, row_bands, xy_tensor
+    from libpillowfight_b200.pages import A4_600DPI
+    w, h = A4_600DPI
+    small = synthetic_page(*A4_300DPI, page_index=0)
+    page = np.ascontiguousarray(np.repeat(np.repeat(small, 2, axis=0), 2, axis=1)[:h, :w])
+    xy = oracle.ace_draw_samples(400, w, h, 12345)
+    ref = oracle.ace_with_samples(page, xy, 10.0, 1000.0, nb_threads=os.cpu_count() or 8)
+    assert_exact(gpu.ace(page, 10, 1000, 400, seed=12345), ref, "ace 600 dpi, host pointers")
+    dev = torch.device("cuda:0")
+    comp = CudaAceCompute()
+    tp, txy = torch.from_numpy(page).to(dev), xy_tensor(xy, dev)
+    assert_exact(ace_sharded(tp, txy, 10.0, 1000.0, comp).cpu().numpy(), ref, "ace 600 dpi, ace_sharded")
+    mm = comp.new_minmax(dev, w, h)
+    spx = comp.sample_pixels(tp, txy)
+    bands = row_bands(h, 3)
+    held = [tp[b0:b1].clone() for b0, b1 in bands]
+    parts = [comp.scores_band(r, h, b, txy, spx, 10.0, 1000.0, mm) for r, b in zip(held, bands)]
+    for r, b, p in zip(held, bands, parts):
+        comp.refine_band(r, h, b, txy, spx, 10.0, 1000.0, p, mm)
+    split = torch.cat([comp.scale_band(r, h, b, txy, spx, 10.0, 1000.0, p, mm)
+                       for r, b, p in zip(held, bands, parts)], dim=0)
+    assert_exact(split.cpu().numpy(), ref, "ace 600 dpi, three row bands")
+
+
+def test_config5_page_batch_at_a4(gpu, oracle):
+    """BASELINE.json config 5 at one GPU's share: 64 A4 pages through the
+    batched Gaussian -> Sobel and Canny entry points; eight of the pages
+    (first, last and some in between) are compared with the oracle bit for bit."""
+    import torch
+    from concurrent.futures import ThreadPoolExecutor
+    from libpillowfight_b200.distributed import CudaChain
+    dev = torch.device("cuda:0")
+    w, h = A4_300DPI
+    nb = 64
+    base = [synthetic_page(w, h, i) for i in range(4)]
+    batch = torch.empty((nb, h, w, 4), dtype=torch.uint8, device=dev)
+    for i in range(nb):
+        batch[i] = torch.from_numpy(np.roll(base[i % 4], 53 * i, axis=0)).to(dev)
+    chain = CudaChain()
+    g = chain.gaussian(batch, torch.empty_like(batch))
+    s = chain.sobel(g, torch.empty_like(batch))
+    c = chain.canny(batch, torch.empty_like(batch), pages_per_launch=8)
+    torch.cuda.synchronize()
+    picks = [0, 1, 7, 8, 31, 40, 62, 63]
+
+    def check(i):
+        page = np.roll(base[i % 4], 53 * i, axis=0)
+        rg = oracle.gaussian(page, 2.0, 5)
+        return (i, np.array_equal(g[i].cpu().numpy(), rg),
+                np.array_equal(s[i].cpu().numpy(), oracle.sobel(rg)),
+                np.array_equal(c[i].cpu().numpy(), oracle.canny(page)))
+
+    with ThreadPoolExecutor(max_workers=8) as ex:
+        for i, ok_g, ok_s, ok_c in ex.map(check, picks):
+            assert ok_g and ok_s and ok_c, "page %d: gaussian %s sobel %s canny %s" % (i, ok_g, ok_s, ok_c)
