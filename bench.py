@@ -644,8 +644,8 @@ def run_b200(args):
             del sc6
         extras["ace_600dpi_row_bands"] = {
             "workload": "pf_apply_ace 4960x7016, 400 samples, rows split over %d GPU(s); NCCL scatter "
-                        "of the bands + broadcast of the samples' pixel values + two 6-double min/max "
-                        "all-reduces + band all-gather inside the timed region" % world,
+                        "of the bands + broadcast of the samples' pixel values + one exchange of the "
+                        "exact extremes (6 + 6 doubles) + band all-gather inside the timed region" % world,
             "ms": float(t6.item()), "mpx_s": w6 * h6 / (float(t6.item()) * 1e-3) / 1e6,
             "scaling": "strong", "equals_single_gpu_result": same6}
         # the same over NVLink peer memory: no scatter, no all-gather
@@ -673,7 +673,7 @@ def run_b200(args):
                     "workload": "the same page; every GPU reads its band out of rank 0's page and the "
                                 "rescale kernel writes it into every GPU's result over NVLink peer "
                                 "memory (torch symmetric memory); NCCL only for the sample values and "
-                                "the min/max exchanges",
+                                "the one exchange of the extremes",
                     "ms": float(tp6.item()), "mpx_s": w6 * h6 / (float(tp6.item()) * 1e-3) / 1e6,
                     "scaling": "strong", "equals_nccl_result_on_every_rank": bool(okp.item()),
                     "result_stores": "multimem.st to an NVLS multicast address" if peer.use_multicast

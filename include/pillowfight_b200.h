@@ -264,10 +264,12 @@ int pf_b200_dev_sobel_batch(const uint32_t *d_in, uint32_t *d_out,
  *
  *   0. pf_b200_dev_ace_minmax_init: once per page and device.
  *   1. pf_b200_dev_ace_scores: rows [row_begin, row_end) of the page.
- *   2. (multi-GPU only) all-reduce d_minmax[0..5]: min over the first 3, max
- *      over the last 3.
+ *   2. (optional) all-reduce d_minmax[0..5] across GPUs: min over the first
+ *      3, max over the last 3.  Pass 3 works from the extremes it finds there:
+ *      a band's own are enough, the page's leave it fewer pixels to look at.
  *   3. pf_b200_dev_ace_refine, same arguments as pass 1.  Not optional.
- *   4. (multi-GPU only) all-reduce d_minmax[6..11] the same way.
+ *   4. (multi-GPU only) all-reduce d_minmax[6..11]: min over [6..8], max over
+ *      [9..11] -- the one exchange the algorithm needs.
  *   5. pf_b200_dev_ace_scale, same arguments plus the destination: the
  *      band's RGBA8 rows into d_out_band ((row_end-row_begin)*width pixels).
  */
@@ -307,6 +309,14 @@ int pf_b200_dev_ace_scale_band(const uint32_t *d_band, int width, int height,
 		const int *d_samples, const uint32_t *d_sample_px, int nb_samples,
 		double slope, double limit,
 		void *d_scores, double *d_minmax, uint32_t *d_out_band, void *stream);
+
+/* What goes to such a GPU besides its rows, gathered where the whole page is,
+ * as one message of 3 * nb_samples ints: the sample table (x0, y0, x1, ...)
+ * followed by the nb_samples sample pixels (d_sample_px for the calls above is
+ * d_message + 2 * nb_samples).  The sample coordinates must lie inside the
+ * page. */
+int pf_b200_dev_ace_gather_samples(const uint32_t *d_page, int width, int height,
+		const int *d_samples, int nb_samples, int *d_message, void *stream);
 
 /* Pass 5 with several destinations: the band's rows are stored to nb_outs
  * images at once (d_outs: HOST array of nb_outs device pointers, 1..16, each

@@ -116,6 +116,8 @@ SIGNATURES = {
     "pf_b200_dev_ace_scale_band": (ctypes.c_int, [_u32p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                                   ctypes.c_int, _vp, _vp, ctypes.c_int, ctypes.c_double,
                                                   ctypes.c_double, _vp, _vp, _u32p, _vp]),
+    "pf_b200_dev_ace_gather_samples": (ctypes.c_int, [_u32p, ctypes.c_int, ctypes.c_int, _vp, ctypes.c_int,
+                                                      _vp, _vp]),
     "pf_b200_dev_ace_scale_to": (ctypes.c_int, [_u32p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                                 ctypes.c_int, _vp, _vp, ctypes.c_int, ctypes.c_double,
                                                 ctypes.c_double, _vp, _vp,

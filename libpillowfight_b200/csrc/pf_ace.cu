@@ -515,6 +515,21 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 	}
 }
 
+// The sample table and the samples' pixel values as one message of 3 N ints:
+// x0, y0, x1, y1, ..., then the N pixels (what a GPU that holds only a band
+// of the page needs besides its rows).
+__global__ void ace_gather_samples_kernel(const uint32_t *__restrict__ page, int w,
+		const int *__restrict__ samples_xy, int n, int *__restrict__ msg)
+{
+	pdl_wait();
+	for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+		const int2 s = __ldg(reinterpret_cast<const int2 *>(samples_xy) + k);
+		msg[2 * k] = s.x;
+		msg[2 * k + 1] = s.y;
+		msg[2 * n + k] = (int)__ldg(page + (size_t)s.y * w + s.x);
+	}
+}
+
 __global__ void ace_minmax_init_kernel(double *minmax, size_t n)
 {
 	pdl_wait();
@@ -1220,6 +1235,14 @@ __global__ void fp32_peak_kernel(float *sink, int iters, float a, float b)
 }
 
 }  // namespace
+
+int launch_ace_gather_samples(const uint32_t *page, int w, const int *samples_xy, int n, int *msg,
+		cudaStream_t st)
+{
+	PFB_CUDA(launch_pdl(ace_gather_samples_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st,
+			page, w, samples_xy, n, msg));
+	return PF_B200_OK;
+}
 
 int launch_ace_minmax_init(double *minmax, int w, int h, cudaStream_t st)
 {

@@ -1338,6 +1338,18 @@ int pf_b200_dev_ace_minmax_init(double *d_minmax, int width, int height, void *s
 	return launch_ace_minmax_init(d_minmax, width, height, static_cast<cudaStream_t>(stream));
 }
 
+int pf_b200_dev_ace_gather_samples(const uint32_t *d_page, int width, int height,
+		const int *d_samples, int nb_samples, int *d_message, void *stream)
+{
+	clear_error();
+	if (!d_page || !d_samples || !d_message)
+		return fail(PF_B200_EINVAL, "NULL device pointer");
+	if (width <= 0 || height <= 0 || nb_samples < 1)
+		return fail(PF_B200_EINVAL, "size %d x %d, %d samples", width, height, nb_samples);
+	return launch_ace_gather_samples(d_page, width, d_samples, nb_samples, d_message,
+			static_cast<cudaStream_t>(stream));
+}
+
 // One pass over a band.  d_band points at row row_begin; with d_sample_px ==
 // NULL the memory around it is the whole page (the samples are read from it).
 enum AcePass { ACE_SCORES, ACE_REFINE, ACE_SCALE };

@@ -146,6 +146,8 @@ AceScores ace_scores_at(void *block, size_t plane);
 // extremes first, then one entry per tile (pf_ace.cu, kMinmaxHead).
 size_t ace_minmax_doubles(int w, int h);
 int launch_ace_minmax_init(double *minmax, int w, int h, cudaStream_t st);
+int launch_ace_gather_samples(const uint32_t *page, int w, const int *samples_xy, int n, int *msg,
+		cudaStream_t st);
 // Pass 1, rows [row_begin, row_end): approximate scores (error bounded) into
 // the planes, their extremes folded into minmax[0..5] and the tile table.
 int launch_ace_scores(const uint32_t *in, const int *samples_xy,

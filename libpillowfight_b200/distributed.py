@@ -168,9 +168,15 @@ def ace_sharded(page, xy, slope, limit, compute, group=None, src=0):
     rows = mine[: b1 - b0]
 
     scores = compute.scores_band(rows, h, (b0, b1), xy, spx, slope, limit, minmax)
-    dist.all_reduce(minmax[0:3], op=dist.ReduceOp.MIN, group=group)
-    dist.all_reduce(minmax[3:6], op=dist.ReduceOp.MAX, group=group)
-    if compute.refine_band(rows, h, (b0, b1), xy, spx, slope, limit, scores, minmax):
+    # The one exchange the algorithm has: the page's extremes.  A band finds the
+    # exact extremes of its own rows from its own approximate ones (refine), so
+    # only the exact ones travel.  (A compute object without a refinement pass
+    # -- the CPU tests' oracle -- has exact scores already: its first six
+    # doubles are exchanged instead.)
+    if not compute.refine_band(rows, h, (b0, b1), xy, spx, slope, limit, scores, minmax):
+        dist.all_reduce(minmax[0:3], op=dist.ReduceOp.MIN, group=group)
+        dist.all_reduce(minmax[3:6], op=dist.ReduceOp.MAX, group=group)
+    else:
         dist.all_reduce(minmax[6:9], op=dist.ReduceOp.MIN, group=group)
         dist.all_reduce(minmax[9:12], op=dist.ReduceOp.MAX, group=group)
     band = compute.scale_band(rows, h, (b0, b1), xy, spx, slope, limit, scores, minmax)
@@ -215,7 +221,19 @@ class AcePeerBands:
         self.compute = CudaAceCompute()
         # NVLS multicast for the result stores when the fabric offers it
         self.use_multicast = bool(use_multicast and getattr(self._ho, "multicast_ptr", 0))
-        self._rows = self._dests = self._tmp = None
+        self._rows = self._dests = None
+        self._tmp = torch.empty(6, dtype=torch.float64, device=device)
+        self._msg = None
+        # the sample table and the samples' pixel values travel through peer
+        # memory too (up to this many samples; more go by NCCL broadcast)
+        self.max_peer_samples = 4096
+        self._msg_sym = symm.empty(3 * self.max_peer_samples, dtype=torch.int32, device=device)
+        self._hm = symm.rendezvous(self._msg_sym, self.group)
+        self._msg_src = {}
+        self._minmax = torch.empty(self._lib.pf_b200_ace_minmax_bytes(width, height) // 8,
+                                   dtype=torch.float64, device=device)
+        b0, b1 = row_bands(height, self.world)[self.rank]
+        self._scores = self.compute.new_scores(device, width, b1 - b0)
 
     def _exchange(self, minmax, lo):
         """min over minmax[lo:lo+3], max over minmax[lo+3:lo+6], in ONE
@@ -227,7 +245,16 @@ class AcePeerBands:
         torch.neg(t[0:3], out=minmax[lo:lo + 3])
         minmax[lo + 3:lo + 6].copy_(t[3:6])
 
-    def run(self, xy, slope, limit, src=0):
+    def run(self, xy, slope, limit, src=0, marks=None):
+        """marks: a list to which (phase name, CUDA event recorded at the END
+        of that phase) pairs are appended (tools/ace_bands_timeline.py)."""
+        def mark(name):
+            if marks is not None:
+                ev = torch.cuda.Event(enable_timing=True)
+                ev.record()
+                marks.append((name, ev))
+
+        mark("start")
         h, w, comp = self.h, self.w, self.compute
         b0, b1 = row_bands(h, self.world)[self.rank]
         n = xy.numel() // 2
@@ -235,22 +262,42 @@ class AcePeerBands:
         # sample table and sample values in one message; it also orders every
         # rank's reads of the page after the copy that put it there (same
         # stream on `src`)
-        msg = torch.empty(3 * n, dtype=torch.int32, device=dev)
+        if self._msg is None or self._msg.numel() != 3 * n:
+            self._msg = torch.empty(3 * n, dtype=torch.int32, device=dev)
+        msg = self._msg
+        by_peer = n <= self.max_peer_samples
         if self.rank == src:
-            msg[: 2 * n].copy_(xy)
-            msg[2 * n:].copy_(comp.sample_pixels(self.page, xy).view(torch.int32).view(-1))
-        dist.broadcast(msg, src=src, group=self.group)
+            if by_peer:
+                msg = self._msg_sym[: 3 * n]
+            self._capi.check(self._lib.pf_b200_dev_ace_gather_samples(
+                self.page.data_ptr(), w, h, xy.data_ptr(), n, msg.data_ptr(),
+                torch.cuda.current_stream().cuda_stream))
+        if by_peer:
+            # the holder's copy is in place: everyone else fetches it over NVLink
+            # (a device-side barrier and one small copy instead of a broadcast)
+            self._hm.barrier()
+            if self.rank != src:
+                if src not in self._msg_src:
+                    self._msg_src[src] = self._hm.get_buffer(src, (3 * self.max_peer_samples,), torch.int32)
+                msg.copy_(self._msg_src[src][: 3 * n])
+        else:
+            dist.broadcast(msg, src=src, group=self.group)
+        mark("broadcast of the samples")
         xy, spx = msg[: 2 * n], msg[2 * n:]
         if self._rows is None:
             self._rows = self._hp.get_buffer(src, (h, w, 4), torch.uint8)[b0:b1]       # peer memory
-            self._tmp = torch.empty(6, dtype=torch.float64, device=dev)
         rows = self._rows
-        minmax = comp.new_minmax(dev, w, h)
-        scores = comp.scores_band(rows, h, (b0, b1), xy, spx, slope, limit, minmax)
-        self._exchange(minmax, 0)
-        comp.refine_band(rows, h, (b0, b1), xy, spx, slope, limit, scores, minmax)
-        self._exchange(minmax, 6)
         st = torch.cuda.current_stream().cuda_stream
+        minmax = self._minmax
+        self._capi.check(self._lib.pf_b200_dev_ace_minmax_init(minmax.data_ptr(), w, h, st))
+        scores = comp.scores_band(rows, h, (b0, b1), xy, spx, slope, limit, minmax, out=self._scores)
+        mark("accumulation (band read over NVLink)")
+        # each band finds the exact extremes of its own rows; those are the one
+        # thing the bands have to tell each other
+        comp.refine_band(rows, h, (b0, b1), xy, spx, slope, limit, scores, minmax)
+        mark("exact extremes of the band")
+        self._exchange(minmax, 6)
+        mark("exchange of the extremes")
         mc = self._ho.multicast_ptr if self.use_multicast else 0
         args = (rows.data_ptr(), w, h, b0, b1, xy.data_ptr(), spx.data_ptr(), n, float(slope),
                 float(limit), scores.data_ptr(), minmax.data_ptr())
@@ -264,7 +311,9 @@ class AcePeerBands:
                 self._dests = [self._ho.get_buffer(r, (h, w, 4), torch.uint8)[b0:b1] for r in order]
             ptrs = (ctypes.c_void_p * len(self._dests))(*[d.data_ptr() for d in self._dests])
             self._capi.check(self._lib.pf_b200_dev_ace_scale_to(*args, ptrs, len(self._dests), st))
+        mark("rescale + fix-up, stores to every GPU")
         self._ho.barrier()          # every band has landed everywhere
+        mark("barrier")
         return self.out
 
 
