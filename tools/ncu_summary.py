@@ -19,6 +19,8 @@ COLS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
         "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
         "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+        "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active",
         "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
         "sm__throughput.avg.pct_of_peak_sustained_elapsed"]
 SCALE = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
@@ -51,7 +53,29 @@ def dram(name_part):
     return tot
 
 
-traffic = {"ace_scores_kernel": dram("ace_scores_kernel"), "gaussian": dram("gaussian"),
+def pct(name_part, col):
+    for name, d in kernels.items():
+        if name_part in name:
+            try:
+                return float(d[col])
+            except (KeyError, ValueError):
+                return None
+    return None
+
+
+rows_json = {"ace_scores_kernel": {
+    "issue_active_pct": pct("ace_scores_kernel", "smsp__issue_active.avg.pct_of_peak_sustained_active"),
+    "pipe_fma_cycles_active_pct": pct("ace_scores_kernel", "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active"),
+    "pipe_xu_pct": pct("ace_scores_kernel", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active"),
+    "pipe_alu_pct": pct("ace_scores_kernel", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"),
+    "warp_instructions": pct("ace_scores_kernel", "smsp__inst_executed.sum"),
+    "registers": pct("ace_scores_kernel", "launch__registers_per_thread"),
+    "source": "profiles/%s_ncu_summary.csv" % tag}}
+with open(os.path.join(ROOT, "profiles", "%s_ncu_rows.json" % tag), "w") as f:
+    json.dump(rows_json, f, indent=1)
+
+traffic = {"ace_scores_kernel": dram("ace_scores_kernel"), "ace_all_kernels": dram("ace_"),
+           "gaussian": dram("gaussian"),
            "sobel": dram("sobel_kernel"), "canny": dram("canny_"),
            "note": "dram__bytes_read.sum + dram__bytes_write.sum per launch from profiles/%s_ncu_summary.csv "
                    "(ncu --set full, tools/profile_step.py, A4 page; canny = classify + hysteresis). Writes that "
