@@ -628,7 +628,14 @@ def run_b200(args):
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         return float(tt.item())
 
+    # the extension that uploads the page once and returns all four results
+    def e2e_chain_step():
+        chk(lib.pf_b200_page_step(ctypes.byref(b_in), ctypes.byref(b_ace), ctypes.byref(b_g), ctypes.byref(b_s),
+                                  ctypes.byref(b_c), 100, xy_p, 10.0, 1000.0, 2.0, 5))
+
     ke = max(5, min(K, 30))
+    t_e2e_chain = timed_host_loop(e2e_chain_step, ke)
+    chain_views = [hv[k + 1].copy() for k in range(4)] if rank == 0 else None
     t_e2e_one = timed_host_loop(e2e_step, ke)
     t_e2e = timed_host_loop(e2e_step_threads, ke)
     for wk in workers:
@@ -682,7 +689,8 @@ def run_b200(args):
                   "pageable": [bool(np.array_equal(pg[k + 1], refs[k])) for k in range(4)],
                   "order": ["ace", "gaussian", "sobel", "canny"],
                   "against": "oracle/pf_oracle.c (bit for bit)"}
-        e2e_ok["all"] = all(e2e_ok["pinned"]) and all(e2e_ok["pageable"])
+        e2e_ok["page_step"] = [bool(np.array_equal(chain_views[k], refs[k])) for k in range(4)]
+        e2e_ok["all"] = all(e2e_ok["pinned"]) and all(e2e_ok["pageable"]) and all(e2e_ok["page_step"])
 
     # ---- extras: ACE 600 dpi, 400 samples, row bands over the ranks -----------
     extras = {}
@@ -870,6 +878,11 @@ def run_b200(args):
                     "one_thread": {"value": world * npix / t_e2e_one / 1e6, "unit": "Mpx/s",
                                    "ms_per_step": t_e2e_one * 1e3},
                     "result_checked": e2e_ok},
+            "e2e_page_step": {"value": world * npix / t_e2e_chain / 1e6, "unit": "Mpx/s",
+                              "ms_per_step": t_e2e_chain * 1e3, "h2d_bytes_per_step": nbytes + xy_host.nbytes,
+                              "d2h_bytes_per_step": 4 * nbytes,
+                              "api": "pf_b200_page_step (an extension, not the drop-in interface): one upload, "
+                                     "the four results of the step"},
             "e2e_pageable": {"value": world * npix / t_pageable / 1e6, "unit": "Mpx/s",
                              "ms_per_step": t_pageable * 1e3,
                              "api": "the same four calls on malloc'ed (pageable) bitmaps, in and out"},

@@ -161,6 +161,24 @@ int pf_b200_gaussian(const struct pf_bitmap *in, struct pf_bitmap *out,
 int pf_b200_sobel(const struct pf_bitmap *in, struct pf_bitmap *out);
 int pf_b200_canny(const struct pf_bitmap *in, struct pf_bitmap *out);
 
+/* An extension beside the drop-in calls (no counterpart in the reference's
+ * interface; its results are those of the calls it stands for): the whole step
+ * on one page with ONE upload.  Any of the four outputs may be NULL:
+ *   out_ace                = pf_b200_ace(in, nb_samples, sample_xy, slope, limit)
+ *   out_gaussian           = pf_b200_gaussian(in, sigma, nb_stddev)
+ *   out_sobel_of_gaussian  = pf_b200_sobel(of that blurred page)
+ *   out_canny              = pf_b200_canny(in)
+ * The four drop-in calls of such a step move the page to the GPU three times
+ * and the blurred page back and forth: 8 page transfers over PCIe; this call
+ * moves 1 plus one per result asked for.  The outputs must be distinct pages,
+ * none of them the input.  Pinned pages (pf_b200_host_alloc) of 512 rows or
+ * more take the overlapped path; anything else is served by the drop-in calls
+ * one after the other. */
+int pf_b200_page_step(const struct pf_bitmap *in, struct pf_bitmap *out_ace,
+		struct pf_bitmap *out_gaussian, struct pf_bitmap *out_sobel_of_gaussian,
+		struct pf_bitmap *out_canny, int nb_samples, const int *sample_xy,
+		double slope, double limit, double sigma, int nb_stddev);
+
 /* Draw nb_samples pairs the way pf_apply_ace does (x = rand() % width, then
  * y = rand() % height, per sample; upstream _ace.c: create_random_pairs). */
 void pf_b200_ace_draw_samples(int nb_samples, int width, int height,

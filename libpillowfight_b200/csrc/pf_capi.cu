@@ -165,7 +165,7 @@ struct Context {
 	cudaStream_t st_down = nullptr;      // device -> host copies of a streamed call
 	cudaEvent_t ev_up[kMaxBands] = {};   // band b is in HBM
 	cudaEvent_t ev_done[kMaxBands] = {}; // band b's result is ready
-	Buffer d_in, d_out, d_scratch, d_scores, d_small;
+	Buffer d_in, d_out, d_scratch, d_scores, d_small, d_blur;
 	Buffer h_stage;   // pinned
 
 	~Context()
@@ -175,7 +175,7 @@ struct Context {
 		if (dev < 0)
 			return;
 		cudaSetDevice(dev);
-		Buffer *bufs[] = { &d_in, &d_out, &d_scratch, &d_scores, &d_small };
+		Buffer *bufs[] = { &d_in, &d_out, &d_scratch, &d_scores, &d_small, &d_blur };
 		for (Buffer *b : bufs)
 			if (b->p)
 				cudaFree(b->p);
@@ -1083,6 +1083,220 @@ static int run_ace_impl(const struct pf_bitmap *in, struct pf_bitmap *out,
 	return download(c, out->pixels, c.d_out.p, bytes);
 }
 
+// ---------------------------------------------------------------------------
+// The whole step on one page with ONE upload (an extension beside the drop-in
+// entry points; include/pillowfight_b200.h, pf_b200_page_step): ACE, Gaussian,
+// Sobel of the blurred page and Canny, any subset.  The four drop-in calls of
+// such a step move the page up three times, the blurred page down and up
+// again: 8 page transfers; this moves 1 + the results asked for.
+// ---------------------------------------------------------------------------
+
+struct StepArgs {
+	const struct pf_bitmap *in;
+	struct pf_bitmap *ace, *gauss, *sobel, *canny;
+	int nb_samples;
+	const int *sample_xy;
+	double slope, limit, sigma;
+	int nb_stddev;
+};
+
+// Pinned pages of at least 512 rows: bands go up on one stream; each band is
+// accumulated (ACE), blurred and classified (Canny) as soon as it and the band
+// below it have arrived; blurred and classified bands go back by DMA as they
+// finish; Sobel runs on the blurred page in HBM and ACE's rescale after the
+// page-wide extremes are known, both writing straight into the caller's pages.
+static int run_step_streamed(Context &c, const StepArgs &a, const Taps &taps)
+{
+	const int w = a.in->size.x, h = a.in->size.y;
+	const size_t npix = (size_t)w * h;
+	const size_t bytes = npix * sizeof(uint32_t);
+	int rc;
+	if ((rc = grow(c.d_in, bytes, false)))
+		return rc;
+	const bool want_blur = a.gauss || a.sobel;
+	if (want_blur && (rc = grow(c.d_blur, bytes, false)))
+		return rc;
+	if (a.canny && ((rc = grow(c.d_out, bytes, false)) || (rc = grow_canny_scratch(c, w, h))
+			|| (rc = grow(c.h_stage, 64, true))))
+		return rc;
+	const size_t mm_bytes = (ace_minmax_doubles(w, h) * sizeof(double) + 63) / 64 * 64;
+	if (a.ace && ((rc = grow(c.d_scores, ace_scores_bytes(w, h), false))
+			|| (rc = grow(c.d_small, mm_bytes + sizeof(int) * 3 * (size_t)a.nb_samples, false))))
+		return rc;
+	const uint32_t *src = reinterpret_cast<const uint32_t *>(a.in->pixels);
+	const uint32_t *din = static_cast<const uint32_t *>(c.d_in.p);
+	uint32_t *dblur = static_cast<uint32_t *>(c.d_blur.p);
+	uint32_t *dcanny = static_cast<uint32_t *>(c.d_out.p);
+	double *minmax = static_cast<double *>(c.d_small.p);
+	int *d_xy = a.ace ? reinterpret_cast<int *>(static_cast<char *>(c.d_small.p) + mm_bytes) : nullptr;
+	uint32_t *d_spx = a.ace ? reinterpret_cast<uint32_t *>(d_xy + 2 * (size_t)a.nb_samples) : nullptr;
+	AceScores sc = {};
+	AceParams p = { w, h, 0, h, a.nb_samples, a.slope, a.limit };
+	if (a.ace) {
+		sc = ace_scores_at(c.d_scores.p, npix);
+		p.score_row0 = 0;
+		p.score_plane = (long)npix;
+		uint32_t spx[4096];
+		for (int i = 0; i < a.nb_samples; i++)
+			spx[i] = src[(size_t)a.sample_xy[2 * i + 1] * w + a.sample_xy[2 * i]];
+		PFB_CUDA(cudaMemcpyAsync(d_xy, a.sample_xy, sizeof(int) * 2 * (size_t)a.nb_samples,
+				cudaMemcpyHostToDevice, c.st));
+		PFB_CUDA(cudaMemcpyAsync(d_spx, spx, sizeof(uint32_t) * (size_t)a.nb_samples,
+				cudaMemcpyHostToDevice, c.st));
+		p.sample_px = d_spx;
+		if ((rc = launch_ace_minmax_init(minmax, w, h, c.st)))
+			return rc;
+	}
+	if (a.canny && (rc = launch_canny_begin(w, h, c.d_scratch.p, c.d_scratch.cap, c.st, true)))
+		return rc;
+
+	const int rows = band_rows_for(h);
+	const int nb = (h + rows - 1) / rows;
+	for (int b = 0; b < nb; b++) {
+		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
+		PFB_CUDA(cudaMemcpyAsync(const_cast<uint32_t *>(din) + (size_t)y0 * w, src + (size_t)y0 * w,
+				(size_t)(y1 - y0) * w * sizeof(uint32_t), cudaMemcpyHostToDevice, c.st_up));
+		PFB_CUDA(cudaEventRecord(c.ev_up[b], c.st_up));
+	}
+	uint32_t *host_gauss = a.gauss ? reinterpret_cast<uint32_t *>(a.gauss->pixels) : nullptr;
+	uint32_t *host_canny = a.canny ? reinterpret_cast<uint32_t *>(a.canny->pixels) : nullptr;
+	for (int b = 0; b < nb; b++) {
+		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
+		const size_t off = (size_t)y0 * w, len = (size_t)(y1 - y0) * w * sizeof(uint32_t);
+		PFB_CUDA(cudaStreamWaitEvent(c.st, c.ev_up[b + 1 < nb ? b + 1 : b], 0));
+		if (a.ace) {
+			p.row_begin = y0;
+			p.row_end = y1;
+			if ((rc = launch_ace_scores(din, d_xy, p, sc, minmax, c.st)))
+				return rc;
+		}
+		if (want_blur && (rc = launch_gaussian(din, dblur, w, h, 1, taps, c.st, y0, y1)))
+			return rc;
+		if (a.canny && (rc = launch_canny_classify_rows(din, dcanny, w, h, y0, y1, canny_thresholds(),
+				c.d_scratch.p, c.st)))
+			return rc;
+		if (a.gauss || a.canny) {
+			PFB_CUDA(cudaEventRecord(c.ev_done[b], c.st));
+			PFB_CUDA(cudaStreamWaitEvent(c.st_down, c.ev_done[b], 0));
+			if (a.gauss)
+				PFB_CUDA(cudaMemcpyAsync(host_gauss + off, dblur + off, len, cudaMemcpyDeviceToHost, c.st_down));
+			if (a.canny)
+				PFB_CUDA(cudaMemcpyAsync(host_canny + off, dcanny + off, len, cudaMemcpyDeviceToHost, c.st_down));
+		}
+	}
+	int *weak_count = static_cast<int *>(c.h_stage.p);
+	if (a.canny) {
+		if ((rc = launch_canny_resolve(dcanny, w, h, c.d_scratch.p, c.st)))
+			return rc;
+		PFB_CUDA(cudaMemcpyAsync(weak_count, static_cast<int *>(c.d_scratch.p) + 3, sizeof(int),
+				cudaMemcpyDeviceToHost, c.st));
+		PFB_CUDA(cudaEventRecord(c.ev_done[0], c.st));
+	}
+	if (a.sobel) {
+		uint32_t *to = static_cast<uint32_t *>(device_alias(a.sobel->pixels));
+		if (!to)
+			return fail(PF_B200_ECUDA, "the sobel page is not mapped for the device");
+		if ((rc = launch_sobel(dblur, to, w, h, 1, c.st)))
+			return rc;
+	}
+	if (a.ace) {
+		uint32_t *to = static_cast<uint32_t *>(device_alias(a.ace->pixels));
+		if (!to)
+			return fail(PF_B200_ECUDA, "the ace page is not mapped for the device");
+		p.row_begin = 0;
+		p.row_end = h;
+		if ((rc = launch_ace_refine(din, d_xy, p, sc, minmax, c.st))
+				|| (rc = launch_ace_scale(p, sc, minmax, 0, h, 0, &to, 1, false, c.st))
+				|| (rc = launch_ace_fixup(din, d_xy, p, sc, minmax, 0, 0, &to, 1, false, c.st)))
+			return rc;
+	}
+	if (a.canny) {
+		// the weak pixels' verdicts into the caller's page, after its bands have landed
+		PFB_CUDA(cudaEventSynchronize(c.ev_done[0]));
+		PFB_CUDA(cudaStreamSynchronize(c.st_down));
+		if (*weak_count > 0) {
+			uint32_t *mirror = static_cast<uint32_t *>(device_alias(a.canny->pixels));
+			if (mirror && (size_t)*weak_count <= npix / 64) {
+				if ((rc = launch_canny_patch(dcanny, mirror, c.d_scratch.p, c.st)))
+					return rc;
+			} else {
+				PFB_CUDA(cudaMemcpyAsync(host_canny, dcanny, bytes, cudaMemcpyDeviceToHost, c.st));
+			}
+		}
+	}
+	PFB_CUDA(cudaStreamSynchronize(c.st_down));
+	PFB_CUDA(cudaStreamSynchronize(c.st));
+	return PF_B200_OK;
+}
+
+static int run_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
+		int nb_samples, const int *sample_xy, double slope, double limit);
+
+static int run_step(const StepArgs &a)
+{
+	clear_error();
+	if (!a.in || !a.in->pixels || a.in->size.x <= 0 || a.in->size.y <= 0)
+		return fail(PF_B200_EINVAL, "NULL or empty input bitmap");
+	struct pf_bitmap *outs[4] = { a.ace, a.gauss, a.sobel, a.canny };
+	bool any = false, pinned = is_pinned(a.in->pixels);
+	for (int i = 0; i < 4; i++) {
+		if (!outs[i])
+			continue;
+		any = true;
+		int rc = check_bitmaps(a.in, outs[i]);
+		if (rc)
+			return rc;
+		if (outs[i]->pixels == a.in->pixels)
+			return fail(PF_B200_EINVAL, "page step: an output page is the input page");
+		for (int j = 0; j < i; j++)
+			if (outs[j] && outs[j]->pixels == outs[i]->pixels)
+				return fail(PF_B200_EINVAL, "page step: two outputs share a page");
+		pinned = pinned && is_pinned(outs[i]->pixels);
+	}
+	if (!any)
+		return fail(PF_B200_EINVAL, "page step: no output asked for");
+	if (a.ace && (a.nb_samples < 1 || !a.sample_xy))
+		return fail(PF_B200_EINVAL, "ace: nb_samples %d", a.nb_samples);
+	const int w = a.in->size.x, h = a.in->size.y;
+	if (a.ace)
+		for (int i = 0; i < a.nb_samples; i++)
+			if (a.sample_xy[2 * i] < 0 || a.sample_xy[2 * i] >= w
+					|| a.sample_xy[2 * i + 1] < 0 || a.sample_xy[2 * i + 1] >= h)
+				return fail(PF_B200_EINVAL, "ace: sample %d (%d, %d) outside the page",
+						i, a.sample_xy[2 * i], a.sample_xy[2 * i + 1]);
+	Taps taps = {};
+	int rc;
+	if ((a.gauss || a.sobel) && (rc = make_taps(a.sigma, a.nb_stddev, taps)))
+		return rc;
+	if (pinned && h >= 512 && (!a.ace || a.nb_samples <= 4096)) {
+		Context &c = t_ctx;
+		if ((rc = ctx_init(c)))
+			return rc;
+		return drained(c, run_step_streamed(c, a, taps));
+	}
+	// small or pageable pages: the drop-in calls one after the other (the blurred
+	// page into a scratch page when the caller does not want it)
+	if (a.ace && (rc = run_ace(a.in, a.ace, a.nb_samples, a.sample_xy, a.slope, a.limit)))
+		return rc;
+	if (a.gauss || a.sobel) {
+		struct pf_bitmap tmp = *a.in;
+		std::vector<uint32_t> scratch_page;
+		struct pf_bitmap *blur = a.gauss;
+		if (!blur) {
+			scratch_page.resize((size_t)w * h);
+			tmp.pixels = reinterpret_cast<union pf_pixel *>(scratch_page.data());
+			blur = &tmp;
+		}
+		if ((rc = run_stencil(OP_GAUSSIAN, a.in, blur, a.sigma, a.nb_stddev)))
+			return rc;
+		if (a.sobel && (rc = run_stencil(OP_SOBEL, blur, a.sobel, 0.0, 0)))
+			return rc;
+	}
+	if (a.canny && (rc = run_stencil(OP_CANNY, a.in, a.canny, 0.0, 0)))
+		return rc;
+	return PF_B200_OK;
+}
+
 static int run_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
 		int nb_samples, const int *sample_xy, double slope, double limit)
 {
@@ -1151,6 +1365,16 @@ int pf_b200_sobel(const struct pf_bitmap *in, struct pf_bitmap *out)
 int pf_b200_canny(const struct pf_bitmap *in, struct pf_bitmap *out)
 {
 	return run_stencil(OP_CANNY, in, out, 0.0, 0);
+}
+
+int pf_b200_page_step(const struct pf_bitmap *in, struct pf_bitmap *out_ace,
+		struct pf_bitmap *out_gaussian, struct pf_bitmap *out_sobel_of_gaussian,
+		struct pf_bitmap *out_canny, int nb_samples, const int *sample_xy,
+		double slope, double limit, double sigma, int nb_stddev)
+{
+	const StepArgs a = { in, out_ace, out_gaussian, out_sobel_of_gaussian, out_canny,
+		nb_samples, sample_xy, slope, limit, sigma, nb_stddev };
+	return run_step(a);
 }
 
 void pf_apply_ace(const struct pf_bitmap *in, struct pf_bitmap *out,

@@ -868,3 +868,69 @@ def test_config5_page_batch_at_a4(gpu, oracle):
     with ThreadPoolExecutor(max_workers=8) as ex:
         for i, ok_g, ok_s, ok_c in ex.map(check, picks):
             assert ok_g and ok_s and ok_c, "page %d: gaussian %s sobel %s canny %s" % (i, ok_g, ok_s, ok_c)
+
+
+def test_page_step_one_upload(gpu, oracle):
+    """pf_b200_page_step: ACE, Gaussian, Sobel of the blurred page and Canny of a
+    page from one upload -- on pinned pages (the overlapped path), with subsets
+    of the outputs, and on ordinary memory (served by the drop-in calls)."""
+    from libpillowfight_b200 import _capi
+    lib = _capi.lib
+    w, h, n = 620, 877, 60
+    page = synthetic_page(w, h, 3)
+    xy = oracle.ace_draw_samples(n, w, h, 31)
+    xyp = xy.ctypes.data_as(ctypes.POINTER(ctypes.c_int))
+    rg = oracle.gaussian(page, 2.0, 5)
+    refs = [oracle.ace_with_samples(page, xy, 10.0, 1000.0, nb_threads=8), rg, oracle.sobel(rg),
+            oracle.canny(page)]
+    nbytes = page.nbytes
+    pin = lib.pf_b200_host_alloc(5 * nbytes)
+    assert pin
+    try:
+        views = [np.ctypeslib.as_array((ctypes.c_uint8 * nbytes).from_address(pin + k * nbytes)).reshape(h, w, 4)
+                 for k in range(5)]
+        views[0][:] = page
+
+        def bm(ptr):
+            b = _capi.PfBitmap()
+            b.size.x, b.size.y, b.pixels = w, h, ptr
+            return b
+
+        bms = [bm(pin + k * nbytes) for k in range(5)]
+        for wanted in ((1, 1, 1, 1), (0, 0, 1, 0), (1, 0, 0, 1), (0, 1, 0, 0)):
+            for v in views[1:]:
+                v[:] = 0x5A
+            outs = [ctypes.byref(bms[k + 1]) if wanted[k] else None for k in range(4)]
+            _capi.check(lib.pf_b200_page_step(ctypes.byref(bms[0]), *outs, n, xyp, 10.0, 1000.0, 2.0, 5))
+            for k in range(4):
+                if wanted[k]:
+                    assert_exact(views[k + 1], refs[k], "page step %s output %d" % (wanted, k))
+                else:
+                    assert (views[k + 1] == 0x5A).all()
+        # refused: an output that is the input, two outputs on one page, nothing asked for
+        assert lib.pf_b200_page_step(ctypes.byref(bms[0]), ctypes.byref(bms[0]), None, None, None,
+                                     n, xyp, 10.0, 1000.0, 2.0, 5) == _capi.PF_B200_EINVAL
+        assert lib.pf_b200_page_step(ctypes.byref(bms[0]), None, ctypes.byref(bms[1]), ctypes.byref(bms[1]), None,
+                                     n, xyp, 10.0, 1000.0, 2.0, 5) == _capi.PF_B200_EINVAL
+        assert lib.pf_b200_page_step(ctypes.byref(bms[0]), None, None, None, None,
+                                     n, xyp, 10.0, 1000.0, 2.0, 5) == _capi.PF_B200_EINVAL
+    finally:
+        lib.pf_b200_host_free(pin)
+    # ordinary memory and a small page: the same answers through the drop-in calls
+    small = synthetic_page(150, 90, 4)
+    xs = oracle.ace_draw_samples(20, 150, 90, 5)
+    outs = [np.empty_like(small) for _ in range(4)]
+
+    def bma(a):
+        b = _capi.PfBitmap()
+        b.size.x, b.size.y, b.pixels = a.shape[1], a.shape[0], a.ctypes.data
+        return b
+
+    b_in, b_outs = bma(small), [bma(o) for o in outs]
+    _capi.check(lib.pf_b200_page_step(ctypes.byref(b_in), ctypes.byref(b_outs[0]), None, ctypes.byref(b_outs[2]),
+                                      ctypes.byref(b_outs[3]), 20,
+                                      xs.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), 10.0, 1000.0, 2.0, 5))
+    sg = oracle.gaussian(small, 2.0, 5)
+    assert_exact(outs[0], oracle.ace_with_samples(small, xs, 10.0, 1000.0), "page step small ace")
+    assert np.array_equal(outs[2], oracle.sobel(sg))
+    assert np.array_equal(outs[3], oracle.canny(small))
