@@ -429,17 +429,26 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 			}
 		}
 
-		// score = 2 * sum(w u) / sum(w) - 1.  Ties first, by exact integer tests
-		// against the extremes of the tile's staged samples (a superset of the
-		// samples that count for this pixel: a tie that only holds for the
-		// subset is not claimed and takes the ordinary route).
-		const int smin[3] = { sh.smin[0], sh.smin[1], sh.smin[2] };
-		const int smax[3] = { sh.smax[0], sh.smax[1], sh.smax[2] };
+		// score = 2 * sum(w u) / sum(w) - 1, and the ties: exact comparisons of the
+		// pixel with the extremes of the tile's staged samples (a superset of
+		// the samples that count for this pixel: a tie that only holds for the
+		// subset is not claimed and takes the ordinary route).  All values are
+		// small integers, exact as floats.
+		float tie_hi[3], tie_lo[3], tie_eq[3];
 #pragma unroll
-		for (int r = 0; r < kRows; r++) {
-			const int y = y0 + r;
-			if (y >= cs.row_begin && y < cs.row_end && y < tile_y1 && x < cs.w) {
-				const size_t o = (size_t)(y - cs.score_row0) * cs.w + x;
+		for (int c = 0; c < 3; c++) {
+			const int lo = sh.smin[c], hi = sh.smax[c];
+			tie_hi[c] = (float)(hi + cs.dsat);          // p >= this: every difference saturates high
+			tie_lo[c] = (float)(lo - cs.dsat);          // p <= this: ... low
+			tie_eq[c] = lo == hi ? (float)lo : -1.f;    // p == this: every difference is zero
+		}
+		if (x < cs.w) {
+			float *row = scores + ((size_t)(y0 - cs.score_row0) * cs.w + x);
+#pragma unroll
+			for (int r = 0; r < kRows; r++, row += cs.w) {
+				const int y = y0 + r;
+				if (y < cs.row_begin || y >= cs.row_end || y >= tile_y1)
+					continue;
 				float a[4], lo, hi;
 #pragma unroll
 				for (int c = 0; c < 4; c++) {
@@ -451,29 +460,23 @@ ace_scores_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 				// makes its sums infinite or NaN, and its score NaN
 				const bool live = a[3] > 0.f && a[3] <= FLT_MAX;
 				const float den = 0.5f * a[3];
-				const float rden = __frcp_rn(den);
-				// (the pixel again, from L1/L2: not kept in registers across the loop)
-				const uint32_t pix = __ldg(in + (size_t)y * cs.w + x);
+				float rden;
+				asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rden) : "f"(den));     // 2^-23: inside the bound's epilogue share
+				float *dst = row;
 #pragma unroll
-				for (int c = 0; c < 3; c++) {
-					const int p = (int)((pix >> (8 * c)) & 0xFF);
+				for (int c = 0; c < 3; c++, dst += plane) {
+					const float p = pv[r][c];
 					float s = (a[c] - den) * rden;
 					// keep approximate scores off the values that mean "tie"
-					if (s == 0.f)
-						s = 1e-30f;
-					else if (fabsf(s) >= 1.f)
-						s = copysignf(0.99999994f, s);
-					if (p - smax[c] >= cs.dsat)
-						s = 1.f;
-					else if (p - smin[c] <= -cs.dsat)
-						s = -1.f;
-					else if (smin[c] == p && smax[c] == p)
-						s = 0.f;
-					if (!live)
-						s = __int_as_float(0x7fc00000);
-					scores[c * plane + o] = s;
-					if (s < mn[c]) mn[c] = s;     // NaN never enters
-					if (s > mx[c]) mx[c] = s;
+					s = fminf(fmaxf(s, -0.99999994f), 0.99999994f);
+					s = s == 0.f ? 1e-30f : s;
+					s = p >= tie_hi[c] ? 1.f : s;
+					s = p <= tie_lo[c] ? -1.f : s;
+					s = p == tie_eq[c] ? 0.f : s;
+					s = live ? s : __int_as_float(0x7fc00000);
+					*dst = s;
+					mn[c] = fminf(mn[c], s);      // NaN never enters: fminf / fmaxf return the other operand
+					mx[c] = fmaxf(mx[c], s);
 				}
 			}
 		}
