@@ -161,6 +161,22 @@ int pf_b200_gaussian(const struct pf_bitmap *in, struct pf_bitmap *out,
 int pf_b200_sobel(const struct pf_bitmap *in, struct pf_bitmap *out);
 int pf_b200_canny(const struct pf_bitmap *in, struct pf_bitmap *out);
 
+/* An extension (no counterpart in the reference's interface; the result is
+ * pf_b200_ace's): ACE of one page with its row bands on several GPUs of this
+ * process -- BASELINE.json config 4 for a C caller that owns the GPUs itself,
+ * without torch or NCCL.  devices: nb_devices distinct device ordinals, or NULL
+ * for devices 0 .. nb_devices-1 (nb_devices <= 0: every visible device).  Each
+ * GPU is sent its band over its own PCIe link, accumulates it as it arrives
+ * and finds the exact extremes of its band; the 12 doubles of every GPU are
+ * folded on the host (the one exchange the algorithm has) and each GPU
+ * rescales and returns its band.  Needs pinned pages (pf_b200_host_alloc), out
+ * of place, and bands of at least 256 rows; anything else is served by
+ * pf_b200_ace on the first device.  The calling thread's current device is
+ * restored on return. */
+int pf_b200_ace_multi_gpu(const struct pf_bitmap *in, struct pf_bitmap *out,
+		int nb_samples, const int *sample_xy, double slope, double limit,
+		const int *devices, int nb_devices);
+
 /* An extension beside the drop-in calls (no counterpart in the reference's
  * interface; its results are those of the calls it stands for): the whole step
  * on one page with ONE upload.  Any of the four outputs may be NULL:

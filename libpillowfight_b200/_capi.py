@@ -79,6 +79,8 @@ SIGNATURES = {
     "pf_b200_gaussian": (ctypes.c_int, [_bp, _bp, ctypes.c_double, ctypes.c_int]),
     "pf_b200_sobel": (ctypes.c_int, [_bp, _bp]),
     "pf_b200_canny": (ctypes.c_int, [_bp, _bp]),
+    "pf_b200_ace_multi_gpu": (ctypes.c_int, [_bp, _bp, ctypes.c_int, _ip, ctypes.c_double, ctypes.c_double,
+                                             _ip, ctypes.c_int]),
     "pf_b200_page_step": (ctypes.c_int, [_bp, _bp, _bp, _bp, _bp, ctypes.c_int, _ip, ctypes.c_double,
                                          ctypes.c_double, ctypes.c_double, ctypes.c_int]),
     "pf_b200_ace_draw_samples": (None, [ctypes.c_int, ctypes.c_int, ctypes.c_int, _ip]),

@@ -5,6 +5,7 @@
 //   host bitmap -> (staging) -> HBM -> kernels -> HBM -> (staging) -> host bitmap
 // and returns after the result is in the caller's memory.  There is no CPU
 // implementation behind any of them: without a CUDA device they fail.
+#include <cfloat>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -1301,6 +1302,239 @@ static int run_ace(const struct pf_bitmap *in, struct pf_bitmap *out,
 	return (rc != PF_B200_OK && t_ctx.st) ? drained(t_ctx, rc) : rc;
 }
 
+// ---------------------------------------------------------------------------
+// ACE of one page with its row bands on several GPUs of this process (an
+// extension; include/pillowfight_b200.h, pf_b200_ace_multi_gpu): what
+// libpillowfight_b200/distributed.py does across processes, for a C caller
+// that owns all the GPUs itself.  Each GPU is sent its band of rows over its
+// own PCIe link (and the samples' pixel values), accumulates it as it arrives
+// and finds the exact extremes of its band; the host folds the 12 doubles of
+// every GPU and sends the result back -- the one exchange the algorithm has --
+// and each GPU rescales its band and returns it.
+// ---------------------------------------------------------------------------
+
+struct DeviceSlot {
+	int dev = -1;
+	cudaStream_t st = nullptr, st_up = nullptr;
+	cudaEvent_t ev_up[kMaxBands] = {};
+	Buffer d_rows, d_out, d_scores, d_small;
+	double *h_mm = nullptr;       // pinned, 12 doubles
+};
+
+struct MultiContext {
+	std::vector<DeviceSlot> slots;
+	~MultiContext()
+	{
+		for (DeviceSlot &s : slots) {
+			if (s.dev < 0 || cudaSetDevice(s.dev) != cudaSuccess)
+				continue;
+			Buffer *bufs[] = { &s.d_rows, &s.d_out, &s.d_scores, &s.d_small };
+			for (Buffer *b : bufs)
+				if (b->p)
+					cudaFree(b->p);
+			if (s.h_mm)
+				cudaFreeHost(s.h_mm);
+			for (int i = 0; i < kMaxBands; i++)
+				if (s.ev_up[i])
+					cudaEventDestroy(s.ev_up[i]);
+			if (s.st_up)
+				cudaStreamDestroy(s.st_up);
+			if (s.st)
+				cudaStreamDestroy(s.st);
+		}
+	}
+};
+
+static thread_local MultiContext t_multi;
+
+static int device_slot(int dev, DeviceSlot **out)
+{
+	for (DeviceSlot &s : t_multi.slots)
+		if (s.dev == dev) {
+			*out = &s;
+			return PF_B200_OK;
+		}
+	PFB_CUDA(cudaSetDevice(dev));
+	DeviceSlot s;
+	s.dev = dev;
+	PFB_CUDA(cudaStreamCreateWithFlags(&s.st, cudaStreamNonBlocking));
+	PFB_CUDA(cudaStreamCreateWithFlags(&s.st_up, cudaStreamNonBlocking));
+	for (int i = 0; i < kMaxBands; i++)
+		PFB_CUDA(cudaEventCreateWithFlags(&s.ev_up[i], cudaEventDisableTiming));
+	PFB_CUDA(cudaMallocHost(reinterpret_cast<void **>(&s.h_mm), 12 * sizeof(double)));
+	t_multi.slots.push_back(s);
+	*out = &t_multi.slots.back();
+	return PF_B200_OK;
+}
+
+static int run_ace_multi_impl(const struct pf_bitmap *in, struct pf_bitmap *out, int nb_samples,
+		const int *sample_xy, double slope, double limit, const int *devices, int n)
+{
+	const int w = in->size.x, h = in->size.y;
+	const uint32_t *src = reinterpret_cast<const uint32_t *>(in->pixels);
+	uint32_t *dst = reinterpret_cast<uint32_t *>(out->pixels);
+	t_multi.slots.reserve(64);       // (pointers into the vector are held below)
+	std::vector<DeviceSlot *> slot(n);
+	int rc;
+	for (int d = 0; d < n; d++)
+		if ((rc = device_slot(devices[d], &slot[d])))
+			return rc;
+	std::vector<uint32_t> spx(nb_samples);
+	for (int i = 0; i < nb_samples; i++)
+		spx[i] = src[(size_t)sample_xy[2 * i + 1] * w + sample_xy[2 * i]];
+	const size_t mm_bytes = (ace_minmax_doubles(w, h) * sizeof(double) + 63) / 64 * 64;
+	struct Band {
+		int b0, b1;
+		AceParams p;
+		AceScores sc;
+		double *minmax;
+		int *d_xy;
+		const uint32_t *page;
+	};
+	std::vector<Band> band(n);
+
+	// every GPU: its rows go up in a few pieces, each accumulated as it arrives
+	for (int d = 0; d < n; d++) {
+		DeviceSlot &s = *slot[d];
+		Band &bd = band[d];
+		bd.b0 = (int)((long)h * d / n);
+		bd.b1 = (int)((long)h * (d + 1) / n);
+		const int rows = bd.b1 - bd.b0;
+		PFB_CUDA(cudaSetDevice(s.dev));
+		const size_t band_bytes = (size_t)rows * w * sizeof(uint32_t);
+		if ((rc = grow(s.d_rows, band_bytes, false)) || (rc = grow(s.d_out, band_bytes, false))
+				|| (rc = grow(s.d_scores, ace_scores_bytes(w, rows), false))
+				|| (rc = grow(s.d_small, mm_bytes + sizeof(int) * 3 * (size_t)nb_samples, false)))
+			return rc;
+		bd.minmax = static_cast<double *>(s.d_small.p);
+		bd.d_xy = reinterpret_cast<int *>(static_cast<char *>(s.d_small.p) + mm_bytes);
+		uint32_t *d_spx = reinterpret_cast<uint32_t *>(bd.d_xy + 2 * (size_t)nb_samples);
+		PFB_CUDA(cudaMemcpyAsync(bd.d_xy, sample_xy, sizeof(int) * 2 * (size_t)nb_samples,
+				cudaMemcpyHostToDevice, s.st));
+		PFB_CUDA(cudaMemcpyAsync(d_spx, spx.data(), sizeof(uint32_t) * (size_t)nb_samples,
+				cudaMemcpyHostToDevice, s.st));
+		if ((rc = launch_ace_minmax_init(bd.minmax, w, h, s.st)))
+			return rc;
+		bd.sc = ace_scores_at(s.d_scores.p, (size_t)rows * w);
+		// the kernels index the page; with the samples' values given they only
+		// ever read this band's rows of it
+		bd.page = static_cast<const uint32_t *>(s.d_rows.p) - (size_t)bd.b0 * w;
+		bd.p = AceParams{ w, h, bd.b0, bd.b1, nb_samples, slope, limit };
+		bd.p.sample_px = d_spx;
+		bd.p.score_row0 = bd.b0;
+		bd.p.score_plane = (long)rows * w;
+		int piece = (rows + 3) / 4;
+		if (piece < 256)
+			piece = 256;
+		int k = 0;
+		for (int y0 = bd.b0; y0 < bd.b1; y0 += piece, k++) {
+			const int y1 = (y0 + piece < bd.b1) ? y0 + piece : bd.b1;
+			PFB_CUDA(cudaMemcpyAsync(static_cast<uint32_t *>(s.d_rows.p) + (size_t)(y0 - bd.b0) * w,
+					src + (size_t)y0 * w, (size_t)(y1 - y0) * w * sizeof(uint32_t),
+					cudaMemcpyHostToDevice, s.st_up));
+			PFB_CUDA(cudaEventRecord(s.ev_up[k], s.st_up));
+			PFB_CUDA(cudaStreamWaitEvent(s.st, s.ev_up[k], 0));
+			AceParams pp = bd.p;
+			pp.row_begin = y0;
+			pp.row_end = y1;
+			if ((rc = launch_ace_scores(bd.page, bd.d_xy, pp, bd.sc, bd.minmax, s.st)))
+				return rc;
+		}
+		if ((rc = launch_ace_refine(bd.page, bd.d_xy, bd.p, bd.sc, bd.minmax, s.st)))
+			return rc;
+		PFB_CUDA(cudaMemcpyAsync(s.h_mm, bd.minmax + 6, 6 * sizeof(double), cudaMemcpyDeviceToHost, s.st));
+	}
+	// the one exchange: the exact extremes of the bands, folded on the host
+	double ext[6] = { DBL_MAX, DBL_MAX, DBL_MAX, -DBL_MAX, -DBL_MAX, -DBL_MAX };
+	for (int d = 0; d < n; d++) {
+		PFB_CUDA(cudaSetDevice(slot[d]->dev));
+		PFB_CUDA(cudaStreamSynchronize(slot[d]->st));
+		for (int c = 0; c < 3; c++) {
+			if (slot[d]->h_mm[c] < ext[c])
+				ext[c] = slot[d]->h_mm[c];
+			if (slot[d]->h_mm[3 + c] > ext[3 + c])
+				ext[3 + c] = slot[d]->h_mm[3 + c];
+		}
+	}
+	for (int d = 0; d < n; d++) {
+		DeviceSlot &s = *slot[d];
+		Band &bd = band[d];
+		PFB_CUDA(cudaSetDevice(s.dev));
+		for (int c = 0; c < 6; c++)
+			s.h_mm[6 + c] = ext[c];
+		PFB_CUDA(cudaMemcpyAsync(bd.minmax + 6, s.h_mm + 6, 6 * sizeof(double), cudaMemcpyHostToDevice, s.st));
+		uint32_t *to = static_cast<uint32_t *>(s.d_out.p);
+		if ((rc = launch_ace_scale(bd.p, bd.sc, bd.minmax, bd.b0, bd.b1 - bd.b0, 0, &to, 1, false, s.st))
+				|| (rc = launch_ace_fixup(bd.page, bd.d_xy, bd.p, bd.sc, bd.minmax, bd.b0, 0, &to, 1, false, s.st)))
+			return rc;
+		PFB_CUDA(cudaMemcpyAsync(dst + (size_t)bd.b0 * w, to, (size_t)(bd.b1 - bd.b0) * w * sizeof(uint32_t),
+				cudaMemcpyDeviceToHost, s.st));
+	}
+	for (int d = 0; d < n; d++) {
+		PFB_CUDA(cudaSetDevice(slot[d]->dev));
+		PFB_CUDA(cudaStreamSynchronize(slot[d]->st));
+	}
+	return PF_B200_OK;
+}
+
+static int run_ace_multi(const struct pf_bitmap *in, struct pf_bitmap *out, int nb_samples,
+		const int *sample_xy, double slope, double limit, const int *devices, int nb_devices)
+{
+	clear_error();
+	int rc = check_bitmaps(in, out);
+	if (rc)
+		return rc;
+	if (nb_samples < 1 || !sample_xy)
+		return fail(PF_B200_EINVAL, "ace: nb_samples %d", nb_samples);
+	const int w = in->size.x, h = in->size.y;
+	for (int i = 0; i < nb_samples; i++)
+		if (sample_xy[2 * i] < 0 || sample_xy[2 * i] >= w
+				|| sample_xy[2 * i + 1] < 0 || sample_xy[2 * i + 1] >= h)
+			return fail(PF_B200_EINVAL, "ace: sample %d (%d, %d) outside the page",
+					i, sample_xy[2 * i], sample_xy[2 * i + 1]);
+	int visible = 0;
+	if (cudaGetDeviceCount(&visible) != cudaSuccess || visible <= 0)
+		return fail(PF_B200_ENODEV, "no CUDA device is usable (%s); this build has no CPU path",
+				cudaGetErrorString(cudaGetLastError()));
+	std::vector<int> devs;
+	if (devices) {
+		for (int d = 0; d < nb_devices; d++) {
+			if (devices[d] < 0 || devices[d] >= visible)
+				return fail(PF_B200_EINVAL, "ace: device %d of %d visible", devices[d], visible);
+			for (int e = 0; e < d; e++)
+				if (devices[e] == devices[d])
+					return fail(PF_B200_EINVAL, "ace: device %d listed twice", devices[d]);
+			devs.push_back(devices[d]);
+		}
+	} else {
+		for (int d = 0; d < (nb_devices > 0 && nb_devices < visible ? nb_devices : visible); d++)
+			devs.push_back(d);
+	}
+	if (devs.empty() || devs.size() > 64)
+		return fail(PF_B200_EINVAL, "ace: %zu devices", devs.size());
+	// every band at least 256 rows; pinned pages (the bands go by DMA); in place is fine
+	// only out of place here (a band's result returns while other bands still go up)
+	int n = (int)devs.size();
+	if (n > h / 256)
+		n = h / 256;
+	int cur = 0;
+	PFB_CUDA(cudaGetDevice(&cur));
+	if (n < 2 || !is_pinned(in->pixels) || !is_pinned(out->pixels) || in->pixels == out->pixels) {
+		// nothing to split, or memory the DMA engines cannot reach: the one-GPU
+		// call, on the calling thread's device
+		return run_ace(in, out, nb_samples, sample_xy, slope, limit);
+	}
+	rc = run_ace_multi_impl(in, out, nb_samples, sample_xy, slope, limit, devs.data(), n);
+	if (rc != PF_B200_OK)
+		for (DeviceSlot &s : t_multi.slots)       // nothing of a failed call may still be in flight
+			if (cudaSetDevice(s.dev) == cudaSuccess) {
+				cudaStreamSynchronize(s.st_up);
+				cudaStreamSynchronize(s.st);
+			}
+	cudaSetDevice(cur);
+	return rc;
+}
+
 static void report(const char *who, int rc)
 {
 	if (rc == PF_B200_OK)
@@ -1362,6 +1596,13 @@ int pf_b200_sobel(const struct pf_bitmap *in, struct pf_bitmap *out)
 int pf_b200_canny(const struct pf_bitmap *in, struct pf_bitmap *out)
 {
 	return run_stencil(OP_CANNY, in, out, 0.0, 0);
+}
+
+int pf_b200_ace_multi_gpu(const struct pf_bitmap *in, struct pf_bitmap *out,
+		int nb_samples, const int *sample_xy, double slope, double limit,
+		const int *devices, int nb_devices)
+{
+	return run_ace_multi(in, out, nb_samples, sample_xy, slope, limit, devices, nb_devices);
 }
 
 int pf_b200_page_step(const struct pf_bitmap *in, struct pf_bitmap *out_ace,

@@ -934,3 +934,38 @@ def test_page_step_one_upload(gpu, oracle):
     assert_exact(outs[0], oracle.ace_with_samples(small, xs, 10.0, 1000.0), "page step small ace")
     assert np.array_equal(outs[2], oracle.sobel(sg))
     assert np.array_equal(outs[3], oracle.canny(small))
+
+
+def test_ace_multi_gpu_from_one_process(gpu, oracle):
+    """pf_b200_ace_multi_gpu: row bands on every visible GPU of this process
+    (one GPU: the call serves the page through pf_b200_ace), against the oracle."""
+    from libpillowfight_b200 import _capi
+    lib = _capi.lib
+    w, h, n = 620, 877, 60
+    page = synthetic_page(w, h, 6)
+    xy = oracle.ace_draw_samples(n, w, h, 9)
+    xyp = xy.ctypes.data_as(ctypes.POINTER(ctypes.c_int))
+    ref = oracle.ace_with_samples(page, xy, 10.0, 1000.0, nb_threads=8)
+    nbytes = page.nbytes
+    pin = lib.pf_b200_host_alloc(2 * nbytes)
+    assert pin
+    try:
+        src = np.ctypeslib.as_array((ctypes.c_uint8 * nbytes).from_address(pin)).reshape(h, w, 4)
+        dst = np.ctypeslib.as_array((ctypes.c_uint8 * nbytes).from_address(pin + nbytes)).reshape(h, w, 4)
+        src[:] = page
+        bi, bo = _capi.PfBitmap(), _capi.PfBitmap()
+        bi.size.x, bi.size.y, bi.pixels = w, h, pin
+        bo.size.x, bo.size.y, bo.pixels = w, h, pin + nbytes
+        for nd in (0, 1, 2, 3):
+            dst[:] = 0x5A
+            _capi.check(lib.pf_b200_ace_multi_gpu(ctypes.byref(bi), ctypes.byref(bo), n, xyp, 10.0, 1000.0, None, nd))
+            assert_exact(dst, ref, "ace on %d devices" % nd)
+        bad = (ctypes.c_int * 2)(0, 0)
+        if gpu.device_count() >= 2:
+            assert lib.pf_b200_ace_multi_gpu(ctypes.byref(bi), ctypes.byref(bo), n, xyp, 10.0, 1000.0, bad, 2) \
+                == _capi.PF_B200_EINVAL
+        bad[0] = 99
+        assert lib.pf_b200_ace_multi_gpu(ctypes.byref(bi), ctypes.byref(bo), n, xyp, 10.0, 1000.0, bad, 1) \
+            == _capi.PF_B200_EINVAL
+    finally:
+        lib.pf_b200_host_free(pin)
