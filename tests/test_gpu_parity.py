@@ -969,3 +969,34 @@ def test_ace_multi_gpu_from_one_process(gpu, oracle):
             == _capi.PF_B200_EINVAL
     finally:
         lib.pf_b200_host_free(pin)
+
+
+def test_ace_low_contrast_pages(gpu, oracle):
+    """Pages whose scores span a tiny range: the rescale magnifies the fast
+    pass's error until every pixel is 'uncertain' (the guard band reaches half
+    an output step) and the whole page goes through the exact passes; pages
+    that are flat except for a few pixels; a smooth ramp (neighbouring pixels'
+    scores closer than the error bound).  All must still equal the oracle."""
+    rng = np.random.default_rng(11)
+    w, h, n = 300, 200, 24
+    xy = oracle.ace_draw_samples(n, w, h, 6)
+    pages = {}
+    blank = np.full((h, w, 4), 255, dtype=np.uint8)
+    blank[..., :3] = 200 + rng.integers(0, 2, size=(h, w, 3), dtype=np.uint8)
+    pages["one level of noise"] = blank
+    faint = np.full((h, w, 4), 255, dtype=np.uint8)
+    faint[..., :3] = (90, 120, 150)
+    faint[50, 60, :3] = (91, 120, 150)
+    faint[150, 200, :3] = (90, 119, 150)
+    pages["flat with two pixels off by one"] = faint
+    ramp = np.full((h, w, 4), 255, dtype=np.uint8)
+    ramp[..., :3] = (np.arange(w)[None, :, None] * 40 // w + 100).astype(np.uint8)
+    pages["smooth ramp"] = ramp
+    dark = np.zeros((h, w, 4), dtype=np.uint8)
+    dark[..., 3] = 255
+    dark[..., :3] = rng.integers(0, 3, size=(h, w, 3), dtype=np.uint8)
+    pages["near black"] = dark
+    for name, page in pages.items():
+        for slope, limit in ((10.0, 1000.0), (3.3, 841.5)):
+            ref = oracle.ace_with_samples(page, xy, slope, limit, nb_threads=8)
+            assert_exact(gpu.ace(page, slope, limit, n, seed=6), ref, "%s, slope %g" % (name, slope))
