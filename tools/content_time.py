@@ -31,7 +31,9 @@ for _ in range(3):
     tex = (tex + np.roll(tex, 1, 0) + np.roll(tex, -1, 0) + np.roll(tex, 1, 1) + np.roll(tex, -1, 1)) / 5
 tex = np.clip(128 + tex * 160, 0, 255).astype(np.uint8)
 texture = np.stack([tex, tex, tex, np.full_like(tex, 255)], -1)
-contents = {"texture": np.ascontiguousarray(texture), "synthetic": synthetic_page(w, h, 0), "noise": uniform_random_page(w, h, seed=1),
+blank = np.full((h, w, 4), 255, dtype=np.uint8)
+blank[..., :3] = np.clip(232 + rng.integers(-2, 3, size=(h, w, 3)), 0, 255).astype(np.uint8)
+contents = {"blank + noise 2": blank, "texture": np.ascontiguousarray(texture), "synthetic": synthetic_page(w, h, 0), "noise": uniform_random_page(w, h, seed=1),
             "white": white, "flat gray": gray, "text on white": text}
 out = torch.empty((h, w, 4), dtype=torch.uint8, device=dev)
 scratch = torch.empty(lib.pf_b200_canny_scratch_bytes(w, h), dtype=torch.uint8, device=dev)
@@ -71,6 +73,7 @@ for name, arr in contents.items():
          timed(lambda: chk(lib.pf_b200_dev_ace_refine(*ace_args))),
          timed(lambda: chk(lib.pf_b200_dev_ace_scale(*ace_args[:-1], out.data_ptr(), st)))]
     import ctypes
-    hdr = torch.zeros(2, dtype=torch.int32)
-    hdr.copy_(scratch[:8].view(torch.int32))
-    print("%-14s %9.1f %9.1f %9.1f %9.1f %9.1f %9.1f   weak pixels %d" % ((name,) + tuple(t) + (int(hdr[0]),)))
+    hdr = torch.zeros(4, dtype=torch.int32)
+    hdr.copy_(scratch[:16].view(torch.int32))
+    print("%-14s %9.1f %9.1f %9.1f %9.1f %9.1f %9.1f   weak pixels %d  ace pixels redone %d" % (
+        (name,) + tuple(t) + (int(hdr[3]), int(scores[:256].view(torch.int32)[32]))))
