@@ -378,7 +378,7 @@ def run_b200(args):
     # run while the next page's kernels fill the GPU.  Everything forks from the
     # current stream at the start of the timed region and joins it at the end:
     # the events that time the region are recorded on that stream.
-    N_SLOTS = 2
+    N_SLOTS = int(os.environ.get("PF_BENCH_SLOTS", "2"))
     slots = [Slot(True) for _ in range(N_SLOTS)]
 
     # (the stage breakdown below)
