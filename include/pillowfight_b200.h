@@ -388,6 +388,14 @@ int pf_b200_dev_ace(const uint32_t *d_in, uint32_t *d_out, int width, int height
 /* Measures the FP64 FMA rate of the current device (the ACE roofline
  * denominator): returns TFLOP/s (FMA = 2 flops), or a negative PF_B200_E*. */
 double pf_b200_fp64_peak_tflops(void);
+/* ACE's exactness rests on two measured constants of the hardware: the worst
+ * relative error of the FP32 reciprocal square root the accumulation pass uses
+ * (which = 0: every mantissa of two binades; the bound assumes <= 1.25e-7) and
+ * of the FP64 one of the exact passes (which = 1: every argument it is ever
+ * given, the integers below 2^31; the bound assumes <= 2^-48).  Returns the
+ * worst error found on the current device, or a negative PF_B200_E*.
+ * tests/test_gpu_parity.py holds every device the tests run on to both. */
+double pf_b200_selftest_rsqrt_error(int which);
 /* The same for FP32 (the pipe the ACE accumulation pass runs on). */
 double pf_b200_fp32_peak_tflops(void);
 

@@ -134,6 +134,7 @@ SIGNATURES = {
                                        ctypes.c_double, ctypes.c_double, _vp, ctypes.c_size_t, _vp]),
     "pf_b200_fp64_peak_tflops": (ctypes.c_double, []),
     "pf_b200_fp32_peak_tflops": (ctypes.c_double, []),
+    "pf_b200_selftest_rsqrt_error": (ctypes.c_double, [ctypes.c_int]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

@@ -42,6 +42,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstdlib>
+#include <cstring>
 
 #include <cooperative_groups.h>
 
@@ -548,28 +549,33 @@ __global__ void ace_minmax_init_kernel(double *minmax, size_t n)
 // ---------------------------------------------------------------------------
 
 // 1/sqrt(x) for an integer-valued x < 2^31: MUFU.RSQ64H looks at the high word
-// of x only (20 mantissa bits: x is off by up to 2^-20, its root by 2^-21) and
-// is itself good to ~2^-22, so the estimate is within 2^-20.4; one Newton
-// step squares that: 1.5 * 2^-40.8 < 2^-40.  (The step: e = 1 - x y^2,
-// y' = y + (y/2) e; y/2 is an exponent decrement of the high word.)
+// of x only (20 mantissa bits) and is good to about 2^-20 of such an argument;
+// two Newton steps (each squares the error: e = 1 - x y^2, y' = y + (y/2) e;
+// y/2 is an exponent decrement of the high word) leave the rounding of the
+// last step, a few 2^-53.  pf_b200_selftest_rsqrt_error(1) measures the
+// result over every argument; the bound below assumes 2^-48.
 __device__ __forceinline__ double rsqrt_f64(double x)
 {
 	double y;
 	asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
-	const double e = fma(-(x * y), y, 1.0);
-	const double h = __hiloint2double(__double2hiint(y) - 0x00100000, __double2loint(y));
-	return fma(h, e, y);
+#pragma unroll
+	for (int i = 0; i < 2; i++) {
+		const double e = fma(-(x * y), y, 1.0);
+		const double h = __hiloint2double(__double2hiint(y) - 0x00100000, __double2loint(y));
+		y = fma(h, e, y);
+	}
+	return y;
 }
 
 // Bound on |FP64 score (ace_accurate_sums) - reference score|.  Both
 // approximate the same real number: the reference with one rounding in the
 // square root, one in each division and one per addition; this with weights
-// within 2^-40 (the score moves by at most twice that: the same weight is in
+// within 2^-48 (the score moves by at most twice that: the same weight is in
 // numerator and denominator), one rounding per FMA (in any order) and one
-// division: 2^-39 + (4 N + 64) * 2^-53, doubled for room.
+// division: 2^-47 + (4 N + 64) * 2^-53, doubled for room.
 __device__ __forceinline__ double ace_accurate_eps(int nb_samples)
 {
-	return 2.0 * (0x1p-39 + (4.0 * nb_samples + 64.0) * 0x1p-53);
+	return 2.0 * (0x1p-47 + (4.0 * nb_samples + 64.0) * 0x1p-53);
 }
 
 // What the exact passes read per sample, staged once per block: coordinates
@@ -1209,6 +1215,34 @@ ace_fixup_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sample
 	}
 }
 
+// The two error constants the bounds above rest on, measured on the device at
+// hand: the worst relative error of MUFU.RSQ (FP32) over every mantissa of an
+// even and an odd binade (the hardware treats all binades alike), and of
+// rsqrt_f64 over EVERY argument it is ever given here -- the integers below
+// 2^31.  worst: the maximum as the bit pattern of a non-negative double
+// (ordered like an integer).
+__global__ void rsqrt_selftest_kernel(int which, unsigned long long *worst)
+{
+	double mx = 0.0;
+	const uint64_t n = which == 0 ? (1ull << 24) : (1ull << 31);
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+		double got, x;
+		if (which == 0) {
+			const float xf = __uint_as_float(0x3F800000u + (uint32_t)i);      // 1 .. 4
+			x = (double)xf;
+			got = (double)rsqrt_f32(xf);
+		} else {
+			if (i == 0)
+				continue;
+			x = (double)i;
+			got = rsqrt_f64(__hiloint2double(0x43300000, (int)i) - 4503599627370496.0);
+		}
+		const double ref = 1.0 / sqrt(x);
+		mx = fmax(mx, fabs(got - ref) / ref);
+	}
+	atomicMax(worst, (unsigned long long)__double_as_longlong(mx));
+}
+
 // FP64 FMA rate probe: 8 independent chains per thread.
 __global__ void fp64_peak_kernel(double *sink, int iters, double a, double b)
 {
@@ -1499,6 +1533,22 @@ static double measure_fma_peak(K kern, T a, T b, const char *what)
 		return -(double)fail(PF_B200_ECUDA, "%s probe: %s", what, cudaGetErrorString(err));
 	const double flops = 2.0 * 8.0 * (double)iters * blocks * threads;
 	return flops / (best_ms * 1e-3) / 1e12;
+}
+
+double measure_rsqrt_error(int which)
+{
+	unsigned long long *d = nullptr, h = 0;
+	if (cudaMalloc(&d, sizeof(h)) != cudaSuccess)
+		return -(double)fail(PF_B200_ECUDA, "rsqrt self-test: cudaMalloc failed");
+	cudaMemset(d, 0, sizeof(h));
+	rsqrt_selftest_kernel<<<sm_count() * 8, 256>>>(which, d);
+	const cudaError_t err = cudaMemcpy(&h, d, sizeof(h), cudaMemcpyDeviceToHost);
+	cudaFree(d);
+	if (err != cudaSuccess)
+		return -(double)fail(PF_B200_ECUDA, "rsqrt self-test: %s", cudaGetErrorString(err));
+	double v;
+	memcpy(&v, &h, sizeof(v));
+	return v;
 }
 
 double measure_fp64_peak_tflops()

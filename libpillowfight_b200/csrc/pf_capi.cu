@@ -1992,6 +1992,16 @@ double pf_b200_fp64_peak_tflops(void)
 	return measure_fp64_peak_tflops();
 }
 
+double pf_b200_selftest_rsqrt_error(int which)
+{
+	clear_error();
+	if (which != 0 && which != 1)
+		return -(double)fail(PF_B200_EINVAL, "rsqrt self-test: which = %d", which);
+	if (pf_b200_device_count() <= 0)
+		return -(double)fail(PF_B200_ENODEV, "no CUDA device");
+	return measure_rsqrt_error(which);
+}
+
 double pf_b200_fp32_peak_tflops(void)
 {
 	clear_error();

@@ -169,5 +169,6 @@ int launch_ace_fixup(const uint32_t *in, const int *samples_xy, const AceParams 
 		uint32_t *const *outs, int nb_outs, bool multicast, cudaStream_t st);
 double measure_fp64_peak_tflops();
 double measure_fp32_peak_tflops();
+double measure_rsqrt_error(int which);
 
 }  // namespace pfb

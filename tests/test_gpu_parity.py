@@ -1000,3 +1000,16 @@ def test_ace_low_contrast_pages(gpu, oracle):
         for slope, limit in ((10.0, 1000.0), (3.3, 841.5)):
             ref = oracle.ace_with_samples(page, xy, slope, limit, nb_threads=8)
             assert_exact(gpu.ace(page, slope, limit, n, seed=6), ref, "%s, slope %g" % (name, slope))
+
+
+def test_ace_error_constants_hold_on_this_device(gpu):
+    """The two hardware constants ACE's error bounds assume (pf_ace.cu:
+    ace_score_eps, ace_accurate_eps), measured exhaustively on the device the
+    tests run on."""
+    from libpillowfight_b200 import _capi
+    e32 = _capi.lib.pf_b200_selftest_rsqrt_error(0)
+    e64 = _capi.lib.pf_b200_selftest_rsqrt_error(1)
+    assert 0.0 < e32 <= 1.25e-7, e32
+    assert 0.0 < e64 <= 2.0 ** -48, e64
+    print("rsqrt errors: FP32 %.3e (2^%.2f), FP64 after two Newton steps %.3e (2^%.2f)" % (
+        e32, np.log2(e32), e64, np.log2(e64)))
