@@ -275,7 +275,7 @@ def run_reference(args):
 class Stage:
     ACE, GAUSS, SOBEL, CANNY = range(4)
     NAMES = ["ace", "gaussian", "sobel", "canny"]
-    LAUNCHES = [5, 1, 1, 2]     # kernels per call (memsets not counted)
+    LAUNCHES = [6, 1, 1, 4]     # kernels per call (memsets not counted)
 
 
 def run_b200(args):

@@ -733,8 +733,7 @@ struct RefineShared {
 // whose FP64 score lies within 2 e2 of that FP64 minimum -- a handful of
 // pixels -- and phase 2 recomputes those in the reference's own arithmetic.
 // Tied scores (0, +-1 in the planes) are exact as they are and take part as
-// they stand.  The two phases are one cooperative launch with a grid barrier
-// between them; each scans the same tiles (a few: the tile table the
+// they stand.  Each phase scans the same tiles (a few: the tile table the
 // accumulation kernel left says which can hold a candidate).
 template <int PHASE>
 __device__ __forceinline__ void refine_scan(RefineShared &sh, const int *__restrict__ samples_xy,
@@ -915,6 +914,10 @@ __device__ __forceinline__ void refine_scan(RefineShared &sh, const int *__restr
 	}
 }
 
+// The two phases as two launches (the launch boundary is the grid-wide barrier
+// between them; with programmatic dependent launch the second is scheduled
+// while the first drains).
+template <int PHASE>
 __global__ void __launch_bounds__(kRefineThreads)
 ace_refine_kernel(const uint32_t *__restrict__ in, const int *__restrict__ samples_xy,
 		const AceConst cs, const float *__restrict__ scores, double *minmax,
@@ -923,10 +926,7 @@ ace_refine_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sampl
 	__shared__ RefineShared sh;
 	pdl_wait();
 	stage_exact_table(sh.tb, in, samples_xy, cs);
-	refine_scan<1>(sh, samples_xy, in, cs, scores, minmax, tiles_x, tiles_y);
-	__threadfence();
-	cooperative_groups::this_grid().sync();
-	refine_scan<2>(sh, samples_xy, in, cs, scores, minmax, tiles_x, tiles_y);
+	refine_scan<PHASE>(sh, samples_xy, in, cs, scores, minmax, tiles_x, tiles_y);
 }
 
 // The reference's linear scaling, operation for operation (true FP64 divide).
@@ -1420,27 +1420,11 @@ int launch_ace_refine(const uint32_t *in, const int *samples_xy,
 	const int rc = ace_setup(p, cs, grid);
 	if (rc)
 		return rc;
-	// a cooperative launch (grid barrier between the two phases) that may also
-	// be scheduled early behind the accumulation
-	int per_sm = 0;
-	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ace_refine_kernel, kRefineThreads, 0)
-			!= cudaSuccess || per_sm < 1) {
-		cudaGetLastError();
-		per_sm = 1;
-	}
-	cudaLaunchConfig_t cfg = {};
-	cfg.gridDim = dim3(sm_count() * (per_sm < 4 ? per_sm : 4));
-	cfg.blockDim = dim3(kRefineThreads);
-	cfg.stream = st;
-	cudaLaunchAttribute attr[2];
-	attr[0].id = cudaLaunchAttributeCooperative;
-	attr[0].val.cooperative = 1;
-	attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-	attr[1].val.programmaticStreamSerializationAllowed = 1;
-	cfg.attrs = attr;
-	cfg.numAttrs = pdl_enabled() ? 2 : 1;
-	PFB_CUDA(cudaLaunchKernelEx(&cfg, ace_refine_kernel, in, samples_xy, cs, (const float *)sc.planes,
-			minmax, (int)grid.x, (int)grid.y));
+	const dim3 blocks(sm_count() * 2);
+	PFB_CUDA(launch_pdl(ace_refine_kernel<1>, blocks, dim3(kRefineThreads), 0, st,
+			in, samples_xy, cs, (const float *)sc.planes, minmax, (int)grid.x, (int)grid.y));
+	PFB_CUDA(launch_pdl(ace_refine_kernel<2>, blocks, dim3(kRefineThreads), 0, st,
+			in, samples_xy, cs, (const float *)sc.planes, minmax, (int)grid.x, (int)grid.y));
 	return PF_B200_OK;
 }
 
