@@ -1147,7 +1147,7 @@ ace_fixup_kernel(const uint32_t *__restrict__ in, const int *__restrict__ sample
 	__shared__ double terms[256 / 32][kExactChunk][4];
 	__shared__ ExactTable tb;
 	pdl_wait();
-	const int count = *reinterpret_cast<volatile int *>(fix_count);
+	const int count = __ldcg(fix_count);
 	if (count == 0)
 		return;
 	stage_exact_table(tb, in, samples_xy, cs);
