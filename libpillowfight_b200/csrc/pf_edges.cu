@@ -327,37 +327,83 @@ canny_classify_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ ou
 // thread, everything in shared memory.  Connected components by hooking and
 // pointer jumping (Shiloach-Vishkin): all trees are flattened, then every edge
 // whose ends have different roots hangs the larger root under the smaller,
-// until no edge does.  A chain of n weak pixels takes two such rounds and
-// log2(n) jumps, where concurrent union-find walked paths of length n (weak
-// pixels follow edges, so chains are the rule: 20 000 cycles for 900 entries,
-// against 3 000 this way).
-__device__ void canny_resolve_small(uint32_t *out, PageGeom pg, const int *list, int count,
-		int *s_pix, int *s_parent, unsigned char *s_keep)
+// until no edge does.  A chain of n weak pixels takes a few such rounds, where
+// concurrent union-find walked paths of length n (weak pixels follow edges, so
+// chains are the rule).  The edges between weak pixels are collected once, as
+// a list in shared memory (each undirected edge is held by its end with the
+// larger index: at most 4 per entry on average), so a round costs a pass over
+// the entries and a pass over the edges, not over eight possible neighbours of
+// every entry.
+
+// A load that is kept in L1: the list follows edges, so the neighbourhoods of
+// its entries overlap.  (The page is written later in the same kernel, so not
+// the read-only path.)
+__device__ __forceinline__ uint32_t ld_l1(const uint32_t *p)
 {
-	const int nt = blockDim.x;
-	for (int i = threadIdx.x; i < count; i += nt) {
-		s_pix[i] = __ldcg(list + i);
-		s_parent[i] = i;
-		s_keep[i] = 0;
-	}
-	__syncthreads();
-	// this thread's entries: their weak neighbours (list indices, -1: none) and
-	// whether a strong pixel is among the eight
-	int nb[2][8];
-	bool strong[2] = { false, false };
+	uint32_t v;
+	asm volatile("ld.global.ca.u32 %0, [%1];" : "=r"(v) : "l"(p));
+	return v;
+}
+
+__device__ __forceinline__ uint4 ld_l1_v4(const uint32_t *p)
+{
+	uint4 v;
+	asm volatile("ld.global.ca.v4.u32 {%0, %1, %2, %3}, [%4];"
+			: "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+	return v;
+}
+
+#ifdef PF_CANNY_CLOCKS
+#define CANNY_STAMP(k) do { if (threadIdx.x == 0) stamps[k] = (int)clock64(); } while (0)
+#else
+#define CANNY_STAMP(k)
+#endif
+
+struct SmallShared {
+	int parent[kSmallList];
+	unsigned edge[4 * kSmallList];      // (larger index << 16) | smaller index
+	unsigned char keep[kSmallList];
+	int nedge;
+};
+
+// The 8 neighbours of pixel (x, y) (index idx in `out`), kBlack outside the
+// page.  Order: the row above (x-1, x, x+1), W, E, the row below.
+template <bool ALIGNED>
+__device__ __forceinline__ void canny_neighbours(const uint32_t *out, PageGeom pg, int idx, int x, int y,
+		uint32_t (&nv)[8])
+{
+	if (ALIGNED) {
+		// rows are whole 16-byte groups of 4 pixels: the group that holds x, and
+		// one more pixel when x is the group's first or last
+		const int q = x & 3;
+		uint4 v[3];
+		uint32_t l[3], r[3];
 #pragma unroll
-	for (int e = 0; e < 2; e++) {
-		const int i = threadIdx.x + e * nt;
+		for (int dy = -1; dy <= 1; dy++) {
+			const bool row = y + dy >= 0 && y + dy < pg.h;
+			const uint32_t *c = out + idx + dy * pg.w;
+			v[dy + 1] = make_uint4(kBlack, kBlack, kBlack, kBlack);
+			l[dy + 1] = kBlack;
+			r[dy + 1] = kBlack;
+			if (row)
+				v[dy + 1] = ld_l1_v4(c - q);
+			if (row && q == 0 && x > 0)
+				l[dy + 1] = ld_l1(c - 1);
+			if (row && q == 3 && x + 1 < pg.w)
+				r[dy + 1] = ld_l1(c + 1);
+		}
+		uint32_t t[3][3];
 #pragma unroll
-		for (int n = 0; n < 8; n++)
-			nb[e][n] = -1;
-		if (i >= count)
-			continue;
-		const int idx = s_pix[i];
-		const int p = idx % pg.npix;
-		const int y = p / pg.w, x = p - y * pg.w;
-		// all eight neighbours first: one memory round trip, not eight
-		uint32_t nv[8];
+		for (int k = 0; k < 3; k++) {
+			const uint4 a = v[k];
+			t[k][0] = q == 0 ? l[k] : (q == 1 ? a.x : (q == 2 ? a.y : a.z));
+			t[k][1] = q == 0 ? a.x : (q == 1 ? a.y : (q == 2 ? a.z : a.w));
+			t[k][2] = q == 0 ? a.y : (q == 1 ? a.z : (q == 2 ? a.w : r[k]));
+		}
+		nv[0] = t[0][0]; nv[1] = t[0][1]; nv[2] = t[0][2];
+		nv[3] = t[1][0]; nv[4] = t[1][2];
+		nv[5] = t[2][0]; nv[6] = t[2][1]; nv[7] = t[2][2];
+	} else {
 		int n = 0;
 #pragma unroll
 		for (int dy = -1; dy <= 1; dy++) {
@@ -366,66 +412,132 @@ __device__ void canny_resolve_small(uint32_t *out, PageGeom pg, const int *list,
 				if (dx == 0 && dy == 0)
 					continue;
 				const bool inside = x + dx >= 0 && x + dx < pg.w && y + dy >= 0 && y + dy < pg.h;
-				nv[n++] = inside ? __ldcg(out + idx + dy * pg.w + dx) : kBlack;
+				nv[n] = kBlack;
+				if (inside)
+					nv[n] = ld_l1(out + idx + dy * pg.w + dx);
+				n++;
 			}
-		}
-#pragma unroll
-		for (n = 0; n < 8; n++) {
-			strong[e] |= nv[n] == kWhite;
-			// (each undirected edge once, from its larger end)
-			nb[e][n] = (nv[n] < kBlack && (int)nv[n] < i) ? (int)nv[n] : -1;
 		}
 	}
-	for (;;) {
-		// flatten: every entry points at its root
-		for (;;) {
-			bool moved = false;
+}
+
+template <bool ALIGNED>
+__device__ void canny_resolve_small(uint32_t *out, PageGeom pg, const int *list, int count,
+		SmallShared &sh, int *stamps)
+{
+	const int nt = blockDim.x;
+	const int lane = threadIdx.x & 31;
+	CANNY_STAMP(0);
+	for (int i = threadIdx.x; i < count; i += nt) {
+		sh.parent[i] = i;
+		sh.keep[i] = 0;
+	}
+	if (threadIdx.x == 0)
+		sh.nedge = 0;
+	// this thread's entries: their pixel and its eight neighbours (the loads of
+	// both entries issued before any is used: one memory round trip)
+	int pix[2] = { -1, -1 };
+	uint32_t nv[2][8];
 #pragma unroll
-			for (int e = 0; e < 2; e++) {
-				const int i = threadIdx.x + e * nt;
-				if (i < count) {
-					volatile int *vp = s_parent;
-					const int pp = vp[i], gp = vp[pp];
-					if (gp != pp) {
-						vp[i] = gp;
-						moved = true;
-					}
-				}
-			}
-			if (!__syncthreads_or(moved))
-				break;
+	for (int e = 0; e < 2; e++) {
+		const int i = threadIdx.x + e * nt;
+#pragma unroll
+		for (int n = 0; n < 8; n++)
+			nv[e][n] = kBlack;
+		if (i < count)
+			pix[e] = __ldcg(list + i);
+	}
+#pragma unroll
+	for (int e = 0; e < 2; e++) {
+		if (pix[e] < 0)
+			continue;
+		const int p = pix[e] % pg.npix;
+		const int y = p / pg.w, x = p - y * pg.w;
+		canny_neighbours<ALIGNED>(out, pg, pix[e], x, y, nv[e]);
+	}
+	CANNY_STAMP(1);
+	// whether a strong pixel is among the eight, and the edges this entry holds
+	bool strong[2] = { false, false };
+	unsigned held[2] = { 0u, 0u };
+#pragma unroll
+	for (int e = 0; e < 2; e++) {
+		const int i = threadIdx.x + e * nt;
+#pragma unroll
+		for (int n = 0; n < 8; n++) {
+			strong[e] |= nv[e][n] == kWhite;
+			if (nv[e][n] < kBlack && (int)nv[e][n] < i)
+				held[e] |= 1u << n;
 		}
-		// hook: an edge between two trees hangs the larger root under the smaller
-		bool hooked = false;
+	}
+	const int mine = __popc(held[0]) + __popc(held[1]);
+	int pre = mine;
+#pragma unroll
+	for (int dlt = 1; dlt < 32; dlt <<= 1) {
+		const int t = __shfl_up_sync(kFull, pre, dlt);
+		if (lane >= dlt)
+			pre += t;
+	}
+	__syncthreads();         // nedge is zero, parent and keep are set
+	int at = 0;
+	if (lane == 31 && pre > 0)
+		at = atomicAdd(&sh.nedge, pre);
+	at = __shfl_sync(kFull, at, 31) + pre - mine;
+#pragma unroll
+	for (int e = 0; e < 2; e++) {
+		const int i = threadIdx.x + e * nt;
+#pragma unroll
+		for (int n = 0; n < 8; n++)
+			if (held[e] >> n & 1u)
+				sh.edge[at++] = ((unsigned)i << 16) | nv[e][n];
+	}
+	__syncthreads();
+	const int nedge = sh.nedge;
+	CANNY_STAMP(2);
+	for (;;) {
+		// flatten: every entry walks to its root and points at it (the only
+		// writes meanwhile are other entries doing the same, which shorten paths)
 #pragma unroll
 		for (int e = 0; e < 2; e++) {
 			const int i = threadIdx.x + e * nt;
-			if (i >= count)
-				continue;
-			const int ri = s_parent[i];
-#pragma unroll
-			for (int n = 0; n < 8; n++) {
-				if (nb[e][n] < 0)
-					continue;
-				const int rj = s_parent[nb[e][n]];
-				if (ri != rj) {
-					atomicMin(&s_parent[max(ri, rj)], min(ri, rj));
-					hooked = true;
+			if (i < count) {
+				volatile int *vp = sh.parent;
+				int r = vp[i];
+				if (r != i) {
+					for (int g = vp[r]; g != r; g = vp[r])
+						r = g;
+					vp[i] = r;
 				}
+			}
+		}
+		__syncthreads();
+		// hook: an edge between two trees hangs the larger root under the smaller
+		bool hooked = false;
+		for (int k = threadIdx.x; k < nedge; k += nt) {
+			const unsigned ed = sh.edge[k];
+			const int ra = sh.parent[ed >> 16], rb = sh.parent[ed & 0xFFFFu];
+			if (ra != rb) {
+				atomicMin(&sh.parent[max(ra, rb)], min(ra, rb));
+				hooked = true;
 			}
 		}
 		if (!__syncthreads_or(hooked))
 			break;
 	}
+	CANNY_STAMP(3);
 #pragma unroll
 	for (int e = 0; e < 2; e++) {
 		const int i = threadIdx.x + e * nt;
 		if (i < count && strong[e])
-			s_keep[s_parent[i]] = 1;
+			sh.keep[sh.parent[i]] = 1;
 	}
 	__syncthreads();
-	for (int i = threadIdx.x; i < count; i += nt)
-		out[s_pix[i]] = s_keep[s_parent[i]] ? kWhite : kBlack;
+#pragma unroll
+	for (int e = 0; e < 2; e++) {
+		const int i = threadIdx.x + e * nt;
+		if (i < count)
+			out[pix[e]] = sh.keep[sh.parent[i]] ? kWhite : kBlack;
+	}
+	CANNY_STAMP(4);
 }
 
 // ---------------------------------------------------------------------------
@@ -436,11 +548,16 @@ __device__ void canny_resolve_small(uint32_t *out, PageGeom pg, const int *list,
 // long a weak chain is and the result does not depend on scheduling.
 // ---------------------------------------------------------------------------
 
+// Root of entry i, or -1 when its component is known to touch a strong pixel
+// (the mark is a root's parent, so it is found -- and short-cut to -- like any
+// other ancestor).
 __device__ __forceinline__ int uf_find(int *parent, int i)
 {
 	// L2 loads/stores: other SMs hook roots with atomics while this runs
 	int p = __ldcg(parent + i);
 	while (p != i) {
+		if (p < 0)
+			return -1;
 		const int gp = __ldcg(parent + p);
 		if (gp != p)
 			__stcg(parent + i, gp);      // path halving; races only shorten paths
@@ -450,11 +567,13 @@ __device__ __forceinline__ int uf_find(int *parent, int i)
 	return i;
 }
 
+// b = -1 joins a's component with the strong mark.
 __device__ __forceinline__ void uf_union(int *parent, int a, int b)
 {
 	for (;;) {
 		a = uf_find(parent, a);
-		b = uf_find(parent, b);
+		if (b >= 0)
+			b = uf_find(parent, b);
 		if (a == b)
 			return;
 		if (a < b) {
@@ -462,44 +581,48 @@ __device__ __forceinline__ void uf_union(int *parent, int a, int b)
 			a = b;
 			b = t;
 		}
-		// a > b: hang root a under b
+		// a > b >= -1: hang root a under b
 		const int old = atomicCAS(&parent[a], a, b);
 		if (old == a)
 			return;
 	}
 }
 
-constexpr int kStrongBit = (int)0x80000000;   // in list[root]: component touches a strong pixel
-
-// The weak pixels that the classification kernel did not resolve itself (a
-// long list, or bands classified by several launches) in three kernels, the
-// launch boundaries being the grid-wide barriers between:
+// The weak pixels that the classification kernel left on the list, in two
+// kernels, the launch boundary being the grid-wide barrier between:
 //   1. join every weak pixel with its weak neighbours (each undirected edge
-//      once, from the pixel with the smaller address: E, SW, S, SE); a short
-//      list is resolved here by block 0 alone, in shared memory;
-//   2. a weak pixel next to a strong one marks its component's root;
-//   3. every weak pixel takes its component's verdict, and the block that
-//      finishes last clears the header for the next call.
+//      once, from the pixel with the smaller address: E, SW, S, SE) and, if
+//      one of its eight neighbours is strong, with the strong mark -- the
+//      "root" -1, smaller than every index, so it stays on top of whatever is
+//      hung under it; a short list is resolved here by block 0 alone, in
+//      shared memory;
+//   2. every weak pixel takes its component's verdict (its root is the mark or
+//      not), and the block that finishes last clears the header for the next
+//      call.
 // With nothing on the list each is a launch that returns at once.
 //
 // Two entries per thread and round, all their neighbour loads issued before
 // any is used: these loops are bound by memory latency, not by work.  The
-// image is only read until kernel 3 writes the verdicts, so the reads may go
+// image is only read until kernel 2 writes the verdicts, so the reads may go
 // through L1 (entries that follow one another in the list are neighbours in
 // the page and share sectors).
-__global__ void __launch_bounds__(kHystThreads)
+#ifndef PF_CANNY_LINK_MINBLOCKS
+#define PF_CANNY_LINK_MINBLOCKS 2
+#endif
+__global__ void __launch_bounds__(kHystThreads, PF_CANNY_LINK_MINBLOCKS)
 canny_link_kernel(uint32_t *out, PageGeom pg, int *list, int *parent, int *hdr)
 {
-	__shared__ int s_pix[kSmallList];
-	__shared__ int s_parent[kSmallList];
-	__shared__ unsigned char s_keep[kSmallList];
+	__shared__ SmallShared sh;
 	pdl_wait();
 	const int count = __ldcg(&hdr[kHdrCount]);
 	if (count == 0)
 		return;
 	if (count <= kSmallList) {
 		if (blockIdx.x == 0) {
-			canny_resolve_small(out, pg, list, count, s_pix, s_parent, s_keep);
+			if (pg.w % 4 == 0 && ((uintptr_t)out & 15) == 0)
+				canny_resolve_small<true>(out, pg, list, count, sh, hdr + 32);
+			else
+				canny_resolve_small<false>(out, pg, list, count, sh, hdr + 32);
 			__syncthreads();
 			if (threadIdx.x == 0) {
 				hdr[kHdrLastCount] = count;
@@ -511,20 +634,20 @@ canny_link_kernel(uint32_t *out, PageGeom pg, int *list, int *parent, int *hdr)
 	const int first = blockIdx.x * blockDim.x + threadIdx.x;
 	const int step = gridDim.x * blockDim.x;
 	for (int i0 = first; i0 < count; i0 += 2 * step) {
-		uint32_t nv[2][4];
+		uint32_t nv[2][8];
 #pragma unroll
 		for (int u = 0; u < 2; u++) {
 			const int i = i0 + u * step;
 #pragma unroll
-			for (int n = 0; n < 4; n++)
+			for (int n = 0; n < 8; n++)
 				nv[u][n] = kBlack;
 			if (i >= count)
 				continue;
 			const int idx = list[i];
 			const int p = idx % pg.npix;
 			const int y = p / pg.w, x = p - y * pg.w;
-			const bool has_e = x + 1 < pg.w, has_w = x > 0, has_s = y + 1 < pg.h;
-			// each undirected edge once, from the pixel with the smaller address
+			const bool has_e = x + 1 < pg.w, has_w = x > 0, has_s = y + 1 < pg.h, has_n = y > 0;
+			// 0-3: E, SW, S, SE (the edges this pixel owns); 4-7: W, NW, N, NE
 			if (has_e)
 				nv[u][0] = __ldg(out + idx + 1);
 			if (has_s && has_w)
@@ -533,52 +656,28 @@ canny_link_kernel(uint32_t *out, PageGeom pg, int *list, int *parent, int *hdr)
 				nv[u][2] = __ldg(out + idx + pg.w);
 			if (has_s && has_e)
 				nv[u][3] = __ldg(out + idx + pg.w + 1);
+			if (has_w)
+				nv[u][4] = __ldg(out + idx - 1);
+			if (has_n && has_w)
+				nv[u][5] = __ldg(out + idx - pg.w - 1);
+			if (has_n)
+				nv[u][6] = __ldg(out + idx - pg.w);
+			if (has_n && has_e)
+				nv[u][7] = __ldg(out + idx - pg.w + 1);
 		}
 #pragma unroll
-		for (int u = 0; u < 2; u++)
+		for (int u = 0; u < 2; u++) {
+			bool strong = false;
+#pragma unroll
+			for (int n = 0; n < 8; n++)
+				strong |= nv[u][n] == kWhite;
 #pragma unroll
 			for (int n = 0; n < 4; n++)
 				if (nv[u][n] < kBlack)
 					uf_union(parent, i0 + u * step, (int)nv[u][n]);
-	}
-}
-
-__global__ void __launch_bounds__(kHystThreads)
-canny_seed_kernel(const uint32_t *__restrict__ out, PageGeom pg, int *list, int *parent,
-		const int *__restrict__ hdr)
-{
-	pdl_wait();
-	const int count = hdr[kHdrCount];
-	if (count == 0)
-		return;
-	const int first = blockIdx.x * blockDim.x + threadIdx.x;
-	const int step = gridDim.x * blockDim.x;
-	for (int i0 = first; i0 < count; i0 += 2 * step) {
-		bool strong[2] = { false, false };
-#pragma unroll
-		for (int u = 0; u < 2; u++) {
-			const int i = i0 + u * step;
-			if (i >= count)
-				continue;
-			const int idx = __ldcg(list + i) & ~kStrongBit;
-			const int p = idx % pg.npix;
-			const int y = p / pg.w, x = p - y * pg.w;
-#pragma unroll
-			for (int dy = -1; dy <= 1; dy++) {
-#pragma unroll
-				for (int dx = -1; dx <= 1; dx++) {
-					if (dx == 0 && dy == 0)
-						continue;
-					if (x + dx < 0 || x + dx >= pg.w || y + dy < 0 || y + dy >= pg.h)
-						continue;
-					strong[u] |= __ldg(out + idx + dy * pg.w + dx) == kWhite;
-				}
-			}
+			if (strong)
+				uf_union(parent, i0 + u * step, -1);
 		}
-#pragma unroll
-		for (int u = 0; u < 2; u++)
-			if (strong[u])
-				atomicOr(&list[uf_find(parent, i0 + u * step)], kStrongBit);
 	}
 }
 
@@ -591,11 +690,8 @@ canny_verdict_kernel(uint32_t *out, int *list, int *parent, int *hdr)
 		return;
 	const int first = blockIdx.x * blockDim.x + threadIdx.x;
 	const int step = gridDim.x * blockDim.x;
-	for (int i = first; i < count; i += step) {
-		const int root = uf_find(parent, i);
-		const bool keep = (__ldcg(list + root) & kStrongBit) != 0;
-		out[__ldcg(list + i) & ~kStrongBit] = keep ? kWhite : kBlack;
-	}
+	for (int i = first; i < count; i += step)
+		out[__ldcg(list + i)] = uf_find(parent, i) < 0 ? kWhite : kBlack;
 	// the block that finishes last clears the header (every block has read
 	// the length before it gets here)
 	__syncthreads();
@@ -606,6 +702,14 @@ canny_verdict_kernel(uint32_t *out, int *list, int *parent, int *hdr)
 	}
 }
 
+// Clears the header of scratch in an unknown state (a caller's): a kernel, not
+// a memset, so that the chain of programmatic launches is not broken.
+__global__ void canny_begin_kernel(int *hdr)
+{
+	pdl_wait();
+	hdr[threadIdx.x] = 0;
+}
+
 // The final values of the weak pixels, copied to a second image (the caller's
 // pinned page, which already holds everything else: see pf_capi.cu).
 __global__ void canny_patch_kernel(const uint32_t *__restrict__ out, uint32_t *__restrict__ mirror,
@@ -614,7 +718,7 @@ __global__ void canny_patch_kernel(const uint32_t *__restrict__ out, uint32_t *_
 	pdl_wait();
 	const int count = hdr[kHdrLastCount];
 	for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
-		const int idx = list[i] & ~kStrongBit;
+		const int idx = list[i];
 		mirror[idx] = out[idx];
 	}
 }
@@ -628,15 +732,17 @@ static int hysteresis_blocks()
 	return sm_count() * (want < 1 ? 1 : (want > 2 ? 2 : want));
 }
 
-// The weak pixels the classification left on the list: link, seed, verdict.
+static cudaError_t clear_canny_header(int *hdr, cudaStream_t st)
+{
+	return launch_pdl(canny_begin_kernel, dim3(1), dim3(64), 0, st, hdr);
+}
+
+// The weak pixels the classification left on the list: link, verdict.
 static cudaError_t launch_hysteresis(uint32_t *out, PageGeom pg, int *list, int *parent,
 		int *hdr, int blocks, cudaStream_t st)
 {
 	cudaError_t e = launch_pdl(canny_link_kernel, dim3(blocks), dim3(kHystThreads), 0, st,
 			out, pg, list, parent, hdr);
-	if (e == cudaSuccess)
-		e = launch_pdl(canny_seed_kernel, dim3(blocks), dim3(kHystThreads), 0, st,
-				(const uint32_t *)out, pg, list, parent, (const int *)hdr);
 	if (e == cudaSuccess)
 		e = launch_pdl(canny_verdict_kernel, dim3(blocks), dim3(kHystThreads), 0, st,
 				out, list, parent, hdr);
@@ -696,7 +802,7 @@ int launch_canny(const uint32_t *in, uint32_t *out, int w, int h, int pages,
 		// every pass leaves the header clear; only scratch in an unknown state
 		// (a caller's, on its first use) has to be cleared here
 		if (!header_is_clear && p0 == 0)
-			PFB_CUDA(cudaMemsetAsync(hdr, 0, 256, st));
+			PFB_CUDA(clear_canny_header(hdr, st));
 		const StripGeom g = make_geom(canny_classify_kernel, pin, pout, w, h, np, 4, 0, -1, 3);
 		const int warps = g.warp_cols * g.strips;
 		dim3 grid((warps + kWarpsPerBlock - 1) / kWarpsPerBlock, np);
@@ -727,7 +833,7 @@ int launch_canny_begin(int w, int h, void *scratch, size_t scratch_bytes, cudaSt
 	if (rc)
 		return rc;
 	if (!header_is_clear)
-		PFB_CUDA(cudaMemsetAsync(scratch, 0, 256, st));
+		PFB_CUDA(clear_canny_header(static_cast<int *>(scratch), st));
 	return PF_B200_OK;
 }
 
