@@ -584,23 +584,26 @@ def run_b200(args):
     #     headline), and one thread.
     import queue
 
-    def e2e_pages_in_flight(steps):
+    def e2e_pages_in_flight(warm, steps):
+        """Seconds for `steps` pages.  The threads are the same for the warm-up and the
+        timed pages (a host thread's context in the library lives as long as the thread)."""
         ready, free, errs = queue.Queue(), threading.Semaphore(N_BLUR - 1), []
+        gate = threading.Barrier(5)
 
         def each(call):
-            def loop():
-                for i in range(steps):
+            def loop(n):
+                for i in range(n):
                     call(i)
             return loop
 
-        def gauss_loop():
-            for i in range(steps):
+        def gauss_loop(n):
+            for i in range(n):
                 free.acquire()
                 chk(lib.pf_b200_gaussian(ctypes.byref(b_in), ctypes.byref(b_blur[i % N_BLUR]), 2.0, 5))
                 ready.put(i)
 
-        def sobel_loop():
-            for _ in range(steps):
+        def sobel_loop(n):
+            for _ in range(n):
                 i = ready.get()
                 chk(lib.pf_b200_sobel(ctypes.byref(b_blur[i % N_BLUR]), ctypes.byref(b_s)))
                 free.release()
@@ -609,9 +612,13 @@ def run_b200(args):
             def run():
                 try:
                     torch.cuda.set_device(local)
-                    fn()
+                    fn(warm)
+                    gate.wait()               # everyone has finished warming up
+                    fn(steps)
+                    gate.wait()               # everyone has finished the timed pages
                 except Exception as exc:      # noqa: BLE001
                     errs.append(exc)
+                    gate.abort()
                     ready.put(0)              # (do not leave the Sobel thread waiting)
                     free.release()
             return run
@@ -621,12 +628,18 @@ def run_b200(args):
                  gauss_loop, sobel_loop,
                  each(lambda i: chk(lib.pf_b200_canny(ctypes.byref(b_in), ctypes.byref(b_c))))]
         threads = [threading.Thread(target=guarded(fn), daemon=True) for fn in loops]
-        t0 = time.perf_counter()
         for th in threads:
             th.start()
+        t = None
+        try:
+            gate.wait()
+            t0 = time.perf_counter()
+            gate.wait()
+            t = time.perf_counter() - t0
+        except threading.BrokenBarrierError:
+            pass
         for th in threads:
             th.join()
-        t = time.perf_counter() - t0
         if errs:
             raise errs[0]
         return t
@@ -698,9 +711,8 @@ def run_b200(args):
     t_e2e_two = timed_host_loop(e2e_step_threads, ke)
     for wk in workers:
         wk.stop()
-    e2e_pages_in_flight(max(3, args.warmup))
     barrier()
-    t_e2e = e2e_pages_in_flight(ke) / ke
+    t_e2e = e2e_pages_in_flight(max(3, args.warmup), ke) / ke
     barrier()
     t_e2e = max_over_ranks(t_e2e)
     blur_copies_equal = all(bool(np.array_equal(hv[2], hv[5 + k])) for k in range(N_BLUR - 1))

@@ -41,46 +41,58 @@ sobel = lambda i: chk(lib.pf_b200_sobel(ctypes.byref(b_g[i % NG]), ctypes.byref(
 canny = lambda i: chk(lib.pf_b200_canny(ctypes.byref(b_in), ctypes.byref(b_c)))
 
 
-def run(groups, barrier, steps, sobel_follows=None):
+def run(groups, barrier, steps, sobel_follows=None, warm=3):
     """groups: one list of calls per thread.  barrier: every thread finishes step i
-    before any starts step i+1.  sobel_follows: (gauss thread, sobel thread) when
-    Sobel runs on its own thread behind Gaussian."""
+    before any starts step i+1.  sobel_follows: Sobel runs on its own thread behind
+    Gaussian.  The threads warm up first (a host thread's context in the library
+    lives as long as the thread), then all start the timed pages together."""
     nthreads = len(groups)
     bar = threading.Barrier(nthreads) if barrier else None
+    gate = threading.Barrier(nthreads + 1)
     ready = queue.Queue()                      # Gaussian results ready for Sobel
     free = threading.Semaphore(NG - 1)         # Gaussian buffers Sobel has released
     errs = []
 
+    def work(t, n):
+        for i in range(n):
+            for call in groups[t]:
+                if sobel_follows and call is gauss:
+                    free.acquire()
+                    call(i)
+                    ready.put(i)
+                elif sobel_follows and call is sobel:
+                    ready.get()
+                    call(i)
+                    free.release()
+                else:
+                    call(i)
+            if bar:
+                bar.wait()
+
     def loop(t):
         try:
-            for i in range(steps):
-                for call in groups[t]:
-                    if sobel_follows and call is gauss:
-                        free.acquire()
-                        call(i)
-                        ready.put(i)
-                    elif sobel_follows and call is sobel:
-                        ready.get()
-                        call(i)
-                        free.release()
-                    else:
-                        call(i)
-                if bar:
-                    bar.wait()
+            work(t, warm)
+            gate.wait()
+            work(t, steps)
+            gate.wait()
         except Exception as exc:                   # noqa: BLE001
             errs.append(exc)
+            gate.abort()
             if bar:
                 bar.abort()
 
     threads = [threading.Thread(target=loop, args=(t,)) for t in range(nthreads)]
-    t0 = time.perf_counter()
     for th in threads:
         th.start()
+    gate.wait()
+    t0 = time.perf_counter()
+    gate.wait()
+    dt = time.perf_counter() - t0
     for th in threads:
         th.join()
     if errs:
         raise errs[0]
-    return (time.perf_counter() - t0) / steps * 1e3
+    return dt / steps * 1e3
 
 
 cases = [
@@ -93,7 +105,6 @@ cases = [
     ("3 threads (ace+canny | gauss | sobel), pages in flight", [[ace, canny], [gauss], [sobel]], False, True),
 ]
 for name, groups, barrier, follows in cases:
-    run(groups, barrier, 3, follows)
     best = min(run(groups, barrier, K, follows) for _ in range(2))
     print("%-58s %.3f ms per page = %.0f Mpx/s" % (name, best, w * h / best / 1e3), flush=True)
 lib.pf_b200_host_free(pin)
