@@ -614,6 +614,28 @@ static int band_rows_for(int h)
 	return rows;
 }
 
+// Queues the upload of a pinned page for a call that works in row bands of
+// `rows` rows: band b's event (ev_up[b]) says that its rows and the kReach rows
+// below them -- further than any stencil here reaches (<= 31 rows) -- are in
+// HBM, so band b's kernels wait for nothing but their own event.
+constexpr int kReach = 32;
+
+static int upload_bands(Context &c, uint32_t *din, const uint32_t *src, int w, int h, int rows, int nb)
+{
+	int u0 = 0;
+	for (int b = 0; b < nb; b++) {
+		int u1 = (b + 1) * rows + kReach;
+		if (u1 > h || b == nb - 1)
+			u1 = h;
+		if (u1 > u0)
+			PFB_CUDA(cudaMemcpyAsync(din + (size_t)u0 * w, src + (size_t)u0 * w,
+					(size_t)(u1 - u0) * w * sizeof(uint32_t), cudaMemcpyHostToDevice, c.st_up));
+		PFB_CUDA(cudaEventRecord(c.ev_up[b], c.st_up));
+		u0 = u1;
+	}
+	return PF_B200_OK;
+}
+
 // Gaussian / Sobel on pinned caller memory: the page goes up band by band on
 // one stream, each band is filtered on the kernel stream as soon as it and
 // the band below it (the stencil's reach) have arrived, and comes back on a
@@ -635,15 +657,12 @@ static int run_stencil_streamed(Context &c, Op op, const struct pf_bitmap *in,
 	static const bool direct_env = !getenv("PF_B200_DIRECT_OUT") || atoi(getenv("PF_B200_DIRECT_OUT"));
 	// (one band = a call beside others: the copy engine, as the link is shared)
 	uint32_t *direct = (direct_env && nb > 1) ? static_cast<uint32_t *>(device_alias(out->pixels)) : nullptr;
+	int rc_up = upload_bands(c, const_cast<uint32_t *>(din), src, w, h, rows, nb);
+	if (rc_up)
+		return rc_up;
 	for (int b = 0; b < nb; b++) {
 		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
-		PFB_CUDA(cudaMemcpyAsync(const_cast<uint32_t *>(din) + (size_t)y0 * w, src + (size_t)y0 * w,
-				(size_t)(y1 - y0) * w * sizeof(uint32_t), cudaMemcpyHostToDevice, c.st_up));
-		PFB_CUDA(cudaEventRecord(c.ev_up[b], c.st_up));
-	}
-	for (int b = 0; b < nb; b++) {
-		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
-		PFB_CUDA(cudaStreamWaitEvent(c.st, c.ev_up[b + 1 < nb ? b + 1 : b], 0));
+		PFB_CUDA(cudaStreamWaitEvent(c.st, c.ev_up[b], 0));
 		uint32_t *to = direct ? direct : dout;
 		int rc = (op == OP_GAUSSIAN) ? launch_gaussian(din, to, w, h, 1, taps, c.st, y0, y1)
 		                             : launch_sobel(din, to, w, h, 1, c.st, y0, y1);
@@ -684,15 +703,12 @@ static int run_canny_streamed(Context &c, const struct pf_bitmap *in, struct pf_
 	int *weak_count = static_cast<int *>(c.h_stage.p);
 	if ((rc = launch_canny_begin(w, h, c.d_scratch.p, c.d_scratch.cap, c.st, true)))
 		return rc;
+	int rc_up = upload_bands(c, const_cast<uint32_t *>(din), src, w, h, rows, nb);
+	if (rc_up)
+		return rc_up;
 	for (int b = 0; b < nb; b++) {
 		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
-		PFB_CUDA(cudaMemcpyAsync(const_cast<uint32_t *>(din) + (size_t)y0 * w, src + (size_t)y0 * w,
-				(size_t)(y1 - y0) * w * sizeof(uint32_t), cudaMemcpyHostToDevice, c.st_up));
-		PFB_CUDA(cudaEventRecord(c.ev_up[b], c.st_up));
-	}
-	for (int b = 0; b < nb; b++) {
-		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
-		PFB_CUDA(cudaStreamWaitEvent(c.st, c.ev_up[b + 1 < nb ? b + 1 : b], 0));
+		PFB_CUDA(cudaStreamWaitEvent(c.st, c.ev_up[b], 0));
 		if ((rc = launch_canny_classify_rows(din, dout, w, h, y0, y1, canny_thresholds(),
 				c.d_scratch.p, c.st)))
 			return rc;
@@ -1184,18 +1200,15 @@ static int run_step_streamed(Context &c, const StepArgs &a, const Taps &taps)
 
 	const int rows = band_rows_for(h);
 	const int nb = (h + rows - 1) / rows;
-	for (int b = 0; b < nb; b++) {
-		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
-		PFB_CUDA(cudaMemcpyAsync(const_cast<uint32_t *>(din) + (size_t)y0 * w, src + (size_t)y0 * w,
-				(size_t)(y1 - y0) * w * sizeof(uint32_t), cudaMemcpyHostToDevice, c.st_up));
-		PFB_CUDA(cudaEventRecord(c.ev_up[b], c.st_up));
-	}
+	int rc_up = upload_bands(c, const_cast<uint32_t *>(din), src, w, h, rows, nb);
+	if (rc_up)
+		return rc_up;
 	uint32_t *host_gauss = a.gauss ? reinterpret_cast<uint32_t *>(a.gauss->pixels) : nullptr;
 	uint32_t *host_canny = a.canny ? reinterpret_cast<uint32_t *>(a.canny->pixels) : nullptr;
 	for (int b = 0; b < nb; b++) {
 		const int y0 = b * rows, y1 = (y0 + rows < h) ? y0 + rows : h;
 		const size_t off = (size_t)y0 * w, len = (size_t)(y1 - y0) * w * sizeof(uint32_t);
-		PFB_CUDA(cudaStreamWaitEvent(c.st, c.ev_up[b + 1 < nb ? b + 1 : b], 0));
+		PFB_CUDA(cudaStreamWaitEvent(c.st, c.ev_up[b], 0));
 		if (a.ace) {
 			p.row_begin = y0;
 			p.row_end = y1;
