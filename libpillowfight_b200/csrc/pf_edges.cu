@@ -601,11 +601,11 @@ __device__ __forceinline__ void uf_union(int *parent, int a, int b)
 //      call.
 // With nothing on the list each is a launch that returns at once.
 //
-// Two entries per thread and round, all their neighbour loads issued before
-// any is used: these loops are bound by memory latency, not by work.  The
-// image is only read until kernel 2 writes the verdicts, so the reads may go
-// through L1 (entries that follow one another in the list are neighbours in
-// the page and share sectors).
+// All neighbour loads of an entry are issued before any is used: these loops
+// are bound by memory latency, not by work.  The image is only read until
+// kernel 2 writes the verdicts, so the reads may go through L1 (entries that
+// follow one another in the list are neighbours in the page and share
+// sectors).
 #ifndef PF_CANNY_LINK_MINBLOCKS
 #define PF_CANNY_LINK_MINBLOCKS 2
 #endif
@@ -633,51 +633,48 @@ canny_link_kernel(uint32_t *out, PageGeom pg, int *list, int *parent, int *hdr)
 	}
 	const int first = blockIdx.x * blockDim.x + threadIdx.x;
 	const int step = gridDim.x * blockDim.x;
-	for (int i0 = first; i0 < count; i0 += 2 * step) {
-		uint32_t nv[2][8];
+	for (int i = first; i < count; i += step) {
+		// all eight neighbours first: one memory round trip (one entry per thread
+		// and round: the block is full, and sixteen loads in flight per thread
+		// would not fit its 32 registers)
+		const int idx = list[i];
+		const int p = idx % pg.npix;
+		const int y = p / pg.w, x = p - y * pg.w;
+		const bool has_e = x + 1 < pg.w, has_w = x > 0, has_s = y + 1 < pg.h, has_n = y > 0;
+		uint32_t nv[8];
 #pragma unroll
-		for (int u = 0; u < 2; u++) {
-			const int i = i0 + u * step;
+		for (int n = 0; n < 8; n++)
+			nv[n] = kBlack;
+		// 0-3: E, SW, S, SE (the edges this pixel owns); 4-7: W, NW, N, NE
+		if (has_e)
+			nv[0] = __ldg(out + idx + 1);
+		if (has_s && has_w)
+			nv[1] = __ldg(out + idx + pg.w - 1);
+		if (has_s)
+			nv[2] = __ldg(out + idx + pg.w);
+		if (has_s && has_e)
+			nv[3] = __ldg(out + idx + pg.w + 1);
+		if (has_w)
+			nv[4] = __ldg(out + idx - 1);
+		if (has_n && has_w)
+			nv[5] = __ldg(out + idx - pg.w - 1);
+		if (has_n)
+			nv[6] = __ldg(out + idx - pg.w);
+		if (has_n && has_e)
+			nv[7] = __ldg(out + idx - pg.w + 1);
+		bool strong = false;
 #pragma unroll
-			for (int n = 0; n < 8; n++)
-				nv[u][n] = kBlack;
-			if (i >= count)
-				continue;
-			const int idx = list[i];
-			const int p = idx % pg.npix;
-			const int y = p / pg.w, x = p - y * pg.w;
-			const bool has_e = x + 1 < pg.w, has_w = x > 0, has_s = y + 1 < pg.h, has_n = y > 0;
-			// 0-3: E, SW, S, SE (the edges this pixel owns); 4-7: W, NW, N, NE
-			if (has_e)
-				nv[u][0] = __ldg(out + idx + 1);
-			if (has_s && has_w)
-				nv[u][1] = __ldg(out + idx + pg.w - 1);
-			if (has_s)
-				nv[u][2] = __ldg(out + idx + pg.w);
-			if (has_s && has_e)
-				nv[u][3] = __ldg(out + idx + pg.w + 1);
-			if (has_w)
-				nv[u][4] = __ldg(out + idx - 1);
-			if (has_n && has_w)
-				nv[u][5] = __ldg(out + idx - pg.w - 1);
-			if (has_n)
-				nv[u][6] = __ldg(out + idx - pg.w);
-			if (has_n && has_e)
-				nv[u][7] = __ldg(out + idx - pg.w + 1);
-		}
+		for (int n = 0; n < 8; n++)
+			strong |= nv[n] == kWhite;
+		// (the mark first: joining two components that both carry it is a pair
+		// of finds and nothing else -- on a page of noise, where nearly every
+		// weak pixel has a strong neighbour, that is most joins)
+		if (strong)
+			uf_union(parent, i, -1);
 #pragma unroll
-		for (int u = 0; u < 2; u++) {
-			bool strong = false;
-#pragma unroll
-			for (int n = 0; n < 8; n++)
-				strong |= nv[u][n] == kWhite;
-#pragma unroll
-			for (int n = 0; n < 4; n++)
-				if (nv[u][n] < kBlack)
-					uf_union(parent, i0 + u * step, (int)nv[u][n]);
-			if (strong)
-				uf_union(parent, i0 + u * step, -1);
-		}
+		for (int n = 0; n < 4; n++)
+			if (nv[n] < kBlack)
+				uf_union(parent, i, (int)nv[n]);
 	}
 }
 
