@@ -494,18 +494,28 @@ __device__ void canny_resolve_small(uint32_t *out, PageGeom pg, const int *list,
 	const int nedge = sh.nedge;
 	CANNY_STAMP(2);
 	for (;;) {
-		// flatten: every entry walks to its root and points at it (the only
-		// writes meanwhile are other entries doing the same, which shorten paths)
-#pragma unroll
-		for (int e = 0; e < 2; e++) {
-			const int i = threadIdx.x + e * nt;
-			if (i < count) {
-				volatile int *vp = sh.parent;
-				int r = vp[i];
-				if (r != i) {
-					for (int g = vp[r]; g != r; g = vp[r])
-						r = g;
-					vp[i] = r;
+		// flatten: every entry points at its parent's parent until that is a
+		// root.  No barrier between the jumps: the only writes meanwhile are other
+		// entries doing the same, which shorten paths, so a chain of n takes each
+		// of its entries about log2(n) jumps, all entries at once.
+		{
+			volatile int *vp = sh.parent;
+			const int i0 = threadIdx.x, i1 = threadIdx.x + nt;
+			bool busy0 = i0 < count, busy1 = i1 < count;
+			while (busy0 || busy1) {
+				const int p0 = busy0 ? vp[i0] : 0, p1 = busy1 ? vp[i1] : 0;
+				const int g0 = vp[p0], g1 = vp[p1];
+				if (busy0) {
+					if (g0 == p0)
+						busy0 = false;
+					else
+						vp[i0] = g0;
+				}
+				if (busy1) {
+					if (g1 == p1)
+						busy1 = false;
+					else
+						vp[i1] = g1;
 				}
 			}
 		}

@@ -125,6 +125,23 @@ def test_canny_long_weak_chains(gpu, oracle):
     assert not ref[100:600, 198:202, 0].any() and not ref[100:600, 258:262, 0].any()
 
 
+@pytest.mark.parametrize("h", [60, 200, 420])
+def test_canny_short_list_long_chain(gpu, oracle, h):
+    # The same on a page small enough for the short-list path (one block, shared
+    # memory): chains shorter and longer than the passes that spread "kept" along
+    # the edges, so both that and the component labelling behind it decide pages.
+    w = 120
+    g = np.zeros((h, w), dtype=np.uint8)
+    g[:, 40:] = 50
+    g[:10, 40:] = 120
+    g[20:h - 8, 80:100] += 50
+    page = np.stack([g, g, g, np.full_like(g, 255)], axis=-1)
+    got, ref = gpu.canny(page), oracle.canny(page)
+    assert np.array_equal(got, ref)
+    assert ref[h - 5, 39:41, 0].any()
+    assert not ref[30:h - 16, 78:82, 0].any()
+
+
 def test_canny_snake_fills_queues(gpu, oracle):
     # dense weak texture seeded by a few strong pixels: a long work list, so the
     # grid-wide union-find path of the hysteresis kernel
