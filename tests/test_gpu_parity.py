@@ -472,6 +472,69 @@ def test_in_place_and_pinned_buffers(gpu, oracle):
         lib.pf_b200_host_free(pin)
 
 
+def test_host_calls_side_by_side_on_several_threads(gpu, oracle):
+    """Four host threads, one per call of a step, each making its call several
+    times while the others run: a call that begins beside others moves its page
+    in one DMA each way instead of row bands (pf_capi.cu, CallScope).  Every
+    result of every round is compared with the oracle; Sobel also in place."""
+    import threading
+    from libpillowfight_b200 import _capi
+    lib = _capi.lib
+    w, h = 700, 1500
+    page = synthetic_page(w, h, 21)
+    n = page.nbytes
+    pin = lib.pf_b200_host_alloc(6 * n)
+    assert pin
+    try:
+        def view(k):
+            return np.ctypeslib.as_array((ctypes.c_uint8 * n).from_address(pin + k * n)).reshape(page.shape)
+
+        def bm(k):
+            b = _capi.PfBitmap()
+            b.size.x, b.size.y, b.pixels = w, h, pin + k * n
+            return b
+
+        view(0)[:] = page
+        xy = oracle.ace_draw_samples(40, w, h, 5)
+        xyp = xy.ctypes.data_as(ctypes.POINTER(ctypes.c_int))
+        refs = {"ace": oracle.ace_with_samples(page, xy, 10.0, 1000.0, nb_threads=8),
+                "gaussian": oracle.gaussian(page, 2.0, 5), "sobel": oracle.sobel(page),
+                "canny": oracle.canny(page)}
+        b_in = bm(0)
+        outs = {"ace": 1, "gaussian": 2, "sobel": 3, "canny": 4}
+        calls = {
+            "ace": lambda: lib.pf_b200_ace(ctypes.byref(b_in), ctypes.byref(bm(1)), 40, xyp, 10.0, 1000.0),
+            "gaussian": lambda: lib.pf_b200_gaussian(ctypes.byref(b_in), ctypes.byref(bm(2)), 2.0, 5),
+            "canny": lambda: lib.pf_b200_canny(ctypes.byref(b_in), ctypes.byref(bm(4))),
+        }
+        bad = []
+        start = threading.Barrier(4)
+
+        def worker(name):
+            try:
+                start.wait()
+                for rnd in range(6):
+                    if name == "sobel":             # in place on a private copy of the page
+                        view(3)[:] = page
+                        _capi.check(lib.pf_b200_sobel(ctypes.byref(bm(3)), ctypes.byref(bm(3))))
+                    else:
+                        view(outs[name])[:] = 0x5A
+                        _capi.check(calls[name]())
+                    if not np.array_equal(view(outs[name]), refs[name]):
+                        bad.append("%s, round %d" % (name, rnd))
+            except Exception as exc:            # noqa: BLE001
+                bad.append("%s: %r" % (name, exc))
+
+        threads = [threading.Thread(target=worker, args=(name,)) for name in outs]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        assert not bad, bad
+    finally:
+        lib.pf_b200_host_free(pin)
+
+
 def test_streamed_paths_on_pinned_pages(gpu, oracle):
     """Pinned caller memory and >= 512 rows: the page is uploaded, processed
     and returned band by band on three streams.  Same results, also in place."""
