@@ -521,6 +521,10 @@ def run_b200(args):
                 # FMA-pipe instruction slots (an add takes a slot like an FMA): 8 of them per pair
                 "fma_pipe_slot_frac": (kept * 8.0 * 2.0 / (ms_ace_scores * 1e-3) / 1e12) / fp32_peak
                 if fp32_peak > 0 else None,
+                # one MUFU.RSQ per pair at the 16 lanes per clock and SM the XU pipe issues
+                # (profiles/r02_pipe_rates.txt), at the SM clock the bench saw: the loop asks the
+                # XU pipe, the FMA pipe and the issue port for about 8 cycles per pair each
+                "mufu_floor_ms": None, "frac_of_mufu_floor": None,
                 "issue_frac_ncu": ncu_row.get("issue_active_pct"),
                 "fma_pipe_frac_ncu": ncu_row.get("pipe_fma_cycles_active_pct"),
                 "xu_pipe_frac_ncu": ncu_row.get("pipe_xu_pct"),
@@ -719,6 +723,11 @@ def run_b200(args):
     e2e_value = world * npix / t_e2e / 1e6
     torch.cuda.synchronize()
     clocks = sampler.stop()
+    sm_mhz = (clocks or {}).get("sm_mhz") or 0
+    if sm_mhz:
+        sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        roofline["mufu_floor_ms"] = kept / (16.0 * sms * sm_mhz * 1e6) * 1e3
+        roofline["frac_of_mufu_floor"] = roofline["mufu_floor_ms"] / ms_ace_scores
 
     # the same four calls on ordinary (malloc'ed, pageable) bitmaps on both sides:
     # what an existing C program passes
