@@ -715,10 +715,15 @@ def run_b200(args):
     t_e2e_two = timed_host_loop(e2e_step_threads, ke)
     for wk in workers:
         wk.stop()
-    barrier()
-    t_e2e = e2e_pages_in_flight(max(3, args.warmup), ke) / ke
-    barrier()
-    t_e2e = max_over_ranks(t_e2e)
+    # (three runs of ke pages, the median reported: 30 pages are 0.1 s of wall clock,
+    # and host threads are at the mercy of the box's scheduler)
+    e2e_runs = []
+    for _ in range(3):
+        barrier()
+        t_run = e2e_pages_in_flight(max(3, args.warmup), ke) / ke
+        barrier()
+        e2e_runs.append(max_over_ranks(t_run))
+    t_e2e = sorted(e2e_runs)[1]
     blur_copies_equal = all(bool(np.array_equal(hv[2], hv[5 + k])) for k in range(N_BLUR - 1))
     e2e_value = world * npix / t_e2e / 1e6
     torch.cuda.synchronize()
@@ -963,7 +968,7 @@ def run_b200(args):
                            "call, each working through the pages in order (pages in flight; the Sobel "
                            "thread takes every blurred page from the Gaussian thread, so each page gets "
                            "all four results of the step)",
-                    "host_threads": 4,
+                    "host_threads": 4, "runs_ms_per_step": [t * 1e3 for t in e2e_runs],
                     "two_threads_step_at_a_time": {"value": world * npix / t_e2e_two / 1e6, "unit": "Mpx/s",
                                                    "ms_per_step": t_e2e_two * 1e3},
                     "one_thread": {"value": world * npix / t_e2e_one / 1e6, "unit": "Mpx/s",

@@ -732,7 +732,7 @@ __global__ void canny_patch_kernel(const uint32_t *__restrict__ out, uint32_t *_
 
 }  // namespace
 
-// Blocks of the three hysteresis kernels (PF_B200_HYST_BLOCKS per SM, default 2).
+// Blocks of the two hysteresis kernels (PF_B200_HYST_BLOCKS per SM, default 2).
 static int hysteresis_blocks()
 {
 	static const int want = getenv("PF_B200_HYST_BLOCKS") ? atoi(getenv("PF_B200_HYST_BLOCKS")) : 2;
