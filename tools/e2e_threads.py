@@ -1,7 +1,7 @@
 """The four host-pointer calls of a page step from 1-4 host threads, with and
 without a barrier between steps (pages in flight), wall clock per page.
 
-    python tools/e2e_threads.py [steps]
+    python tools/e2e_threads.py [steps] [pageable]
 """
 import ctypes
 import os
@@ -18,10 +18,16 @@ from libpillowfight_b200.pages import A4_300DPI, synthetic_page  # noqa: E402
 lib, chk = _capi.lib, _capi.check
 w, h = A4_300DPI
 K = int(sys.argv[1]) if len(sys.argv) > 1 else 30
+PAGEABLE = len(sys.argv) > 2 and sys.argv[2] == "pageable"     # malloc'ed pages instead of pinned ones
 page = synthetic_page(w, h, 0)
 n = page.nbytes
 NG = 3                                      # Gaussian results in flight (free-running Sobel thread)
-pin = lib.pf_b200_host_alloc((4 + NG) * n)
+if PAGEABLE:
+    import numpy as np
+    heap = np.empty((4 + NG) * n + 4096, dtype=np.uint8)
+    pin = (heap.ctypes.data + 4095) // 4096 * 4096
+else:
+    pin = lib.pf_b200_host_alloc((4 + NG) * n)
 ctypes.memmove(pin, page.ctypes.data, n)
 
 
@@ -107,4 +113,5 @@ cases = [
 for name, groups, barrier, follows in cases:
     best = min(run(groups, barrier, K, follows) for _ in range(2))
     print("%-58s %.3f ms per page = %.0f Mpx/s" % (name, best, w * h / best / 1e3), flush=True)
-lib.pf_b200_host_free(pin)
+if not PAGEABLE:
+    lib.pf_b200_host_free(pin)
