@@ -1,6 +1,6 @@
 """G independent groups of four threads (one per call), pages in flight."""
 import ctypes, os, queue, sys, threading, time
-sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", ".."))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
 import libpillowfight_b200 as pf
 from libpillowfight_b200 import _capi
 from libpillowfight_b200.pages import A4_300DPI, synthetic_page

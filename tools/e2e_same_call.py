@@ -1,5 +1,10 @@
+"""One entry point called from 1-4 host threads at once, each thread on its own pinned
+pages: per-call time in all (what the link gives when calls run side by side).
+
+    python tools/e2e_same_call.py [gaussian sobel canny ace]
+"""
 import ctypes, os, sys, threading, time
-sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", ".."))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
 import libpillowfight_b200 as pf
 from libpillowfight_b200 import _capi
 from libpillowfight_b200.pages import A4_300DPI, synthetic_page
