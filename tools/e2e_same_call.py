@@ -28,16 +28,27 @@ def mk(name, t):
     return lambda: chk(lib.pf_b200_canny(ctypes.byref(bi), ctypes.byref(bo)))
 def run(name, nt, K=30):
     fns = [mk(name, t) for t in range(nt)]
+    gate = threading.Barrier(nt + 1)
+
     def loop(f):
-        for _ in range(K): f()
-    for f in fns:
-        for _ in range(3): f()
+        for _ in range(3):          # (also creates the thread's context in the library)
+            f()
+        gate.wait()
+        for _ in range(K):
+            f()
+        gate.wait()
     ths = [threading.Thread(target=loop, args=(f,)) for f in fns]
+    for th in ths:
+        th.start()
+    gate.wait()
     t0 = time.perf_counter()
-    for th in ths: th.start()
-    for th in ths: th.join()
+    gate.wait()
     dt = (time.perf_counter() - t0) / (K * nt) * 1e3
-    print("%-9s %d threads: %.3f ms per call aggregated (%.1f GB/s each way)" % (name, nt, dt, n / dt / 1e6), flush=True)
+    for th in ths:
+        th.join()
+    print("%-9s %d threads: %.3f ms per call in all (%.1f GB/s each way)" % (name, nt, dt, n / dt / 1e6), flush=True)
+
+
 for name in (sys.argv[1:] or ["gaussian", "sobel", "canny", "ace"]):
     for nt in [1, 2, 3, 4]:
         run(name, nt)
