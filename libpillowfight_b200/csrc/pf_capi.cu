@@ -574,8 +574,8 @@ enum Op { OP_GAUSSIAN, OP_SOBEL, OP_CANNY };
 // so that its own upload, kernels and download overlap; calls that run side by
 // side on several host threads already keep both directions of PCIe busy with
 // each other's pages, and then whole-page DMAs are the better use of the link
-// (measured, 4 threads on one B200: 0.77 ms per Gaussian call in all with one
-// DMA each way, 0.91 ms with 8 bands; alone 1.35 against 1.03 ms).
+// (measured, 2-4 threads on one B200: 0.75 ms per Gaussian call in all with one
+// DMA each way, 0.88 ms with 8 bands; alone 1.30 against 0.96 ms).
 static std::atomic<int> g_calls_in_flight{0};
 static thread_local int t_calls_beside = 0;      // other calls in flight when this one began
 static thread_local int t_call_depth = 0;        // (pf_b200_page_step may go through the single calls)
