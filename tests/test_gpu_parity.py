@@ -142,6 +142,31 @@ def test_canny_short_list_long_chain(gpu, oracle, h):
     assert not ref[30:h - 16, 78:82, 0].any()
 
 
+def test_canny_list_lengths_around_the_short_list_limit(gpu, oracle):
+    """Work lists just under and just over the 2048 entries that one block
+    resolves in shared memory: both paths, and the hand-over between them."""
+    import torch
+    from libpillowfight_b200 import _capi
+    lib = _capi.lib
+    dev = torch.device("cuda:0")
+    seen = []
+    for h in (580, 600, 612, 614, 615, 616, 618, 640):
+        w = 120
+        g = np.zeros((h, w), dtype=np.uint8)
+        g[:, 40:] = 50                 # a weak vertical edge: three weak pixels per row
+        g[:10, 40:] = 120              # strong at the top: the whole chain is kept
+        page = np.stack([g, g, g, np.full_like(g, 255)], axis=-1)
+        tin = torch.from_numpy(page).to(dev)
+        tout = torch.empty_like(tin)
+        scratch = torch.empty(lib.pf_b200_canny_scratch_bytes(w, h), dtype=torch.uint8, device=dev)
+        _capi.check(lib.pf_b200_dev_canny(tin.data_ptr(), tout.data_ptr(), w, h, 1,
+                                          scratch.data_ptr(), scratch.numel(), 0))
+        torch.cuda.synchronize()
+        seen.append(int(scratch[:16].view(torch.int32)[3].item()))     # length of the list just resolved
+        assert np.array_equal(tout.cpu().numpy(), oracle.canny(page)), "h = %d, %d weak pixels" % (h, seen[-1])
+    assert min(seen) < 2048 < max(seen), seen
+
+
 def test_canny_snake_fills_queues(gpu, oracle):
     # dense weak texture seeded by a few strong pixels: a long work list, so the
     # grid-wide union-find path of the hysteresis kernel
